@@ -1,0 +1,1003 @@
+// comd_core.cu -- lifecycle, atom I/O, link-cell binning (counting sort + scan), the atom
+// halo pack/unpack kernels, velocity-Verlet updates and energy reductions for sm_100a.
+//
+// Reference behaviour being replaced (file:line into /root/reference/src-mpi):
+//   updateLinkCellsCpu / updateLinkCellsGpu      linkCells.c:383-405, gpu_kernels.cu:470-504
+//   getBoxFromCoord (ownership rule)             linkCells.c:448-480
+//   loadAtomsBuffer / unloadAtomsBuffer          haloExchange.c:1576-1688
+//   sortAtomsGpu (order inside boundary cells)   gpu_kernels.cu:1014-1043
+//   advanceVelocity / advancePosition            timestep.c:135-180
+//   kineticEnergy / computeEnergy                timestep.c:109-133, gpu_kernels.cu:1046-1059
+#include "comd_dev.cuh"
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+// ------------------------------------------------------------------ errors
+static thread_local char g_err[512] = "";
+void comdSetError(const char* fmt, ...)
+{
+   va_list ap; va_start(ap, fmt); vsnprintf(g_err, sizeof g_err, fmt, ap); va_end(ap);
+}
+extern "C" const char* comd_last_error(void) { return g_err; }
+extern "C" const char* comd_version(void) { return "comd-cuda-async_b200 0.1 (sm_100a)"; }
+
+// ------------------------------------------------------------------ small kernels
+__global__ void k_set_int(int* p, int v, int n)
+{
+   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) p[i] = v;
+}
+
+// start of a redistribute: the source pool is the current sorted array
+__global__ void k_redist_begin(int* cnt)
+{
+   cnt[C_NSRC] = cnt[C_NATOMS];
+   cnt[C_NSHELL] = 0;
+   cnt[C_NLOCAL] = 0;
+   for (int f = 0; f < 6; ++f) { cnt[C_SEND0 + f] = 0; cnt[C_RECV0 + f] = 0; }
+}
+
+// Re-bin: every atom that was local gets its new owner cell (linkCells.c:383-405 +
+// 448-480); last step's ghosts are dropped (emptyHaloCells, linkCells.c:483-487).
+// Atoms whose new cell lies in the 2-plane shell are remembered for the exchange.
+__global__ void __launch_bounds__(256)
+k_rebin(DevGeom g, const double* __restrict__ rx, const double* __restrict__ ry, const double* __restrict__ rz,
+        const int* __restrict__ cellOld, const unsigned char* __restrict__ cellType,
+        int* __restrict__ cellKey, int* __restrict__ cellCount, int* __restrict__ shell, int* __restrict__ cnt)
+{
+   const int n = cnt[C_NATOMS];
+   const int lane = threadIdx.x & 31;
+   const int stride = gridDim.x * blockDim.x;
+   for (int base = blockIdx.x * blockDim.x + (threadIdx.x & ~31); base < n; base += stride)
+   {
+      const int i = base + lane;
+      bool inShell = false;
+      if (i < n)
+      {
+         int key = -1;
+         if (cellType[cellOld[i]] & CT_LOCAL)
+         {
+            int err = 0;
+            key = cellOfPos(g, rx[i], ry[i], rz[i], err);
+            if (err) atomicOr(&cnt[C_ERR], ERRB_ESCAPE);
+            atomicAdd(&cellCount[key], 1);
+            inShell = cellType[key] & CT_SHELL;
+         }
+         cellKey[i] = key;
+      }
+      const unsigned m = __ballot_sync(0xffffffffu, inShell);
+      if (m)
+      {
+         int b = 0;
+         if (lane == 0) b = atomicAdd(&cnt[C_NSHELL], __popc(m));
+         b = __shfl_sync(0xffffffffu, b, 0);
+         if (inShell) shell[b + __popc(m & ((1u << lane) - 1))] = i;
+      }
+   }
+}
+
+// Pack the two faces of one axis: every shell atom whose (new) cell is in the two
+// outermost planes incl. halo cells (mkAtomCellList, haloExchange.c:1543-1567) goes out,
+// shifted by +-globalExtent across a periodic face (loadAtomsBuffer, :1576-1611).
+__global__ void __launch_bounds__(256)
+k_pack_atoms(int axis, const double* __restrict__ rx, const double* __restrict__ ry, const double* __restrict__ rz,
+             const double* __restrict__ px, const double* __restrict__ py, const double* __restrict__ pz,
+             const int* __restrict__ gid, const int* __restrict__ spec,
+             const int* __restrict__ cellKey, const unsigned char* __restrict__ cellType,
+             const int* __restrict__ shell, int* __restrict__ cnt,
+             double* __restrict__ bufM, double* __restrict__ bufP, long msgCap,
+             double shMx, double shMy, double shMz, double shPx, double shPy, double shPz)
+{
+   const int n = cnt[C_NSHELL];
+   const int lane = threadIdx.x & 31;
+   const int stride = gridDim.x * blockDim.x;
+   const int fM = 2 * axis, fP = fM + 1;
+   for (int base = blockIdx.x * blockDim.x + (threadIdx.x & ~31); base < n; base += stride)
+   {
+      const int s = base + lane;
+      int i = -1; unsigned char t = 0;
+      if (s < n) { i = shell[s]; t = cellType[cellKey[i]]; }
+      #pragma unroll
+      for (int d = 0; d < 2; ++d)
+      {
+         const int face = d ? fP : fM;
+         const bool go = (t & CT_FACE(face)) != 0;
+         const unsigned m = __ballot_sync(0xffffffffu, go);
+         if (!m) continue;
+         int b = 0;
+         if (lane == 0) b = atomicAdd(&cnt[C_SEND0 + face], __popc(m));
+         b = __shfl_sync(0xffffffffu, b, 0);
+         if (go)
+         {
+            const long k = b + __popc(m & ((1u << lane) - 1));
+            if (k >= msgCap) { atomicOr(&cnt[C_ERR], ERRB_CAPACITY); continue; }
+            double* o = (d ? bufP : bufM) + k * COMD_MSG_DOUBLES;
+            int2 id = make_int2(gid[i], spec[i]);
+            o[0] = *reinterpret_cast<double*>(&id);
+            o[1] = rx[i] + (d ? shPx : shMx);
+            o[2] = ry[i] + (d ? shPy : shMy);
+            o[3] = rz[i] + (d ? shPz : shMz);
+            o[4] = px[i]; o[5] = py[i]; o[6] = pz[i];
+         }
+      }
+   }
+}
+
+// Unpack one received message: putAtomInBox for every atom (unloadAtomsBuffer,
+// haloExchange.c:1649-1688; linkCells.c:228-256): it joins the source pool with the cell its
+// coordinates select, so ownership transfers by position alone.
+__global__ void __launch_bounds__(256)
+k_unpack_atoms(DevGeom g, const double* __restrict__ buf, const int* __restrict__ nRecvPtr,
+               double* __restrict__ rx, double* __restrict__ ry, double* __restrict__ rz,
+               double* __restrict__ px, double* __restrict__ py, double* __restrict__ pz,
+               int* __restrict__ gid, int* __restrict__ spec,
+               int* __restrict__ cellKey, int* __restrict__ cellCount, int* __restrict__ shell,
+               int* __restrict__ cnt, long cap)
+{
+   const int n = *nRecvPtr;
+   const int lane = threadIdx.x & 31;
+   const int stride = gridDim.x * blockDim.x;
+   for (int base = blockIdx.x * blockDim.x + (threadIdx.x & ~31); base < n; base += stride)
+   {
+      const int k = base + lane;
+      const bool have = k < n;
+      const unsigned m = __ballot_sync(0xffffffffu, have);
+      int b = 0, bs = 0;
+      if (lane == 0) { b = atomicAdd(&cnt[C_NSRC], __popc(m)); bs = atomicAdd(&cnt[C_NSHELL], __popc(m)); }
+      b = __shfl_sync(0xffffffffu, b, 0);
+      bs = __shfl_sync(0xffffffffu, bs, 0);
+      if (!have) continue;
+      const long j = b + lane;            // lanes with `have` are a prefix of the warp
+      if (j >= cap) { atomicOr(&cnt[C_ERR], ERRB_CAPACITY); continue; }
+      const double* in = buf + (long)k * COMD_MSG_DOUBLES;
+      double w = in[0];
+      int2 id = *reinterpret_cast<int2*>(&w);
+      const double x = in[1], y = in[2], z = in[3];
+      int err = 0;
+      const int c = cellOfPos(g, x, y, z, err);
+      if (err) atomicOr(&cnt[C_ERR], ERRB_ESCAPE);
+      gid[j] = id.x; spec[j] = id.y;
+      rx[j] = x; ry[j] = y; rz[j] = z;
+      px[j] = in[4]; py[j] = in[5]; pz[j] = in[6];
+      cellKey[j] = c;
+      atomicAdd(&cellCount[c], 1);
+      shell[bs + lane] = (int)j;
+   }
+}
+
+// ---- exclusive scan of the per-cell histogram -> cellStart (replaces the CUB call of
+// gpu_scan.h:34-39).  Three small launches: tile scan, scan of tile sums, add back.
+#define SCAN_TILE 2048
+__global__ void __launch_bounds__(1024)
+k_scan_tiles(const int* __restrict__ in, int* __restrict__ out, int* __restrict__ tileSum, int n)
+{
+   __shared__ int warpSum[32];
+   const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+   const int i0 = blockIdx.x * SCAN_TILE + 2 * t;
+   int a = i0 < n ? in[i0] : 0, b = i0 + 1 < n ? in[i0 + 1] : 0;
+   int v = a + b, incl = v;
+   #pragma unroll
+   for (int o = 1; o < 32; o <<= 1) { int u = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += u; }
+   if (lane == 31) warpSum[w] = incl;
+   __syncthreads();
+   if (w == 0)
+   {
+      int s = warpSum[lane], si = s;
+      #pragma unroll
+      for (int o = 1; o < 32; o <<= 1) { int u = __shfl_up_sync(0xffffffffu, si, o); if (lane >= o) si += u; }
+      warpSum[lane] = si - s;
+      if (lane == 31) tileSum[blockIdx.x] = si;
+   }
+   __syncthreads();
+   const int excl = incl - v + warpSum[w];
+   if (i0 < n) out[i0] = excl;
+   if (i0 + 1 < n) out[i0 + 1] = excl + a;
+}
+__global__ void __launch_bounds__(1024)
+k_scan_sums(int* __restrict__ tileSum, int nTiles, int* __restrict__ cellStart, int nCells, int* __restrict__ cnt)
+{
+   __shared__ int warpSum[32];
+   __shared__ int carry;
+   const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+   if (t == 0) carry = 0;
+   __syncthreads();
+   for (int base = 0; base < nTiles; base += 1024)
+   {
+      const int i = base + t;
+      const int v = i < nTiles ? tileSum[i] : 0;
+      int incl = v;
+      #pragma unroll
+      for (int o = 1; o < 32; o <<= 1) { int u = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += u; }
+      if (lane == 31) warpSum[w] = incl;
+      __syncthreads();
+      if (w == 0)
+      {
+         int s = warpSum[lane], si = s;
+         #pragma unroll
+         for (int o = 1; o < 32; o <<= 1) { int u = __shfl_up_sync(0xffffffffu, si, o); if (lane >= o) si += u; }
+         warpSum[lane] = si - s;
+      }
+      __syncthreads();
+      const int excl = incl - v + warpSum[w] + carry;
+      if (i < nTiles) tileSum[i] = excl;
+      __syncthreads();
+      if (t == 1023) carry = excl + v;
+      __syncthreads();
+   }
+   if (t == 0) { cellStart[nCells] = carry; cnt[C_NATOMS] = carry; }
+}
+__global__ void k_scan_add(int* __restrict__ cellStart, const int* __restrict__ tileSum, int n)
+{
+   const int i = blockIdx.x * blockDim.x + threadIdx.x;
+   if (i < n) cellStart[i] += tileSum[i / SCAN_TILE];
+}
+
+// counting-sort scatter: (gid, source index, cell) of every pool atom lands in its cell's
+// segment; the order inside the segment is whatever the atomics give and is fixed next.
+__global__ void __launch_bounds__(256)
+k_scatter(const int* __restrict__ cellKey, const int* __restrict__ gid, const int* __restrict__ cellStart,
+          int* __restrict__ cellFill, int* __restrict__ tmpSrc, int* __restrict__ tmpGid, int* __restrict__ tmpCell,
+          int* __restrict__ cnt, long cap)
+{
+   const int n = cnt[C_NSRC];
+   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+   {
+      const int c = cellKey[i];
+      if (c < 0) continue;
+      const long pos = cellStart[c] + atomicAdd(&cellFill[c], 1);
+      if (pos >= cap) { atomicOr(&cnt[C_ERR], ERRB_CAPACITY); continue; }
+      tmpSrc[pos] = i; tmpGid[pos] = gid[i]; tmpCell[pos] = c;
+   }
+}
+
+// Canonical order + payload move: inside its cell every atom takes the rank of its gid
+// (ascending), which makes the layout -- hence every summation order downstream --
+// independent of atomics and identical on sender and receiver (what sortAtomsGpu /
+// sortAtomsInCell aim for, gpu_kernels.cu:1014, haloExchange.c:1926-1981).
+__global__ void __launch_bounds__(256)
+k_rank_gather(const int* __restrict__ tmpSrc, const int* __restrict__ tmpGid, const int* __restrict__ tmpCell,
+              const int* __restrict__ cellStart, const unsigned char* __restrict__ cellType,
+              AtomArrays src, AtomArrays dst, int* __restrict__ cnt)
+{
+   const int n = cnt[C_NATOMS];
+   const int lane = threadIdx.x & 31;
+   const int stride = gridDim.x * blockDim.x;
+   for (int base = blockIdx.x * blockDim.x + (threadIdx.x & ~31); base < n; base += stride)
+   {
+      const int t = base + lane;
+      bool isLocal = false;
+      if (t < n)
+      {
+         const int c = tmpCell[t], g = tmpGid[t];
+         const int b = cellStart[c], e = cellStart[c + 1];
+         int rank = 0;
+         for (int u = b; u < e; ++u) { const int gu = tmpGid[u]; rank += (gu < g) || (gu == g && u < t); }
+         const int d = b + rank, s = tmpSrc[t];
+         dst.r[0][d] = src.r[0][s]; dst.r[1][d] = src.r[1][s]; dst.r[2][d] = src.r[2][s];
+         dst.p[0][d] = src.p[0][s]; dst.p[1][d] = src.p[1][s]; dst.p[2][d] = src.p[2][s];
+         dst.gid[d] = g; dst.spec[d] = src.spec[s]; dst.cell[d] = c;
+         isLocal = cellType[c] & CT_LOCAL;
+      }
+      const unsigned m = __ballot_sync(0xffffffffu, isLocal);
+      if (m && lane == 0) atomicAdd(&cnt[C_NLOCAL], __popc(m));
+   }
+}
+
+// ---- integrator (timestep.c:143-176).  __dmul_rn/__dadd_rn keep the host's operation
+// order (no FMA contraction) so positions, hence cell ids, track the CPU path bit by bit
+// for as long as the forces do.
+__global__ void __launch_bounds__(256)
+k_advance_velocity(double dt, const int* __restrict__ cell, const unsigned char* __restrict__ cellType,
+                   double* __restrict__ px, double* __restrict__ py, double* __restrict__ pz,
+                   const double* __restrict__ fx, const double* __restrict__ fy, const double* __restrict__ fz,
+                   const int* __restrict__ cnt)
+{
+   const int n = cnt[C_NATOMS];
+   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+   {
+      if (!(cellType[cell[i]] & CT_LOCAL)) continue;
+      px[i] = __dadd_rn(px[i], __dmul_rn(dt, fx[i]));
+      py[i] = __dadd_rn(py[i], __dmul_rn(dt, fy[i]));
+      pz[i] = __dadd_rn(pz[i], __dmul_rn(dt, fz[i]));
+   }
+}
+__global__ void __launch_bounds__(256)
+k_advance_position(double dt, double invMass, const int* __restrict__ cell, const unsigned char* __restrict__ cellType,
+                   double* __restrict__ rx, double* __restrict__ ry, double* __restrict__ rz,
+                   const double* __restrict__ px, const double* __restrict__ py, const double* __restrict__ pz,
+                   const int* __restrict__ cnt)
+{
+   const int n = cnt[C_NATOMS];
+   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+   {
+      if (!(cellType[cell[i]] & CT_LOCAL)) continue;
+      rx[i] = __dadd_rn(rx[i], __dmul_rn(__dmul_rn(dt, px[i]), invMass));
+      ry[i] = __dadd_rn(ry[i], __dmul_rn(__dmul_rn(dt, py[i]), invMass));
+      rz[i] = __dadd_rn(rz[i], __dmul_rn(__dmul_rn(dt, pz[i]), invMass));
+   }
+}
+// first half of a step in one pass: p += dt/2 f ; r += dt p / m
+__global__ void __launch_bounds__(256)
+k_kick_drift(double dtHalf, double dt, double invMass, const int* __restrict__ cell, const unsigned char* __restrict__ cellType,
+             double* __restrict__ rx, double* __restrict__ ry, double* __restrict__ rz,
+             double* __restrict__ px, double* __restrict__ py, double* __restrict__ pz,
+             const double* __restrict__ fx, const double* __restrict__ fy, const double* __restrict__ fz,
+             const int* __restrict__ cnt)
+{
+   const int n = cnt[C_NATOMS];
+   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+   {
+      if (!(cellType[cell[i]] & CT_LOCAL)) continue;
+      const double a = __dadd_rn(px[i], __dmul_rn(dtHalf, fx[i]));
+      const double b = __dadd_rn(py[i], __dmul_rn(dtHalf, fy[i]));
+      const double c = __dadd_rn(pz[i], __dmul_rn(dtHalf, fz[i]));
+      px[i] = a; py[i] = b; pz[i] = c;
+      rx[i] = __dadd_rn(rx[i], __dmul_rn(__dmul_rn(dt, a), invMass));
+      ry[i] = __dadd_rn(ry[i], __dmul_rn(__dmul_rn(dt, b), invMass));
+      rz[i] = __dadd_rn(rz[i], __dmul_rn(__dmul_rn(dt, c), invMass));
+   }
+}
+
+// ---- energy: deterministic two-level reduction (fixed grid, fixed tree); replaces
+// ReduceEnergy's atomicAdd(double) (gpu_reduce.h:32-98).
+#define RED_BLOCKS 592
+__global__ void __launch_bounds__(256)
+k_energy_partial(double halfInvMass, const int* __restrict__ cell, const unsigned char* __restrict__ cellType,
+                 const double* __restrict__ e, const double* __restrict__ px, const double* __restrict__ py,
+                 const double* __restrict__ pz, const int* __restrict__ cnt, double* __restrict__ partial)
+{
+   __shared__ double sU[8], sK[8];
+   const int n = cnt[C_NATOMS];
+   double u = 0.0, k = 0.0;
+   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+   {
+      if (!(cellType[cell[i]] & CT_LOCAL)) continue;
+      u += e[i];
+      k += (px[i] * px[i] + py[i] * py[i] + pz[i] * pz[i]) * halfInvMass;
+   }
+   #pragma unroll
+   for (int o = 16; o > 0; o >>= 1) { u += __shfl_down_sync(0xffffffffu, u, o); k += __shfl_down_sync(0xffffffffu, k, o); }
+   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+   if (lane == 0) { sU[w] = u; sK[w] = k; }
+   __syncthreads();
+   if (threadIdx.x == 0)
+   {
+      double a = 0.0, b = 0.0;
+      for (int i = 0; i < 8; ++i) { a += sU[i]; b += sK[i]; }
+      partial[2 * blockIdx.x] = a; partial[2 * blockIdx.x + 1] = b;
+   }
+}
+__global__ void __launch_bounds__(1024)
+k_energy_final(const double* __restrict__ partial, int nPart, double* __restrict__ out)
+{
+   __shared__ double sU[32], sK[32];
+   double u = 0.0, k = 0.0;
+   for (int i = threadIdx.x; i < nPart; i += 1024) { u += partial[2 * i]; k += partial[2 * i + 1]; }
+   #pragma unroll
+   for (int o = 16; o > 0; o >>= 1) { u += __shfl_down_sync(0xffffffffu, u, o); k += __shfl_down_sync(0xffffffffu, k, o); }
+   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+   if (lane == 0) { sU[w] = u; sK[w] = k; }
+   __syncthreads();
+   if (threadIdx.x == 0)
+   {
+      double a = 0.0, b = 0.0;
+      for (int i = 0; i < 32; ++i) { a += sU[i]; b += sK[i]; }
+      out[0] = a; out[1] = b;
+   }
+}
+
+// ------------------------------------------------------------------ host side
+static int allocAtoms(AtomArrays& a, long cap)
+{
+   for (int k = 0; k < 3; ++k)
+   {
+      CUDA_TRY(cudaMalloc(&a.r[k], cap * sizeof(double)));
+      CUDA_TRY(cudaMalloc(&a.p[k], cap * sizeof(double)));
+   }
+   CUDA_TRY(cudaMalloc(&a.gid, cap * sizeof(int)));
+   CUDA_TRY(cudaMalloc(&a.spec, cap * sizeof(int)));
+   CUDA_TRY(cudaMalloc(&a.cell, cap * sizeof(int)));
+   return COMD_OK;
+}
+static void freeAtoms(AtomArrays& a)
+{
+   for (int k = 0; k < 3; ++k) { cudaFree(a.r[k]); cudaFree(a.p[k]); }
+   cudaFree(a.gid); cudaFree(a.spec); cudaFree(a.cell);
+}
+
+extern "C" int comd_dev_create(ComdDev** out, int deviceId, const ComdGeometry* geom, long atomCapacity)
+{
+   if (!out || !geom || atomCapacity <= 0) { comdSetError("comd_dev_create: bad argument"); return COMD_E_ARG; }
+   for (int a = 0; a < 3; ++a)
+      if (geom->gridSize[a] < 2) { comdSetError("comd_dev_create: gridSize[%d]=%d < 2 (linkCells.c:181)", a, geom->gridSize[a]); return COMD_E_ARG; }
+   int nDev = 0;
+   if (cudaGetDeviceCount(&nDev) != cudaSuccess || nDev == 0)
+   {
+      comdSetError("comd_dev_create: no CUDA device (this library has no CPU fallback)");
+      return COMD_E_CUDA;
+   }
+   CUDA_TRY(cudaSetDevice(deviceId));
+   ComdDev* d = new ComdDev();
+   memset(d, 0, sizeof(ComdDev));
+   d->device = deviceId;
+   d->hostGeom = *geom;
+   DevGeom& g = d->g;
+   for (int a = 0; a < 3; ++a)
+   {
+      g.n[a] = geom->gridSize[a]; g.P[a] = g.n[a] + 2;
+      g.lMin[a] = geom->localMin[a]; g.lMax[a] = geom->localMax[a]; g.inv[a] = geom->invBoxSize[a];
+   }
+   g.nCells = g.P[0] * g.P[1] * g.P[2];
+   d->cap = atomCapacity;
+   d->rank = 0; d->nRanks = 1;
+   // neighbours + periodic shifts exactly as initHaloExchange / initAtomHaloExchange
+   // (haloExchange.c:756-770, 310-323; processorNum, decomposition.c:57-66)
+   for (int f = 0; f < 6; ++f)
+   {
+      const int ax = f / 2, dir = (f % 2) ? +1 : -1;
+      int pc[3] = { geom->procCoord[0], geom->procCoord[1], geom->procCoord[2] };
+      pc[ax] = (pc[ax] + dir + geom->procGrid[ax]) % geom->procGrid[ax];
+      d->nbrRank[f] = pc[0] + geom->procGrid[0] * (pc[1] + geom->procGrid[1] * pc[2]);
+      for (int a = 0; a < 3; ++a) d->shift[f][a] = 0.0;
+      if (dir < 0 && geom->procCoord[ax] == 0) d->shift[f][ax] = +1.0 * geom->globalExtent[ax];
+      if (dir > 0 && geom->procCoord[ax] == geom->procGrid[ax] - 1) d->shift[f][ax] = -1.0 * geom->globalExtent[ax];
+   }
+   d->rank = geom->procCoord[0] + geom->procGrid[0] * (geom->procCoord[1] + geom->procGrid[1] * geom->procCoord[2]);
+   d->nRanks = geom->procGrid[0] * geom->procGrid[1] * geom->procGrid[2];
+
+   CUDA_TRY(cudaStreamCreateWithFlags(&d->stream, cudaStreamNonBlocking));
+   for (int k = 0; k < 256; ++k) CUDA_TRY(cudaEventCreate(&d->evForce[k]));
+   CUDA_TRY(cudaEventCreate(&d->evT0)); CUDA_TRY(cudaEventCreate(&d->evT1));
+   const long cap = d->cap;
+   int rc;
+   if ((rc = allocAtoms(d->A, cap)) != COMD_OK) return rc;
+   if ((rc = allocAtoms(d->B, cap)) != COMD_OK) return rc;
+   for (int k = 0; k < 3; ++k) { CUDA_TRY(cudaMalloc(&d->f[k], cap * sizeof(double))); CUDA_TRY(cudaMemset(d->f[k], 0, cap * sizeof(double))); }
+   CUDA_TRY(cudaMalloc(&d->e, cap * sizeof(double))); CUDA_TRY(cudaMemset(d->e, 0, cap * sizeof(double)));
+   CUDA_TRY(cudaMalloc(&d->cellStart, (g.nCells + 1) * sizeof(int)));
+   CUDA_TRY(cudaMemset(d->cellStart, 0, (g.nCells + 1) * sizeof(int)));
+   CUDA_TRY(cudaMalloc(&d->cellCount, g.nCells * sizeof(int)));
+   CUDA_TRY(cudaMalloc(&d->cellFill, g.nCells * sizeof(int)));
+   CUDA_TRY(cudaMalloc(&d->cellType, g.nCells));
+   CUDA_TRY(cudaMalloc(&d->cellKey, cap * sizeof(int)));
+   CUDA_TRY(cudaMalloc(&d->shell, cap * sizeof(int)));
+   CUDA_TRY(cudaMalloc(&d->tmpSrc, cap * sizeof(int)));
+   CUDA_TRY(cudaMalloc(&d->tmpGid, cap * sizeof(int)));
+   CUDA_TRY(cudaMalloc(&d->tmpCell, cap * sizeof(int)));
+   CUDA_TRY(cudaMalloc(&d->scanBlock, ((g.nCells + SCAN_TILE - 1) / SCAN_TILE + 1) * sizeof(int)));
+   CUDA_TRY(cudaMalloc(&d->cnt, C_COUNT * sizeof(int)));
+   CUDA_TRY(cudaMemset(d->cnt, 0, C_COUNT * sizeof(int)));
+   CUDA_TRY(cudaMallocHost(&d->hCnt, C_COUNT * sizeof(int)));
+   CUDA_TRY(cudaMalloc(&d->redPartial, 2 * RED_BLOCKS * sizeof(double)));
+   CUDA_TRY(cudaMalloc(&d->redOut, 2 * sizeof(double)));
+   CUDA_TRY(cudaMallocHost(&d->hRed, 2 * sizeof(double)));
+   CUDA_TRY(cudaMalloc(&d->rhobar, cap * sizeof(double)));
+   CUDA_TRY(cudaMalloc(&d->dfEmbed, cap * sizeof(double)));
+   CUDA_TRY(cudaMemset(d->dfEmbed, 0, cap * sizeof(double)));
+
+   // message capacity: the two largest planes of cells, generously populated
+   // (bufCapacity, haloExchange.c:202-207, sized without MAXATOMS padding)
+   long plane = 0;
+   for (int a = 0; a < 3; ++a)
+   {
+      long p = (long)g.P[(a + 1) % 3] * g.P[(a + 2) % 3];
+      if (p > plane) plane = p;
+   }
+   const double perCell = (double)cap / (double)g.nCells;
+   d->msgCap = (long)(2 * plane * (perCell * 1.5 + 8)) + 1024;
+   if (d->msgCap > cap) d->msgCap = cap;
+   for (int k = 0; k < 2; ++k)
+   {
+      CUDA_TRY(cudaMalloc(&d->sendBuf[k], d->msgCap * COMD_MSG_DOUBLES * sizeof(double)));
+      CUDA_TRY(cudaMalloc(&d->recvBuf[k], d->msgCap * COMD_MSG_DOUBLES * sizeof(double)));
+      CUDA_TRY(cudaMalloc(&d->fpSend[k], d->msgCap * sizeof(double)));
+      CUDA_TRY(cudaMalloc(&d->fpRecv[k], d->msgCap * sizeof(double)));
+   }
+   CUDA_TRY(cudaMalloc(&d->runOff, (plane + 2) * 24 * sizeof(int)));
+
+   // cell classes
+   std::vector<unsigned char> ct(g.nCells, 0);
+   for (int z = 0; z < g.P[2]; ++z) for (int y = 0; y < g.P[1]; ++y) for (int x = 0; x < g.P[0]; ++x)
+   {
+      const int q[3] = { x, y, z };
+      unsigned char t = 0;
+      if (x >= 1 && x <= g.n[0] && y >= 1 && y <= g.n[1] && z >= 1 && z <= g.n[2]) t |= CT_LOCAL;
+      for (int a = 0; a < 3; ++a)
+      {
+         if (q[a] <= 1) t |= CT_FACE(2 * a);
+         if (q[a] >= g.P[a] - 2) t |= CT_FACE(2 * a + 1);
+      }
+      if (t & ~CT_LOCAL) t |= CT_SHELL;
+      ct[x + g.P[0] * (y + g.P[1] * z)] = t;
+   }
+   CUDA_TRY(cudaMemcpy(d->cellType, ct.data(), g.nCells, cudaMemcpyHostToDevice));
+   d->approxAtoms = 0;
+   d->mass = 1.0;
+   *out = d;
+   return COMD_OK;
+}
+
+extern "C" int comd_dev_destroy(ComdDev* d)
+{
+   if (!d) return COMD_OK;
+   cudaSetDevice(d->device);
+   cudaStreamSynchronize(d->stream);
+   freeAtoms(d->A); freeAtoms(d->B);
+   for (int k = 0; k < 3; ++k) { cudaFree(d->f[k]); cudaFree(d->nlLastR[k]); }
+   cudaFree(d->e); cudaFree(d->cellStart); cudaFree(d->cellCount); cudaFree(d->cellFill); cudaFree(d->cellType);
+   cudaFree(d->cellKey); cudaFree(d->shell); cudaFree(d->tmpSrc); cudaFree(d->tmpGid); cudaFree(d->tmpCell);
+   cudaFree(d->scanBlock); cudaFree(d->cnt); cudaFreeHost(d->hCnt); cudaFree(d->redPartial); cudaFree(d->redOut);
+   cudaFreeHost(d->hRed); cudaFree(d->rhobar); cudaFree(d->dfEmbed); cudaFree(d->tabMem); cudaFree(d->runOff);
+   cudaFree(d->nlList); cudaFree(d->nlCount);
+   for (int k = 0; k < 2; ++k) { cudaFree(d->sendBuf[k]); cudaFree(d->recvBuf[k]); cudaFree(d->fpSend[k]); cudaFree(d->fpRecv[k]); }
+   if (d->hStage) cudaFreeHost(d->hStage);
+   for (int k = 0; k < 256; ++k) cudaEventDestroy(d->evForce[k]);
+   cudaEventDestroy(d->evT0); cudaEventDestroy(d->evT1);
+   cudaStreamDestroy(d->stream);
+   delete d;
+   return COMD_OK;
+}
+
+extern "C" int comd_dev_set_mass(ComdDev* d, double m)
+{
+   if (!d || !(m > 0.0)) { comdSetError("comd_dev_set_mass: bad argument"); return COMD_E_ARG; }
+   d->mass = m;
+   return COMD_OK;
+}
+
+extern "C" int comd_dev_set_lj(ComdDev* d, double sigma, double epsilon, double cutoff)
+{
+   if (!d || !(cutoff > 0.0)) { comdSetError("comd_dev_set_lj: bad argument"); return COMD_E_ARG; }
+   for (int a = 0; a < 3; ++a)
+      if (d->hostGeom.boxSize[a] < cutoff)
+      { comdSetError("comd_dev_set_lj: cell size %g < cutoff %g on axis %d", d->hostGeom.boxSize[a], cutoff, a); return COMD_E_ARG; }
+   d->potKind = 1; d->ljSigma = sigma; d->ljEps = epsilon; d->cutoff = cutoff;
+   return COMD_OK;
+}
+
+extern "C" int comd_dev_set_eam(ComdDev* d, double cutoff, const ComdTable* phi, const ComdTable* rho, const ComdTable* f)
+{
+   if (!d || !phi || !rho || !f || !(cutoff > 0.0)) { comdSetError("comd_dev_set_eam: bad argument"); return COMD_E_ARG; }
+   for (int a = 0; a < 3; ++a)
+      if (d->hostGeom.boxSize[a] < cutoff)
+      { comdSetError("comd_dev_set_eam: cell size %g < cutoff %g on axis %d", d->hostGeom.boxSize[a], cutoff, a); return COMD_E_ARG; }
+   CUDA_TRY(cudaSetDevice(d->device));
+   const ComdTable* t[3] = { phi, rho, f };
+   long total = 0;
+   for (int k = 0; k < 3; ++k) total += t[k]->n + 3 + 1;
+   if (d->tabMem) cudaFree(d->tabMem);
+   CUDA_TRY(cudaMalloc(&d->tabMem, total * sizeof(double)));
+   DevTable* out[3] = { &d->tPhi, &d->tRho, &d->tF };
+   long off = 0;
+   for (int k = 0; k < 3; ++k)
+   {
+      const int n = t[k]->n;
+      CUDA_TRY(cudaMemcpy(d->tabMem + off, t[k]->values - 1, (n + 3) * sizeof(double), cudaMemcpyHostToDevice));
+      out[k]->n = n; out[k]->x0 = t[k]->x0; out[k]->invDx = t[k]->invDx; out[k]->v = d->tabMem + off + 1;
+      off += n + 3 + ((n + 3) & 1);      // keep every table 16-byte aligned
+   }
+   d->potKind = 2; d->cutoff = cutoff;
+   return COMD_OK;
+}
+
+int comdCheckErrors(ComdDev* d, const char* where)
+{
+   // caller has synchronised and refreshed hCnt
+   const int e = d->hCnt[C_ERR];
+   if (!e) return COMD_OK;
+   if (e & ERRB_CAPACITY) { comdSetError("%s: atom or message capacity exceeded (capacity %ld atoms)", where, d->cap); return COMD_E_CAPACITY; }
+   if (e & ERRB_ESCAPE) { comdSetError("%s: an atom moved more than one link cell beyond the local domain in one step", where); return COMD_E_STATE; }
+   if (e & ERRB_FPMISMATCH) { comdSetError("%s: F' halo message does not match the ghost population", where); return COMD_E_MISMATCH; }
+   if (e & ERRB_NLFULL) { comdSetError("%s: neighbour-list row overflow", where); return COMD_E_CAPACITY; }
+   comdSetError("%s: device error bits 0x%x", where, e);
+   return COMD_E_STATE;
+}
+
+static int syncCounters(ComdDev* d, const char* where)
+{
+   CUDA_TRY(cudaMemcpyAsync(d->hCnt, d->cnt, C_COUNT * sizeof(int), cudaMemcpyDeviceToHost, d->stream));
+   CUDA_TRY(cudaStreamSynchronize(d->stream));
+   d->approxAtoms = d->hCnt[C_NATOMS];
+   return comdCheckErrors(d, where);
+}
+
+extern "C" int comd_dev_sync(ComdDev* d)
+{
+   if (!d) return COMD_E_ARG;
+   CUDA_TRY(cudaSetDevice(d->device));
+   return syncCounters(d, "comd_dev_sync");
+}
+
+extern "C" int comd_dev_redistribute(ComdDev* d)
+{
+   if (!d) return COMD_E_ARG;
+   CUDA_TRY(cudaSetDevice(d->device));
+   const DevGeom& g = d->g;
+   cudaStream_t s = d->stream;
+   const int nGuess = d->approxAtoms > 0 ? d->approxAtoms : (int)d->cap;
+   CUDA_TRY(cudaMemsetAsync(d->cellCount, 0, g.nCells * sizeof(int), s));
+   CUDA_TRY(cudaMemsetAsync(d->cellFill, 0, g.nCells * sizeof(int), s));
+   k_redist_begin<<<1, 1, 0, s>>>(d->cnt); LAUNCH_CHECK(d);
+   AtomArrays& A = d->A;
+   k_rebin<<<gridFor(nGuess, 256), 256, 0, s>>>(g, A.r[0], A.r[1], A.r[2], A.cell, d->cellType, d->cellKey,
+                                                 d->cellCount, d->shell, d->cnt); LAUNCH_CHECK(d);
+   const int nShellGuess = nGuess;   // grid-stride: any grid is correct
+   for (int ax = 0; ax < 3; ++ax)
+   {
+      const int fM = 2 * ax, fP = fM + 1;
+      k_pack_atoms<<<gridFor(nShellGuess, 256, 148 * 4), 256, 0, s>>>(ax, A.r[0], A.r[1], A.r[2], A.p[0], A.p[1], A.p[2],
+         A.gid, A.spec, d->cellKey, d->cellType, d->shell, d->cnt, d->sendBuf[0], d->sendBuf[1], d->msgCap,
+         d->shift[fM][0], d->shift[fM][1], d->shift[fM][2], d->shift[fP][0], d->shift[fP][1], d->shift[fP][2]); LAUNCH_CHECK(d);
+      int rc = comdExchangeAtomsPhase(d, ax);
+      if (rc != COMD_OK) return rc;
+      // unload order: the message that came across the - face first (haloExchange.c:1518-1519)
+      for (int k = 0; k < 2; ++k)
+      {
+         k_unpack_atoms<<<gridFor(nShellGuess / 8 + 1, 256, 148 * 2), 256, 0, s>>>(g, d->recvBuf[k], d->cnt + C_RECV0 + fM + k,
+            A.r[0], A.r[1], A.r[2], A.p[0], A.p[1], A.p[2], A.gid, A.spec, d->cellKey, d->cellCount, d->shell, d->cnt, d->cap);
+         LAUNCH_CHECK(d);
+      }
+   }
+   const int nTiles = (g.nCells + SCAN_TILE - 1) / SCAN_TILE;
+   k_scan_tiles<<<nTiles, 1024, 0, s>>>(d->cellCount, d->cellStart, d->scanBlock, g.nCells); LAUNCH_CHECK(d);
+   k_scan_sums<<<1, 1024, 0, s>>>(d->scanBlock, nTiles, d->cellStart, g.nCells, d->cnt); LAUNCH_CHECK(d);
+   k_scan_add<<<(g.nCells + 255) / 256, 256, 0, s>>>(d->cellStart, d->scanBlock, g.nCells); LAUNCH_CHECK(d);
+   k_scatter<<<gridFor(nGuess, 256), 256, 0, s>>>(d->cellKey, A.gid, d->cellStart, d->cellFill, d->tmpSrc, d->tmpGid,
+                                                   d->tmpCell, d->cnt, d->cap); LAUNCH_CHECK(d);
+   k_rank_gather<<<gridFor(nGuess, 256), 256, 0, s>>>(d->tmpSrc, d->tmpGid, d->tmpCell, d->cellStart, d->cellType,
+                                                       d->A, d->B, d->cnt); LAUNCH_CHECK(d);
+   AtomArrays t = d->A; d->A = d->B; d->B = t;
+   d->nlValid = 0;
+   return COMD_OK;
+}
+
+extern "C" int comd_dev_upload_atoms(ComdDev* d, int n, const int* gid, const int* species,
+                                     const double* rx, const double* ry, const double* rz,
+                                     const double* px, const double* py, const double* pz)
+{
+   if (!d || n < 0 || !gid || !rx || !ry || !rz) { comdSetError("comd_dev_upload_atoms: bad argument"); return COMD_E_ARG; }
+   if (n > d->cap) { comdSetError("comd_dev_upload_atoms: %d atoms > capacity %ld", n, d->cap); return COMD_E_CAPACITY; }
+   CUDA_TRY(cudaSetDevice(d->device));
+   cudaStream_t s = d->stream;
+   AtomArrays& A = d->A;
+   const double* hr[3] = { rx, ry, rz };
+   const double* hp[3] = { px, py, pz };
+   for (int k = 0; k < 3; ++k)
+   {
+      CUDA_TRY(cudaMemcpyAsync(A.r[k], hr[k], n * sizeof(double), cudaMemcpyHostToDevice, s));
+      if (hp[k]) CUDA_TRY(cudaMemcpyAsync(A.p[k], hp[k], n * sizeof(double), cudaMemcpyHostToDevice, s));
+      else CUDA_TRY(cudaMemsetAsync(A.p[k], 0, n * sizeof(double), s));
+      CUDA_TRY(cudaMemsetAsync(d->f[k], 0, d->cap * sizeof(double), s));
+   }
+   CUDA_TRY(cudaMemsetAsync(d->e, 0, d->cap * sizeof(double), s));
+   CUDA_TRY(cudaMemcpyAsync(A.gid, gid, n * sizeof(int), cudaMemcpyHostToDevice, s));
+   if (species) CUDA_TRY(cudaMemcpyAsync(A.spec, species, n * sizeof(int), cudaMemcpyHostToDevice, s));
+   else CUDA_TRY(cudaMemsetAsync(A.spec, 0, n * sizeof(int), s));
+   // mark everything "was local" so the re-bin keeps it: any local cell id will do
+   k_set_int<<<gridFor(n, 256), 256, 0, s>>>(A.cell, cellIndex(d->g, 0, 0, 0), n); LAUNCH_CHECK(d);
+   k_set_int<<<1, 1, 0, s>>>(d->cnt + C_NATOMS, n, 1); LAUNCH_CHECK(d);
+   k_set_int<<<1, 1, 0, s>>>(d->cnt + C_ERR, 0, 1); LAUNCH_CHECK(d);
+   d->approxAtoms = n;
+   int rc = comd_dev_redistribute(d);
+   if (rc != COMD_OK) return rc;
+   return syncCounters(d, "comd_dev_upload_atoms");
+}
+
+extern "C" int comd_dev_num_local(ComdDev* d, int* nLocal)
+{
+   if (!d || !nLocal) return COMD_E_ARG;
+   CUDA_TRY(cudaSetDevice(d->device));
+   int rc = syncCounters(d, "comd_dev_num_local");
+   *nLocal = d->hCnt[C_NLOCAL];
+   return rc;
+}
+extern "C" int comd_dev_num_total(ComdDev* d, int* n)
+{
+   if (!d || !n) return COMD_E_ARG;
+   CUDA_TRY(cudaSetDevice(d->device));
+   int rc = syncCounters(d, "comd_dev_num_total");
+   *n = d->hCnt[C_NATOMS];
+   return rc;
+}
+
+static int downloadCommon(ComdDev* d, bool localOnly, int* nOut, int capacity, int* gid, int* species, int* refBox,
+                          double* r[3], double* p[3], double* f[3], double* U)
+{
+   CUDA_TRY(cudaSetDevice(d->device));
+   int rc = syncCounters(d, "comd_dev_download");
+   if (rc != COMD_OK) return rc;
+   const int n = d->hCnt[C_NATOMS];
+   std::vector<int> cell(n), tmpI(n);
+   std::vector<unsigned char> ct(d->g.nCells);
+   std::vector<double> tmpD(n);
+   CUDA_TRY(cudaMemcpy(cell.data(), d->A.cell, n * sizeof(int), cudaMemcpyDeviceToHost));
+   CUDA_TRY(cudaMemcpy(ct.data(), d->cellType, d->g.nCells, cudaMemcpyDeviceToHost));
+   std::vector<int> keep; keep.reserve(n);
+   for (int i = 0; i < n; ++i) if (!localOnly || (ct[cell[i]] & CT_LOCAL)) keep.push_back(i);
+   const int m = (int)keep.size();
+   if (nOut) *nOut = m;
+   if (m > capacity) { comdSetError("comd_dev_download: %d atoms > caller capacity %d", m, capacity); return COMD_E_CAPACITY; }
+   if (refBox) for (int k = 0; k < m; ++k) refBox[k] = refBoxOfCell(d->g, cell[keep[k]]);
+   auto pullI = [&](const int* src, int* dst) -> int {
+      if (!dst) return COMD_OK;
+      CUDA_TRY(cudaMemcpy(tmpI.data(), src, n * sizeof(int), cudaMemcpyDeviceToHost));
+      for (int k = 0; k < m; ++k) dst[k] = tmpI[keep[k]];
+      return COMD_OK; };
+   auto pullD = [&](const double* src, double* dst) -> int {
+      if (!dst) return COMD_OK;
+      CUDA_TRY(cudaMemcpy(tmpD.data(), src, n * sizeof(double), cudaMemcpyDeviceToHost));
+      for (int k = 0; k < m; ++k) dst[k] = tmpD[keep[k]];
+      return COMD_OK; };
+   if ((rc = pullI(d->A.gid, gid))) return rc;
+   if ((rc = pullI(d->A.spec, species))) return rc;
+   for (int k = 0; k < 3; ++k)
+   {
+      if (r && (rc = pullD(d->A.r[k], r[k]))) return rc;
+      if (p && (rc = pullD(d->A.p[k], p[k]))) return rc;
+      if (f && (rc = pullD(d->f[k], f[k]))) return rc;
+   }
+   if ((rc = pullD(d->e, U))) return rc;
+   return COMD_OK;
+}
+
+extern "C" int comd_dev_download_atoms(ComdDev* d, int* nLocalOut, int capacity, int* gid, int* species, int* refBox,
+                                       double* rx, double* ry, double* rz, double* px, double* py, double* pz,
+                                       double* fx, double* fy, double* fz, double* U)
+{
+   if (!d) return COMD_E_ARG;
+   double* r[3] = { rx, ry, rz }; double* p[3] = { px, py, pz }; double* f[3] = { fx, fy, fz };
+   return downloadCommon(d, true, nLocalOut, capacity, gid, species, refBox, r, p, f, U);
+}
+
+extern "C" int comd_dev_download_all(ComdDev* d, int* nOut, int capacity, int* gid, int* refBox,
+                                     double* rx, double* ry, double* rz)
+{
+   if (!d) return COMD_E_ARG;
+   double* r[3] = { rx, ry, rz };
+   return downloadCommon(d, false, nOut, capacity, gid, nullptr, refBox, r, nullptr, nullptr, nullptr);
+}
+
+extern "C" int comd_dev_cell_counts(ComdDev* d, int* nAtomsPerRefBox, int nTotalBoxes)
+{
+   if (!d || !nAtomsPerRefBox) return COMD_E_ARG;
+   const DevGeom& g = d->g;
+   const int expect = g.n[0] * g.n[1] * g.n[2] + 2 * ((g.n[0] + 2) * (g.n[1] + g.n[2] + 2) + g.n[1] * g.n[2]);
+   if (nTotalBoxes != expect) { comdSetError("comd_dev_cell_counts: nTotalBoxes %d != %d", nTotalBoxes, expect); return COMD_E_ARG; }
+   CUDA_TRY(cudaSetDevice(d->device));
+   int rc = syncCounters(d, "comd_dev_cell_counts");
+   if (rc != COMD_OK) return rc;
+   std::vector<int> cs(g.nCells + 1);
+   CUDA_TRY(cudaMemcpy(cs.data(), d->cellStart, (g.nCells + 1) * sizeof(int), cudaMemcpyDeviceToHost));
+   for (int c = 0; c < g.nCells; ++c) nAtomsPerRefBox[refBoxOfCell(g, c)] = cs[c + 1] - cs[c];
+   return COMD_OK;
+}
+
+extern "C" int comd_dev_advance_velocity(ComdDev* d, double dt)
+{
+   if (!d) return COMD_E_ARG;
+   CUDA_TRY(cudaSetDevice(d->device));
+   k_advance_velocity<<<gridFor(d->approxAtoms, 256), 256, 0, d->stream>>>(dt, d->A.cell, d->cellType, d->A.p[0], d->A.p[1], d->A.p[2],
+      d->f[0], d->f[1], d->f[2], d->cnt); LAUNCH_CHECK(d);
+   return COMD_OK;
+}
+
+extern "C" int comd_dev_advance_position(ComdDev* d, double dt)
+{
+   if (!d) return COMD_E_ARG;
+   CUDA_TRY(cudaSetDevice(d->device));
+   k_advance_position<<<gridFor(d->approxAtoms, 256), 256, 0, d->stream>>>(dt, 1.0 / d->mass, d->A.cell, d->cellType,
+      d->A.r[0], d->A.r[1], d->A.r[2], d->A.p[0], d->A.p[1], d->A.p[2], d->cnt); LAUNCH_CHECK(d);
+   return COMD_OK;
+}
+
+extern "C" int comd_dev_energy(ComdDev* d, double eLocal[2])
+{
+   if (!d || !eLocal) return COMD_E_ARG;
+   CUDA_TRY(cudaSetDevice(d->device));
+   k_energy_partial<<<RED_BLOCKS, 256, 0, d->stream>>>(0.5 / d->mass, d->A.cell, d->cellType, d->e, d->A.p[0], d->A.p[1], d->A.p[2],
+      d->cnt, d->redPartial); LAUNCH_CHECK(d);
+   k_energy_final<<<1, 1024, 0, d->stream>>>(d->redPartial, RED_BLOCKS, d->redOut); LAUNCH_CHECK(d);
+   CUDA_TRY(cudaMemcpyAsync(d->hRed, d->redOut, 2 * sizeof(double), cudaMemcpyDeviceToHost, d->stream));
+   int rc = syncCounters(d, "comd_dev_energy");
+   eLocal[0] = d->hRed[0]; eLocal[1] = d->hRed[1];
+   return rc;
+}
+
+extern "C" int comd_dev_compute_force(ComdDev* d)
+{
+   if (!d) return COMD_E_ARG;
+   if (d->potKind == 0) { comdSetError("comd_dev_compute_force: no potential set"); return COMD_E_STATE; }
+   CUDA_TRY(cudaSetDevice(d->device));
+   if (d->useNL) { int rc = comdNeighborBuildIfNeeded(d); if (rc != COMD_OK) return rc; }
+   const int slot = d->nForceEv % 128;
+   CUDA_TRY(cudaEventRecord(d->evForce[2 * slot], d->stream));
+   int rc = d->potKind == 1 ? comdForceLJ(d) : comdForceEAM(d);
+   if (rc != COMD_OK) return rc;
+   CUDA_TRY(cudaEventRecord(d->evForce[2 * slot + 1], d->stream));
+   d->nForceEv++;
+   return COMD_OK;
+}
+
+extern "C" int comd_dev_timestep(ComdDev* d, int nSteps, double dt)
+{
+   if (!d || nSteps < 0) return COMD_E_ARG;
+   if (d->potKind == 0) { comdSetError("comd_dev_timestep: no potential set"); return COMD_E_STATE; }
+   CUDA_TRY(cudaSetDevice(d->device));
+   for (int it = 0; it < nSteps; ++it)
+   {
+      k_kick_drift<<<gridFor(d->approxAtoms, 256), 256, 0, d->stream>>>(0.5 * dt, dt, 1.0 / d->mass, d->A.cell, d->cellType,
+         d->A.r[0], d->A.r[1], d->A.r[2], d->A.p[0], d->A.p[1], d->A.p[2], d->f[0], d->f[1], d->f[2], d->cnt); LAUNCH_CHECK(d);
+      int rc = comd_dev_redistribute(d);
+      if (rc != COMD_OK) return rc;
+      rc = comd_dev_compute_force(d);
+      if (rc != COMD_OK) return rc;
+      rc = comd_dev_advance_velocity(d, 0.5 * dt);
+      if (rc != COMD_OK) return rc;
+   }
+   return COMD_OK;
+}
+
+extern "C" int comd_dev_kernel_stats(ComdDev* d, double* meanForceMs, long* nLaunches)
+{
+   if (!d) return COMD_E_ARG;
+   CUDA_TRY(cudaSetDevice(d->device));
+   if (meanForceMs)
+   {
+      // mean CUDA-event duration of the force calls since the previous query (ring of 128)
+      CUDA_TRY(cudaStreamSynchronize(d->stream));
+      const int n = d->nForceEv < 128 ? d->nForceEv : 128;
+      double sum = 0.0;
+      for (int k = 0; k < n; ++k)
+      {
+         float ms = 0.f;
+         if (cudaEventElapsedTime(&ms, d->evForce[2 * k], d->evForce[2 * k + 1]) == cudaSuccess) sum += ms;
+      }
+      cudaGetLastError();
+      if (n > 0) d->lastForceMs = sum / n;
+      d->nForceEv = 0;
+      *meanForceMs = d->lastForceMs;
+   }
+   if (nLaunches) *nLaunches = d->nLaunches;
+   return COMD_OK;
+}
+
+// CUDA-event stopwatch on the library's own stream (bench.py times its K steps with it)
+extern "C" int comd_dev_timer_start(ComdDev* d)
+{
+   if (!d) return COMD_E_ARG;
+   CUDA_TRY(cudaSetDevice(d->device));
+   CUDA_TRY(cudaStreamSynchronize(d->stream));
+   CUDA_TRY(cudaEventRecord(d->evT0, d->stream));
+   return COMD_OK;
+}
+extern "C" int comd_dev_timer_stop(ComdDev* d, double* ms)
+{
+   if (!d || !ms) return COMD_E_ARG;
+   CUDA_TRY(cudaSetDevice(d->device));
+   CUDA_TRY(cudaEventRecord(d->evT1, d->stream));
+   CUDA_TRY(cudaEventSynchronize(d->evT1));
+   float f = 0.f;
+   CUDA_TRY(cudaEventElapsedTime(&f, d->evT0, d->evT1));
+   *ms = f;
+   return COMD_OK;
+}
+
+// End-to-end step through HOST buffers: one full timestep() whose inputs (gid, r, p, f at
+// time t) start in host memory and whose results (gid, r, p, f, U at t+dt, device order)
+// end there.  bench.py times this as `e2e`; staging goes through pinned memory.
+extern "C" int comd_dev_step_host(ComdDev* d, int n, double dt,
+                                  const int* gidIn, const double* rIn[3], const double* pIn[3], const double* fIn[3],
+                                  int* nOut, int* gidOut, double* rOut[3], double* pOut[3], double* fOut[3], double* UOut,
+                                  double eLocal[2])
+{
+   if (!d || n <= 0 || !gidIn || !rIn || !pIn || !fIn) { comdSetError("comd_dev_step_host: bad argument"); return COMD_E_ARG; }
+   if (n > d->cap) { comdSetError("comd_dev_step_host: %d atoms > capacity %ld", n, d->cap); return COMD_E_CAPACITY; }
+   if (d->potKind == 0) { comdSetError("comd_dev_step_host: no potential set"); return COMD_E_STATE; }
+   CUDA_TRY(cudaSetDevice(d->device));
+   cudaStream_t s = d->stream;
+   // pinned staging: 10 doubles per atom (r,p,f + gid/U slots)
+   const long need = (long)d->cap * 11;
+   if (d->hStageDoubles < need)
+   {
+      if (d->hStage) cudaFreeHost(d->hStage);
+      CUDA_TRY(cudaMallocHost(&d->hStage, need * sizeof(double)));
+      d->hStageDoubles = need;
+   }
+   double* st = d->hStage;
+   const long cap = d->cap;
+   AtomArrays& A = d->A;
+   for (int k = 0; k < 3; ++k)
+   {
+      memcpy(st + (0 + k) * cap, rIn[k], n * sizeof(double));
+      memcpy(st + (3 + k) * cap, pIn[k], n * sizeof(double));
+      memcpy(st + (6 + k) * cap, fIn[k], n * sizeof(double));
+      CUDA_TRY(cudaMemcpyAsync(A.r[k], st + (0 + k) * cap, n * sizeof(double), cudaMemcpyHostToDevice, s));
+      CUDA_TRY(cudaMemcpyAsync(A.p[k], st + (3 + k) * cap, n * sizeof(double), cudaMemcpyHostToDevice, s));
+      CUDA_TRY(cudaMemcpyAsync(d->f[k], st + (6 + k) * cap, n * sizeof(double), cudaMemcpyHostToDevice, s));
+   }
+   memcpy(st + 9 * cap, gidIn, n * sizeof(int));
+   CUDA_TRY(cudaMemcpyAsync(A.gid, st + 9 * cap, n * sizeof(int), cudaMemcpyHostToDevice, s));
+   CUDA_TRY(cudaMemsetAsync(A.spec, 0, n * sizeof(int), s));
+   k_set_int<<<gridFor(n, 256), 256, 0, s>>>(A.cell, cellIndex(d->g, 0, 0, 0), n); LAUNCH_CHECK(d);
+   k_set_int<<<1, 1, 0, s>>>(d->cnt + C_NATOMS, n, 1); LAUNCH_CHECK(d);
+   d->approxAtoms = n;
+   int rc = comd_dev_timestep(d, 1, dt);
+   if (rc != COMD_OK) return rc;
+   rc = comd_dev_energy(d, eLocal);          // syncs, refreshes hCnt
+   if (rc != COMD_OK) return rc;
+   // results: local atoms are interleaved with ghosts in device order; bring everything
+   // back through pinned staging and compact on the host.
+   const int nAll = d->hCnt[C_NATOMS];
+   std::vector<int> cell(nAll);
+   std::vector<unsigned char> ct(d->g.nCells);
+   CUDA_TRY(cudaMemcpyAsync(st + 9 * cap, d->A.gid, nAll * sizeof(int), cudaMemcpyDeviceToHost, s));
+   for (int k = 0; k < 3; ++k)
+   {
+      CUDA_TRY(cudaMemcpyAsync(st + (0 + k) * cap, d->A.r[k], nAll * sizeof(double), cudaMemcpyDeviceToHost, s));
+      CUDA_TRY(cudaMemcpyAsync(st + (3 + k) * cap, d->A.p[k], nAll * sizeof(double), cudaMemcpyDeviceToHost, s));
+      CUDA_TRY(cudaMemcpyAsync(st + (6 + k) * cap, d->f[k], nAll * sizeof(double), cudaMemcpyDeviceToHost, s));
+   }
+   CUDA_TRY(cudaMemcpyAsync(st + 10 * cap, d->e, nAll * sizeof(double), cudaMemcpyDeviceToHost, s));
+   CUDA_TRY(cudaMemcpyAsync(cell.data(), d->A.cell, nAll * sizeof(int), cudaMemcpyDeviceToHost, s));
+   CUDA_TRY(cudaMemcpyAsync(ct.data(), d->cellType, d->g.nCells, cudaMemcpyDeviceToHost, s));
+   CUDA_TRY(cudaStreamSynchronize(s));
+   const int* gAll = reinterpret_cast<const int*>(st + 9 * cap);
+   int m = 0;
+   for (int i = 0; i < nAll; ++i)
+   {
+      if (!(ct[cell[i]] & CT_LOCAL)) continue;
+      if (m >= n + (int)(d->cap - n)) break;
+      if (gidOut) gidOut[m] = gAll[i];
+      for (int k = 0; k < 3; ++k)
+      {
+         if (rOut) rOut[k][m] = st[(0 + k) * cap + i];
+         if (pOut) pOut[k][m] = st[(3 + k) * cap + i];
+         if (fOut) fOut[k][m] = st[(6 + k) * cap + i];
+      }
+      if (UOut) UOut[m] = st[10 * cap + i];
+      ++m;
+   }
+   if (nOut) *nOut = m;
+   return COMD_OK;
+}
+
+// ---- FP64 FMA-pipe peak, measured on this very GPU (the roofline denominator for the
+// force kernels; MEASURED_PEAKS.json only carries HBM and bf16 figures).
+__global__ void __launch_bounds__(256)
+k_dfma_peak(double* out, int iters, double a, double b)
+{
+   double x0 = threadIdx.x * 1e-3, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5, x6 = x0 + 6, x7 = x0 + 7;
+   for (int i = 0; i < iters; ++i)
+   {
+      x0 = fma(x0, a, b); x1 = fma(x1, a, b); x2 = fma(x2, a, b); x3 = fma(x3, a, b);
+      x4 = fma(x4, a, b); x5 = fma(x5, a, b); x6 = fma(x6, a, b); x7 = fma(x7, a, b);
+   }
+   const double s = x0 + x1 + x2 + x3 + x4 + x5 + x6 + x7;
+   if (s == 12345.678) out[0] = s;        // never true; keeps the chain alive
+}
+
+extern "C" int comd_dev_fp64_peak(ComdDev* d, double* tflops)
+{
+   if (!d || !tflops) return COMD_E_ARG;
+   CUDA_TRY(cudaSetDevice(d->device));
+   const int blocks = 148 * 8, threads = 256, iters = 1 << 15;
+   cudaEvent_t a, b;
+   CUDA_TRY(cudaEventCreate(&a)); CUDA_TRY(cudaEventCreate(&b));
+   double best = 0.0;
+   for (int rep = 0; rep < 6; ++rep)
+   {
+      CUDA_TRY(cudaEventRecord(a, d->stream));
+      k_dfma_peak<<<blocks, threads, 0, d->stream>>>(d->redOut, iters, 0.999999, 1e-9); LAUNCH_CHECK(d);
+      CUDA_TRY(cudaEventRecord(b, d->stream));
+      CUDA_TRY(cudaEventSynchronize(b));
+      float ms = 0.f;
+      CUDA_TRY(cudaEventElapsedTime(&ms, a, b));
+      const double tf = 2.0 * 8.0 * (double)iters * blocks * threads / (ms * 1e-3) * 1e-12;
+      if (rep > 0 && tf > best) best = tf;
+   }
+   cudaEventDestroy(a); cudaEventDestroy(b);
+   *tflops = best;
+   return COMD_OK;
+}

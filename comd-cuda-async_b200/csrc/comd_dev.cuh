@@ -1,0 +1,178 @@
+// comd_dev.cuh -- internal device-side context shared by the sm_100a translation units.
+//
+// Data layout in HBM (see DESIGN.md "Data layout"):
+//   * atoms are dense structure-of-arrays, sorted by (cell, gid); no MAXATOMS padding
+//     (the reference pads every cell to MAXATOMS slots, linkCells.c:111-116).
+//   * cells live on a PADDED grid (nx+2)(ny+2)(nz+2), x fastest, halo cells included,
+//     so the three x-adjacent cells of every stencil row are ONE contiguous atom run:
+//     the 27-cell stencil is 9 contiguous runs [cellStart[c-1], cellStart[c+2]).
+//   * the reference's own box numbering (getBoxFromTuple, linkCells.c:299-346) is
+//     recovered by refBoxOfCell() whenever ids cross the C ABI.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/comd_b200.h"
+
+#define COMD_MSG_DOUBLES 7          // AtomMsg on the wire: {gid|species}, r[3], p[3] = 56 B (haloExchange.h:32-38)
+#define COMD_MAX_CELL_ATOMS 256     // sanity bound used by the in-cell rank sort
+
+// device counters (ints)
+enum {
+   C_NATOMS = 0,   // atoms in the sorted arrays (local + ghost)
+   C_NLOCAL,       // atoms in local cells
+   C_NSRC,         // size of the source pool while redistributing
+   C_NSHELL,       // entries in the shell list
+   C_SEND0,        // 6 send counts (face order x-,x+,y-,y+,z-,z+ as haloExchange.h:20-22)
+   C_RECV0 = C_SEND0 + 6,
+   C_FPSEND0 = C_RECV0 + 6,   // F' message sizes
+   C_FPRECV0 = C_FPSEND0 + 6,
+   C_FPGOT0 = C_FPRECV0 + 6,  // F' elements actually received per face
+   C_ERR = C_FPGOT0 + 6,      // sticky error bits
+   C_NLREBUILD,               // neighbour-list: rebuild required flag
+   C_NLPAIRS,                 // neighbour-list: stored entries
+   C_NLMAX,                   // neighbour-list: max per atom
+   C_COUNT = 64
+};
+// error bits
+#define ERRB_ESCAPE    1   // an atom left the halo shell in one step (moved > 1 cell)
+#define ERRB_CAPACITY  2   // atom or message capacity exceeded
+#define ERRB_CELLFULL  4   // a cell holds more than COMD_MAX_CELL_ATOMS atoms
+#define ERRB_FPMISMATCH 8  // F' halo: message length != ghost population
+#define ERRB_NLFULL    16  // neighbour list row overflow
+
+// cell type bits
+#define CT_LOCAL  1
+#define CT_SHELL  2                      // within two planes of any face (may have to travel)
+#define CT_FACE(f) (4 << (f))            // belongs to the 2-plane send set of face f
+
+struct DevGeom
+{
+   int n[3];            // local cells per axis
+   int P[3];            // padded
+   int nCells;          // padded total
+   double lMin[3], lMax[3], inv[3];
+};
+
+struct DevTable { int n; double x0, invDx; const double* v; /* entry 0; valid [-1,n+1] */ };
+
+struct AtomArrays
+{
+   double *r[3], *p[3];
+   int *gid, *spec, *cell;
+};
+
+struct ComdDev
+{
+   int device;
+   cudaStream_t stream;
+   DevGeom g;
+   ComdGeometry hostGeom;
+   double shift[6][3];          // PBC shift added when packing for face f (haloExchange.c:310-323)
+   int nbrRank[6];
+   int rank, nRanks;
+   long cap;                    // atom capacity of every per-atom array
+   AtomArrays A, B;             // current (sorted) and staging
+   double *f[3], *e;            // forces, per-atom potential energy (eV)
+   int *cellStart;              // nCells+1
+   int *cellCount, *cellFill;   // nCells
+   unsigned char* cellType;     // nCells
+   int *cellKey;                // new cell per source atom (cap)
+   int *shell;                  // shell list (cap)
+   int *tmpSrc, *tmpGid, *tmpCell;  // scatter staging (cap)
+   int *scanBlock;              // block sums for the scan
+   int *cnt;                    // C_COUNT device counters
+   int *hCnt;                   // pinned mirror
+   int approxAtoms;             // host-side estimate for grid sizing only
+   // messages
+   long msgCap;                 // atoms per face message
+   double *sendBuf[2], *recvBuf[2];
+   double *fpSend[2], *fpRecv[2];
+   int *runOff;                 // F' run offsets scratch
+   // potential
+   int potKind;                 // 0 none, 1 LJ, 2 EAM
+   double mass;
+   double ljSigma, ljEps, cutoff;
+   DevTable tPhi, tRho, tF;
+   double *tabMem;
+   double *rhobar, *dfEmbed;
+   // neighbour list
+   int useNL; double skin;
+   int *nlList; int *nlCount; int nlStride; int nlMax; double* nlLastR[3]; int nlBuilds; int nlValid;
+   // reductions
+   double *redPartial; double *redOut; double *hRed;
+   // stats
+   cudaEvent_t evForce[2 * 128]; int nForceEv; cudaEvent_t evT0, evT1; double lastForceMs; long nLaunches;   // force-time ring (128 calls) + user timer
+   // e2e staging
+   double* hStage; long hStageDoubles;
+   // nccl
+   void* nccl; void* ncclComm;
+};
+
+// ---- geometry helpers -----------------------------------------------------------
+__host__ __device__ inline int cellIndex(const DevGeom& g, int ix, int iy, int iz)   // unpadded coords in [-1, n]
+{
+   return (ix + 1) + g.P[0] * ((iy + 1) + g.P[1] * (iz + 1));
+}
+
+// Owner cell of a position: the reference's getBoxFromCoord (linkCells.c:448-480) on the
+// padded grid.  (x - lMin) * inv is a subtract followed by a multiply, which nvcc cannot
+// contract into an FMA, so the floor() argument is bit-identical to the host's.
+__device__ inline int axisCell(double x, double lMin, double lMax, double inv, int n, int& err)
+{
+   int i = (int)floor((x - lMin) * inv);
+   if (x < lMax) { if (i == n) i = n - 1; }
+   else i = n;
+   if (i < -1) { i = -1; err = 1; }
+   if (i > n) { i = n; err = 1; }
+   return i;
+}
+
+__device__ inline int cellOfPos(const DevGeom& g, double x, double y, double z, int& err)
+{
+   int ix = axisCell(x, g.lMin[0], g.lMax[0], g.inv[0], g.n[0], err);
+   int iy = axisCell(y, g.lMin[1], g.lMax[1], g.inv[1], g.n[1], err);
+   int iz = axisCell(z, g.lMin[2], g.lMax[2], g.inv[2], g.n[2], err);
+   return cellIndex(g, ix, iy, iz);
+}
+
+// reference box id (getBoxFromTuple, linkCells.c:299-346) of a padded cell
+__host__ __device__ inline int refBoxOfTuple(const int* n, int ix, int iy, int iz)
+{
+   const int nl = n[0] * n[1] * n[2];
+   if (iz == n[2]) return nl + 2*n[2]*n[1] + 2*n[2]*(n[0]+2) + (n[0]+2)*(n[1]+2) + (n[0]+2)*(iy+1) + (ix+1);
+   if (iz == -1)   return nl + 2*n[2]*n[1] + 2*n[2]*(n[0]+2) + (n[0]+2)*(iy+1) + (ix+1);
+   if (iy == n[1]) return nl + 2*n[2]*n[1] + n[2]*(n[0]+2) + (n[0]+2)*iz + (ix+1);
+   if (iy == -1)   return nl + 2*n[2]*n[1] + iz*(n[0]+2) + (ix+1);
+   if (ix == n[0]) return nl + n[1]*n[2] + iz*n[1] + iy;
+   if (ix == -1)   return nl + iz*n[1] + iy;
+   return ix + n[0]*iy + n[0]*n[1]*iz;
+}
+__host__ __device__ inline int refBoxOfCell(const DevGeom& g, int c)
+{
+   int ix = c % g.P[0] - 1, iy = (c / g.P[0]) % g.P[1] - 1, iz = c / (g.P[0] * g.P[1]) - 1;
+   return refBoxOfTuple(g.n, ix, iy, iz);
+}
+
+// ---- error plumbing -------------------------------------------------------------
+void comdSetError(const char* fmt, ...);
+#define CUDA_TRY(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { \
+   comdSetError("%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); return COMD_E_CUDA; } } while (0)
+#define LAUNCH_CHECK(dev) do { (dev)->nLaunches++; cudaError_t e_ = cudaGetLastError(); if (e_ != cudaSuccess) { \
+   comdSetError("%s:%d: kernel launch -> %s", __FILE__, __LINE__, cudaGetErrorString(e_)); return COMD_E_CUDA; } } while (0)
+
+static inline int gridFor(long n, int block, int maxBlocks = 148 * 16)
+{
+   long b = (n + block - 1) / block;
+   if (b < 1) b = 1;
+   if (b > maxBlocks) b = maxBlocks;
+   return (int)b;
+}
+
+// implemented across the translation units
+int comdForceLJ(ComdDev* d);
+int comdForceEAM(ComdDev* d);
+int comdFprimeHalo(ComdDev* d);
+int comdNeighborBuildIfNeeded(ComdDev* d);
+int comdCheckErrors(ComdDev* d, const char* where);
+int comdExchangeAtomsPhase(ComdDev* d, int axis);       // comm.cu: moves send buffers to recv buffers (self or NCCL)
+int comdExchangeFprimePhase(ComdDev* d, int axis);

@@ -1,0 +1,270 @@
+// force_eam.cu -- three-phase EAM force (sm_100a) and the F'(rho) ghost fill.
+//
+// Replaces eamForce{1,2,3}Gpu and the EAM_Force_* kernels (gpu_kernels.cu:282-325,
+// gpu_eam_thread_atom.h:35-287, gpu_eam_cta_cell.h:37-295) plus LoadForceBuffer /
+// UnloadForceBuffer (gpu_redistribute.h:638-672); results must match the CPU
+// eamForceCpuNL (eam.c:266-419) and its table lookup interpolate (eam.c:557-579):
+//   pass 1  per pair r2 <= rc2 : r = sqrt(r2); (phi,phi') , (rho,.) ; f_i -= phi' dr/r ;
+//           U_i += phi/2 ; rhobar_i += rho
+//   pass 2  per local atom     : (F,F') = interp(F, rhobar_i) ; U_i += F ; dfEmbed_i = F'
+//   halo    F' of ghost atoms  : three axis phases, plane by plane (haloExchange.c:1712-1860)
+//   pass 3  per pair r2 <  rc2 : f_i -= (F'_i + F'_j) rho' dr/r
+#include "comd_dev.cuh"
+
+// interpolate(), eam.c:557-579, incl. its one-sided clamps
+__device__ __forceinline__ void tableLookup(const DevTable& t, double r, double& f, double& df)
+{
+   const double* __restrict__ tt = t.v;
+   if (r < t.x0) r = t.x0;
+   r = (r - t.x0) * t.invDx;
+   int ii = (int)floor(r);
+   if (ii > t.n) { ii = t.n; r = t.n / t.invDx; }
+   r = r - floor(r);
+   const double tm = __ldg(tt + ii - 1), t0 = __ldg(tt + ii), t1 = __ldg(tt + ii + 1), t2 = __ldg(tt + ii + 2);
+   const double g1 = t1 - tm;
+   const double g2 = t2 - t0;
+   f = t0 + 0.5 * r * (g1 + r * (t1 + tm - 2.0 * t0));
+   df = 0.5 * (g1 + r * (g2 - g1)) * t.invDx;
+}
+
+__global__ void __launch_bounds__(128)
+k_eam_pass1(DevGeom g, DevTable tPhi, DevTable tRho, DevTable tF, double rc2,
+            const double* __restrict__ rx, const double* __restrict__ ry, const double* __restrict__ rz,
+            const int* __restrict__ cell, const unsigned char* __restrict__ cellType,
+            const int* __restrict__ cellStart, const int* __restrict__ cnt,
+            double* __restrict__ fx, double* __restrict__ fy, double* __restrict__ fz, double* __restrict__ e,
+            double* __restrict__ rhobar, double* __restrict__ dfEmbed)
+{
+   const int n = cnt[C_NATOMS];
+   const int rowY = g.P[0], rowZ = g.P[0] * g.P[1];
+   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+   {
+      const int c = cell[i];
+      if (!(cellType[c] & CT_LOCAL)) continue;
+      const double xi = rx[i], yi = ry[i], zi = rz[i];
+      double ax = 0.0, ay = 0.0, az = 0.0, u = 0.0, rb = 0.0;
+      #pragma unroll 1
+      for (int dz = -1; dz <= 1; ++dz)
+      {
+         #pragma unroll 1
+         for (int dy = -1; dy <= 1; ++dy)
+         {
+            const int rc = c + dy * rowY + dz * rowZ;
+            const int jb = cellStart[rc - 1], je = cellStart[rc + 2];
+            for (int j = jb; j < je; ++j)
+            {
+               const double dx = xi - rx[j], dyy = yi - ry[j], dzz = zi - rz[j];
+               const double r2 = dx * dx + dyy * dyy + dzz * dzz;
+               if (r2 <= rc2 && j != i)
+               {
+                  const double r = sqrt(r2);
+                  double phi, dphi, rho, drho;
+                  tableLookup(tPhi, r, phi, dphi);
+                  tableLookup(tRho, r, rho, drho);
+                  const double s = dphi / r;
+                  ax -= s * dx; ay -= s * dyy; az -= s * dzz;
+                  u += 0.5 * phi;
+                  rb += rho;
+               }
+            }
+         }
+      }
+      double fe, dfe;
+      tableLookup(tF, rb, fe, dfe);
+      fx[i] = ax; fy[i] = ay; fz[i] = az;
+      e[i] = u + fe;
+      rhobar[i] = rb;
+      dfEmbed[i] = dfe;
+   }
+}
+
+__global__ void __launch_bounds__(128)
+k_eam_pass3(DevGeom g, DevTable tRho, double rc2,
+            const double* __restrict__ rx, const double* __restrict__ ry, const double* __restrict__ rz,
+            const int* __restrict__ cell, const unsigned char* __restrict__ cellType,
+            const int* __restrict__ cellStart, const int* __restrict__ cnt, const double* __restrict__ dfEmbed,
+            double* __restrict__ fx, double* __restrict__ fy, double* __restrict__ fz)
+{
+   const int n = cnt[C_NATOMS];
+   const int rowY = g.P[0], rowZ = g.P[0] * g.P[1];
+   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+   {
+      const int c = cell[i];
+      if (!(cellType[c] & CT_LOCAL)) continue;
+      const double xi = rx[i], yi = ry[i], zi = rz[i];
+      const double dfi = dfEmbed[i];
+      double ax = 0.0, ay = 0.0, az = 0.0;
+      #pragma unroll 1
+      for (int dz = -1; dz <= 1; ++dz)
+      {
+         #pragma unroll 1
+         for (int dy = -1; dy <= 1; ++dy)
+         {
+            const int rc = c + dy * rowY + dz * rowZ;
+            const int jb = cellStart[rc - 1], je = cellStart[rc + 2];
+            for (int j = jb; j < je; ++j)
+            {
+               const double dx = xi - rx[j], dyy = yi - ry[j], dzz = zi - rz[j];
+               const double r2 = dx * dx + dyy * dyy + dzz * dzz;
+               if (r2 < rc2 && j != i)
+               {
+                  const double r = sqrt(r2);
+                  double rho, drho;
+                  tableLookup(tRho, r, rho, drho);
+                  const double s = (dfi + dfEmbed[j]) * drho / r;
+                  ax -= s * dx; ay -= s * dyy; az -= s * dzz;
+               }
+            }
+         }
+      }
+      fx[i] += ax; fy[i] += ay; fz[i] += az;
+   }
+}
+
+// ------------------------------------------------------------------ F' halo
+// A face's message is the concatenation of "runs" of consecutive cells, in a canonical
+// order both sides derive from the grid alone; inside a run atoms are in memory order
+// (cell, then gid), which is identical on sender and receiver.
+//   x faces: ny*nz runs of one cell      (send ix = 0 | nx-1, recv ix = -1 | nx,  iy,iz local)
+//   y faces: nz runs of a whole x-row    (send iy = 0 | ny-1, recv iy = -1 | ny,  ix incl. halo, iz local)
+//   z faces: one run = a whole xy-plane  (send iz = 0 | nz-1, recv iz = -1 | nz,  ix,iy incl. halo)
+// (mkForceSendCellList / mkForceRecvCellList, haloExchange.c:1712-1801.)
+struct FpFace { int firstCell, strideA, countA, strideB, countB, cellsPerRun, nRuns; };
+
+__host__ __device__ inline FpFace fpFace(const DevGeom& g, int face, int isRecv)
+{
+   const int ax = face / 2, plus = face % 2;
+   const int PX = g.P[0], PY = g.P[1];
+   int coord;                          // unpadded coordinate of the plane along ax
+   if (!isRecv) coord = plus ? g.n[ax] - 1 : 0; else coord = plus ? g.n[ax] : -1;
+   FpFace f;
+   if (ax == 0) { f.firstCell = cellIndex(g, coord, 0, 0); f.strideA = PX; f.countA = g.n[1]; f.strideB = PX * PY; f.countB = g.n[2]; f.cellsPerRun = 1; }
+   else if (ax == 1) { f.firstCell = cellIndex(g, -1, coord, 0); f.strideA = 0; f.countA = 1; f.strideB = PX * PY; f.countB = g.n[2]; f.cellsPerRun = PX; }
+   else { f.firstCell = cellIndex(g, -1, -1, coord); f.strideA = 0; f.countA = 1; f.strideB = 0; f.countB = 1; f.cellsPerRun = PX * PY; }
+   f.nRuns = f.countA * f.countB;
+   return f;
+}
+
+// one block per (face, send|recv): run starts + exclusive offsets + total
+__global__ void __launch_bounds__(1024)
+k_fp_layout(DevGeom g, const int* __restrict__ cellStart, int* __restrict__ runTab, int runStride, int* __restrict__ cnt)
+{
+   __shared__ int warpSum[32];
+   __shared__ int carry;
+   const int face = blockIdx.x >> 1, isRecv = blockIdx.x & 1;
+   const FpFace F = fpFace(g, face, isRecv);
+   int* runStart = runTab + (long)blockIdx.x * 2 * runStride;
+   int* runOff = runStart + runStride;
+   const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+   if (t == 0) carry = 0;
+   __syncthreads();
+   for (int base = 0; base < F.nRuns; base += 1024)
+   {
+      const int k = base + t;
+      int len = 0, b = 0;
+      if (k < F.nRuns)
+      {
+         const int c0 = F.firstCell + (k % F.countA) * F.strideA + (k / F.countA) * F.strideB;
+         b = cellStart[c0]; len = cellStart[c0 + F.cellsPerRun] - b;
+      }
+      int incl = len;
+      #pragma unroll
+      for (int o = 1; o < 32; o <<= 1) { int u = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += u; }
+      if (lane == 31) warpSum[w] = incl;
+      __syncthreads();
+      if (w == 0)
+      {
+         int s = warpSum[lane], si = s;
+         #pragma unroll
+         for (int o = 1; o < 32; o <<= 1) { int u = __shfl_up_sync(0xffffffffu, si, o); if (lane >= o) si += u; }
+         warpSum[lane] = si - s;
+      }
+      __syncthreads();
+      const int excl = incl - len + warpSum[w] + carry;
+      if (k < F.nRuns) { runStart[k] = b; runOff[k] = excl; }
+      __syncthreads();
+      if (t == 1023) carry = excl + len;
+      __syncthreads();
+   }
+   if (t == 0) { runOff[F.nRuns] = carry; cnt[(isRecv ? C_FPRECV0 : C_FPSEND0) + face] = carry; }
+}
+
+// message element m -> run by binary search in runOff, then a straight copy
+__device__ __forceinline__ int fpLocate(const int* __restrict__ runOff, int nRuns, int m)
+{
+   int lo = 0, hi = nRuns;            // runOff[lo] <= m < runOff[hi]
+   while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (runOff[mid] <= m) lo = mid; else hi = mid; }
+   return lo;
+}
+
+__global__ void __launch_bounds__(256)
+k_fp_pack(DevGeom g, int axis, const int* __restrict__ runTab, int runStride, const double* __restrict__ dfEmbed,
+          double* __restrict__ bufM, double* __restrict__ bufP, long msgCap, int* __restrict__ cnt)
+{
+   const int d = blockIdx.y, face = 2 * axis + d;
+   const FpFace F = fpFace(g, face, 0);
+   const int* runStart = runTab + (long)(2 * face) * 2 * runStride;
+   const int* runOff = runStart + runStride;
+   const int total = runOff[F.nRuns];
+   if (total > msgCap) { if (threadIdx.x == 0 && blockIdx.x == 0) atomicOr(&cnt[C_ERR], ERRB_CAPACITY); return; }
+   double* out = d ? bufP : bufM;
+   for (int m = blockIdx.x * blockDim.x + threadIdx.x; m < total; m += gridDim.x * blockDim.x)
+   {
+      const int k = fpLocate(runOff, F.nRuns, m);
+      out[m] = dfEmbed[runStart[k] + (m - runOff[k])];
+   }
+}
+
+__global__ void __launch_bounds__(256)
+k_fp_unpack(DevGeom g, int axis, const int* __restrict__ runTab, int runStride, double* __restrict__ dfEmbed,
+            const double* __restrict__ bufFromM, const double* __restrict__ bufFromP,
+            const int* __restrict__ nFromM, const int* __restrict__ nFromP, int* __restrict__ cnt)
+{
+   const int d = blockIdx.y, face = 2 * axis + d;
+   const FpFace F = fpFace(g, face, 1);
+   const int* runStart = runTab + (long)(2 * face + 1) * 2 * runStride;
+   const int* runOff = runStart + runStride;
+   const int total = runOff[F.nRuns];
+   const int got = d ? *nFromP : *nFromM;
+   if (got != total) { if (threadIdx.x == 0 && blockIdx.x == 0) atomicOr(&cnt[C_ERR], ERRB_FPMISMATCH); return; }
+   const double* in = d ? bufFromP : bufFromM;
+   for (int m = blockIdx.x * blockDim.x + threadIdx.x; m < total; m += gridDim.x * blockDim.x)
+   {
+      const int k = fpLocate(runOff, F.nRuns, m);
+      dfEmbed[runStart[k] + (m - runOff[k])] = in[m];
+   }
+}
+
+int comdFprimeHalo(ComdDev* d)
+{
+   const DevGeom& g = d->g;
+   cudaStream_t s = d->stream;
+   int maxRuns = g.n[1] * g.n[2];
+   if (g.n[2] > maxRuns) maxRuns = g.n[2];
+   const int runStride = maxRuns + 2;
+   k_fp_layout<<<12, 1024, 0, s>>>(g, d->cellStart, d->runOff, runStride, d->cnt); LAUNCH_CHECK(d);
+   for (int ax = 0; ax < 3; ++ax)
+   {
+      dim3 grid(148, 2);
+      k_fp_pack<<<grid, 256, 0, s>>>(g, ax, d->runOff, runStride, d->dfEmbed, d->fpSend[0], d->fpSend[1], d->msgCap, d->cnt); LAUNCH_CHECK(d);
+      int rc = comdExchangeFprimePhase(d, ax);
+      if (rc != COMD_OK) return rc;
+      k_fp_unpack<<<grid, 256, 0, s>>>(g, ax, d->runOff, runStride, d->dfEmbed, d->fpRecv[0], d->fpRecv[1],
+                                       d->cnt + C_FPGOT0 + 2 * ax, d->cnt + C_FPGOT0 + 2 * ax + 1, d->cnt); LAUNCH_CHECK(d);
+   }
+   return COMD_OK;
+}
+
+int comdForceEAM(ComdDev* d)
+{
+   const double rc2 = d->cutoff * d->cutoff;
+   cudaStream_t s = d->stream;
+   const int grid = gridFor(d->approxAtoms, 128, 148 * 64);
+   k_eam_pass1<<<grid, 128, 0, s>>>(d->g, d->tPhi, d->tRho, d->tF, rc2, d->A.r[0], d->A.r[1], d->A.r[2], d->A.cell, d->cellType,
+      d->cellStart, d->cnt, d->f[0], d->f[1], d->f[2], d->e, d->rhobar, d->dfEmbed); LAUNCH_CHECK(d);
+   int rc = comdFprimeHalo(d);
+   if (rc != COMD_OK) return rc;
+   k_eam_pass3<<<grid, 128, 0, s>>>(d->g, d->tRho, rc2, d->A.r[0], d->A.r[1], d->A.r[2], d->A.cell, d->cellType,
+      d->cellStart, d->cnt, d->dfEmbed, d->f[0], d->f[1], d->f[2]); LAUNCH_CHECK(d);
+   return COMD_OK;
+}

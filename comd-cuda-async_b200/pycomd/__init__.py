@@ -1,0 +1,300 @@
+"""pycomd -- thin ctypes binding of the C ABI in include/comd_b200.h.
+
+This is plumbing for the tests and bench.py; the product is the shared library
+(hand-written sm_100a kernels behind a plain C interface) and the C host layer in host/.
+There is NO CPU fallback: if the CUDA library is missing or no GPU is present every
+device call raises ``ComdError``.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+PKG_DIR = os.path.dirname(_HERE)
+LIB_PATH = os.path.join(PKG_DIR, "libcomd_b200.so")
+
+_dp = C.POINTER(C.c_double)
+_ip = C.POINTER(C.c_int)
+
+COMD_OK = 0
+ERRORS = {-1: "COMD_E_CUDA", -2: "COMD_E_ARG", -3: "COMD_E_CAPACITY", -4: "COMD_E_STATE", -5: "COMD_E_COMM",
+          -6: "COMD_E_MISMATCH"}
+
+
+class ComdError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("%s (%d): %s" % (ERRORS.get(code, "COMD_E_?"), code, msg))
+        self.code = code
+
+
+class ComdGeometry(C.Structure):
+    _fields_ = [("gridSize", C.c_int * 3), ("localMin", C.c_double * 3), ("localMax", C.c_double * 3),
+                ("boxSize", C.c_double * 3), ("invBoxSize", C.c_double * 3), ("globalExtent", C.c_double * 3),
+                ("procGrid", C.c_int * 3), ("procCoord", C.c_int * 3)]
+
+
+class ComdTable(C.Structure):
+    _fields_ = [("n", C.c_int), ("x0", C.c_double), ("invDx", C.c_double), ("values", _dp)]
+
+
+# every symbol include/comd_b200.h declares (tests/test_abi.py checks the .so exports them all)
+ABI_SYMBOLS = [
+    "comd_dev_create", "comd_dev_destroy", "comd_last_error", "comd_version", "comd_dev_set_mass", "comd_dev_set_lj",
+    "comd_dev_set_eam", "comd_dev_upload_atoms", "comd_dev_download_atoms", "comd_dev_num_local", "comd_dev_num_total",
+    "comd_dev_cell_counts", "comd_dev_download_all", "comd_dev_redistribute", "comd_dev_compute_force",
+    "comd_dev_advance_velocity", "comd_dev_advance_position", "comd_dev_energy", "comd_dev_timestep",
+    "comd_dev_set_neighbor_list", "comd_dev_neighbor_stats", "comd_comm_unique_id", "comd_comm_init",
+    "comd_comm_allreduce_sum", "comd_comm_allreduce_sum_int", "comd_comm_barrier", "comd_dev_sync",
+    "comd_dev_kernel_stats", "comd_dev_step_host", "comd_dev_fp64_peak", "comd_dev_timer_start", "comd_dev_timer_stop",
+]
+
+_lib = None
+
+
+def lib():
+    """Load libcomd_b200.so (fails loudly when it has not been built)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise FileNotFoundError(LIB_PATH + " not built: run `make -C comd-cuda-async_b200` "
+                                    "(or python -c 'import __graft_entry__ as g; g.build()')")
+        L = C.CDLL(LIB_PATH)
+        L.comd_last_error.restype = C.c_char_p
+        L.comd_version.restype = C.c_char_p
+        L.comd_dev_create.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.POINTER(ComdGeometry), C.c_long]
+        L.comd_dev_destroy.argtypes = [C.c_void_p]
+        L.comd_dev_set_mass.argtypes = [C.c_void_p, C.c_double]
+        L.comd_dev_set_lj.argtypes = [C.c_void_p, C.c_double, C.c_double, C.c_double]
+        L.comd_dev_set_eam.argtypes = [C.c_void_p, C.c_double, C.POINTER(ComdTable), C.POINTER(ComdTable), C.POINTER(ComdTable)]
+        L.comd_dev_upload_atoms.argtypes = [C.c_void_p, C.c_int, _ip, _ip] + [_dp] * 6
+        L.comd_dev_download_atoms.argtypes = [C.c_void_p, _ip, C.c_int, _ip, _ip, _ip] + [_dp] * 10
+        L.comd_dev_num_local.argtypes = [C.c_void_p, _ip]
+        L.comd_dev_num_total.argtypes = [C.c_void_p, _ip]
+        L.comd_dev_cell_counts.argtypes = [C.c_void_p, _ip, C.c_int]
+        L.comd_dev_download_all.argtypes = [C.c_void_p, _ip, C.c_int, _ip, _ip, _dp, _dp, _dp]
+        L.comd_dev_redistribute.argtypes = [C.c_void_p]
+        L.comd_dev_compute_force.argtypes = [C.c_void_p]
+        L.comd_dev_advance_velocity.argtypes = [C.c_void_p, C.c_double]
+        L.comd_dev_advance_position.argtypes = [C.c_void_p, C.c_double]
+        L.comd_dev_energy.argtypes = [C.c_void_p, _dp]
+        L.comd_dev_timestep.argtypes = [C.c_void_p, C.c_int, C.c_double]
+        L.comd_dev_set_neighbor_list.argtypes = [C.c_void_p, C.c_int, C.c_double]
+        L.comd_dev_neighbor_stats.argtypes = [C.c_void_p, C.POINTER(C.c_long), _ip, _ip]
+        L.comd_comm_unique_id.argtypes = [C.c_char_p]
+        L.comd_comm_init.argtypes = [C.c_void_p, C.c_char_p, C.c_int, C.c_int]
+        L.comd_comm_allreduce_sum.argtypes = [C.c_void_p, _dp, C.c_int]
+        L.comd_comm_allreduce_sum_int.argtypes = [C.c_void_p, C.POINTER(C.c_long), C.c_int]
+        L.comd_comm_barrier.argtypes = [C.c_void_p]
+        L.comd_dev_sync.argtypes = [C.c_void_p]
+        L.comd_dev_kernel_stats.argtypes = [C.c_void_p, _dp, C.POINTER(C.c_long)]
+        L.comd_dev_fp64_peak.argtypes = [C.c_void_p, _dp]
+        L.comd_dev_timer_start.argtypes = [C.c_void_p]
+        L.comd_dev_timer_stop.argtypes = [C.c_void_p, _dp]
+        L.comd_dev_step_host.argtypes = [C.c_void_p, C.c_int, C.c_double, _ip, C.POINTER(_dp), C.POINTER(_dp), C.POINTER(_dp),
+                                         _ip, _ip, C.POINTER(_dp), C.POINTER(_dp), C.POINTER(_dp), _dp, _dp]
+        _lib = L
+    return _lib
+
+
+def _chk(rc):
+    if rc != COMD_OK:
+        raise ComdError(rc, lib().comd_last_error().decode())
+
+
+def _d(a):
+    return a.ctypes.data_as(_dp) if a is not None else None
+
+
+def _i(a):
+    return a.ctypes.data_as(_ip) if a is not None else None
+
+
+def make_geometry(global_extent, cell_cutoff, proc_grid=(1, 1, 1), proc_coord=(0, 0, 0)):
+    """Host arithmetic of initDecomposition (decomposition.c:18-50) + initLinkCells
+    (linkCells.c:122-182), in IEEE doubles exactly as the C does it."""
+    g = ComdGeometry()
+    for a in range(3):
+        gext = float(global_extent[a])
+        lext = gext / proc_grid[a]
+        g.globalExtent[a] = gext
+        g.procGrid[a] = proc_grid[a]
+        g.procCoord[a] = proc_coord[a]
+        g.localMin[a] = 0.0 + proc_coord[a] * lext
+        g.localMax[a] = 0.0 + (proc_coord[a] + 1) * lext
+        g.gridSize[a] = int(lext / cell_cutoff)
+        g.boxSize[a] = lext / float(g.gridSize[a])
+        g.invBoxSize[a] = 1.0 / g.boxSize[a]
+    return g
+
+
+def n_total_boxes(grid):
+    nx, ny, nz = grid
+    return nx * ny * nz + 2 * ((nx + 2) * (ny + nz + 2) + ny * nz)
+
+
+class Device:
+    """One rank's device context (ComdDev*)."""
+
+    def __init__(self, geom, capacity, device_id=0):
+        self.h = C.c_void_p()
+        self.geom = geom
+        self.capacity = int(capacity)
+        _chk(lib().comd_dev_create(C.byref(self.h), device_id, C.byref(geom), int(capacity)))
+        self._keep = []
+
+    def close(self):
+        if self.h:
+            lib().comd_dev_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # --- potential
+    def set_mass(self, m):
+        _chk(lib().comd_dev_set_mass(self.h, m))
+
+    def set_lj(self, sigma=2.315, epsilon=0.167, cutoff=2.5 * 2.315):
+        _chk(lib().comd_dev_set_lj(self.h, sigma, epsilon, cutoff))
+
+    def set_eam(self, cutoff, phi, rho, f):
+        """phi/rho/f: dict(n, x0, inv_dx, padded) with padded = values[-1..n+1]."""
+        tabs = []
+        for t in (phi, rho, f):
+            pad = np.ascontiguousarray(t["padded"], np.float64)
+            self._keep.append(pad)
+            ct = ComdTable(t["n"], t["x0"], t["inv_dx"], C.cast(pad.ctypes.data + 8, _dp))
+            tabs.append(ct)
+        _chk(lib().comd_dev_set_eam(self.h, cutoff, C.byref(tabs[0]), C.byref(tabs[1]), C.byref(tabs[2])))
+
+    # --- atoms
+    def upload(self, gid, r, p=None, species=None):
+        gid = np.ascontiguousarray(gid, np.int32)
+        rs = [np.ascontiguousarray(r[:, k], np.float64) for k in range(3)]
+        ps = [np.ascontiguousarray(p[:, k], np.float64) for k in range(3)] if p is not None else [None] * 3
+        sp = np.ascontiguousarray(species, np.int32) if species is not None else None
+        _chk(lib().comd_dev_upload_atoms(self.h, len(gid), _i(gid), _i(sp), _d(rs[0]), _d(rs[1]), _d(rs[2]),
+                                         _d(ps[0]), _d(ps[1]), _d(ps[2])))
+
+    def num_local(self):
+        n = C.c_int()
+        _chk(lib().comd_dev_num_local(self.h, C.byref(n)))
+        return n.value
+
+    def num_total(self):
+        n = C.c_int()
+        _chk(lib().comd_dev_num_total(self.h, C.byref(n)))
+        return n.value
+
+    def download(self):
+        cap = self.capacity
+        n = C.c_int()
+        gid = np.zeros(cap, np.int32); sp = np.zeros(cap, np.int32); box = np.zeros(cap, np.int32)
+        arr = [np.zeros(cap) for _ in range(10)]
+        _chk(lib().comd_dev_download_atoms(self.h, C.byref(n), cap, _i(gid), _i(sp), _i(box), *[_d(a) for a in arr]))
+        m = n.value
+        return dict(gid=gid[:m], species=sp[:m], box=box[:m],
+                    r=np.stack([a[:m] for a in arr[0:3]], 1), p=np.stack([a[:m] for a in arr[3:6]], 1),
+                    f=np.stack([a[:m] for a in arr[6:9]], 1), U=arr[9][:m].copy())
+
+    def download_all(self):
+        cap = self.capacity
+        n = C.c_int()
+        gid = np.zeros(cap, np.int32); box = np.zeros(cap, np.int32)
+        arr = [np.zeros(cap) for _ in range(3)]
+        _chk(lib().comd_dev_download_all(self.h, C.byref(n), cap, _i(gid), _i(box), *[_d(a) for a in arr]))
+        m = n.value
+        return dict(gid=gid[:m], box=box[:m], r=np.stack([a[:m] for a in arr], 1))
+
+    def cell_counts(self):
+        g = self.geom.gridSize
+        nt = n_total_boxes((g[0], g[1], g[2]))
+        out = np.zeros(nt, np.int32)
+        _chk(lib().comd_dev_cell_counts(self.h, _i(out), nt))
+        return out
+
+    # --- the path
+    def redistribute(self):
+        _chk(lib().comd_dev_redistribute(self.h))
+
+    def compute_force(self):
+        _chk(lib().comd_dev_compute_force(self.h))
+
+    def advance_velocity(self, dt):
+        _chk(lib().comd_dev_advance_velocity(self.h, dt))
+
+    def advance_position(self, dt):
+        _chk(lib().comd_dev_advance_position(self.h, dt))
+
+    def energy(self):
+        e = np.zeros(2)
+        _chk(lib().comd_dev_energy(self.h, _d(e)))
+        return float(e[0]), float(e[1])
+
+    def timestep(self, n, dt):
+        _chk(lib().comd_dev_timestep(self.h, n, dt))
+
+    def sync(self):
+        _chk(lib().comd_dev_sync(self.h))
+
+    def set_neighbor_list(self, use, skin):
+        _chk(lib().comd_dev_set_neighbor_list(self.h, 1 if use else 0, skin))
+
+    def neighbor_stats(self):
+        a = C.c_long(); b = C.c_int(); c = C.c_int()
+        _chk(lib().comd_dev_neighbor_stats(self.h, C.byref(a), C.byref(b), C.byref(c)))
+        return dict(pairs=a.value, max_per_atom=b.value, builds=c.value)
+
+    def kernel_stats(self):
+        ms = C.c_double(); n = C.c_long()
+        _chk(lib().comd_dev_kernel_stats(self.h, C.byref(ms), C.byref(n)))
+        return dict(last_force_ms=ms.value, launches=n.value)
+
+    def timer_start(self):
+        _chk(lib().comd_dev_timer_start(self.h))
+
+    def timer_stop(self):
+        t = C.c_double()
+        _chk(lib().comd_dev_timer_stop(self.h, C.byref(t)))
+        return t.value
+
+    def fp64_peak(self):
+        t = C.c_double()
+        _chk(lib().comd_dev_fp64_peak(self.h, C.byref(t)))
+        return t.value
+
+    def step_host(self, dt, gid, r, p, f):
+        """One timestep through host buffers.  r,p,f: lists of three contiguous float64 arrays."""
+        n = len(gid)
+        cap = self.capacity
+        P3 = _dp * 3
+        rin = P3(*[_d(a) for a in r]); pin = P3(*[_d(a) for a in p]); fin = P3(*[_d(a) for a in f])
+        if not hasattr(self, "_out"):
+            self._out = dict(gid=np.zeros(cap, np.int32), r=[np.zeros(cap) for _ in range(3)],
+                             p=[np.zeros(cap) for _ in range(3)], f=[np.zeros(cap) for _ in range(3)], U=np.zeros(cap))
+        o = self._out
+        rout = P3(*[_d(a) for a in o["r"]]); pout = P3(*[_d(a) for a in o["p"]]); fout = P3(*[_d(a) for a in o["f"]])
+        e = np.zeros(2)
+        m = C.c_int()
+        _chk(lib().comd_dev_step_host(self.h, n, dt, _i(gid), rin, pin, fin, C.byref(m), _i(o["gid"]), rout, pout, fout,
+                                      _d(o["U"]), _d(e)))
+        return m.value, o, (float(e[0]), float(e[1]))
+
+    # --- multi-GPU
+    @staticmethod
+    def comm_unique_id():
+        buf = C.create_string_buffer(128)
+        _chk(lib().comd_comm_unique_id(buf))
+        return buf.raw
+
+    def comm_init(self, uid, rank, nranks):
+        _chk(lib().comd_comm_init(self.h, uid, rank, nranks))
+
+    def allreduce_sum(self, vals):
+        a = np.ascontiguousarray(vals, np.float64).copy()
+        _chk(lib().comd_comm_allreduce_sum(self.h, _d(a), len(a)))
+        return a

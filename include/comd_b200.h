@@ -1,0 +1,166 @@
+/* comd_b200.h -- C ABI of the B200-native device layer for CoMD's short-range force path.
+ *
+ * This is the drop-in boundary: the set of entry points the reference's host C
+ * (timestep.c, ljForce.c, eam.c, haloExchange.c, CoMD.c) reaches its GPU through.
+ * The reference declares them in src-mpi/gpu_kernels.h:13-92 and gpu_utility.h:55-69
+ * and passes a ~600-byte SimGpu struct of raw device pointers BY VALUE
+ * (gpu_types.h:159-190).  Here every call takes one opaque per-rank handle instead;
+ * each declaration below names the reference interface it replaces.
+ * INTEGRATION.md shows the one-line rebinding of each reference call site.
+ *
+ * Conventions
+ *   - plain C linkage, plain pointers and sizes; no C++/torch types.
+ *   - every function returns 0 on success, a negative COMD_E_* code on failure;
+ *     comd_last_error() returns a human-readable message for the calling thread.
+ *     (The reference prints and exit(-1)s on any CUDA error, gpu_utility.h:71-84;
+ *     a library must not, so the error is returned and the host decides.)
+ *   - one host thread per rank, one rank per GPU (CoMD.c:105-117).
+ *   - all work is enqueued on the handle's own stream; calls that return values to
+ *     the host synchronise that stream, the others do not.
+ *   - atom data are structure-of-arrays, FP64 (COMD_DOUBLE; -DCOMD_SINGLE builds
+ *     switch comd_real to float like mytype.h:8-20).
+ *   - there is no CPU fallback: without a CUDA device every call fails with
+ *     COMD_E_CUDA.
+ */
+#ifndef COMD_B200_H
+#define COMD_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#ifdef COMD_SINGLE
+typedef float comd_real;
+#else
+typedef double comd_real;
+#endif
+
+#define COMD_OK            0
+#define COMD_E_CUDA       -1   /* a CUDA runtime call failed (or no device)          */
+#define COMD_E_ARG        -2   /* bad argument                                       */
+#define COMD_E_CAPACITY   -3   /* atom / message capacity exceeded                   */
+#define COMD_E_STATE      -4   /* call order violated (e.g. force before potential)  */
+#define COMD_E_COMM       -5   /* NCCL failure                                       */
+#define COMD_E_MISMATCH   -6   /* F' halo: ghost-cell population differs from sender */
+
+typedef struct ComdDev ComdDev;      /* opaque; replaces SimGpu (gpu_types.h:159-190) */
+
+/* Local link-cell geometry + domain decomposition of one rank.
+ * Filled by the host exactly as initLinkCells (linkCells.c:122-182) and
+ * initDecomposition (decomposition.c:18-50) do; the device never re-derives
+ * boxSize/invBoxSize so the ownership arithmetic stays bit-identical. */
+typedef struct ComdGeometry
+{
+   int    gridSize[3];       /* local cells per axis (LinkCell.gridSize)           */
+   double localMin[3];       /* LinkCell.localMin                                   */
+   double localMax[3];       /* LinkCell.localMax                                   */
+   double boxSize[3];        /* LinkCell.boxSize                                    */
+   double invBoxSize[3];     /* LinkCell.invBoxSize                                 */
+   double globalExtent[3];   /* Domain.globalExtent                                 */
+   int    procGrid[3];       /* Domain.procGrid                                     */
+   int    procCoord[3];      /* Domain.procCoord                                    */
+} ComdGeometry;
+
+/* Uniform-grid table as the reference stores it (InterpolationObject,
+ * CoMDTypes.h:169-176): values points at entry 0 of an array valid on [-1, n+1]
+ * (padding of initInterpolationObject, eam.c:496-519). */
+typedef struct ComdTable
+{
+   int           n;
+   double        x0;
+   double        invDx;
+   const double* values;
+} ComdTable;
+
+/* ---- lifecycle: SetupGpu / AllocateGpu / DestroyGpu (gpu_utility.h:55-62) -------- */
+int  comd_dev_create(ComdDev** out, int deviceId, const ComdGeometry* geom, long atomCapacity);
+int  comd_dev_destroy(ComdDev* dev);
+const char* comd_last_error(void);
+const char* comd_version(void);
+
+/* ---- potential + species: the potential block of CopyDataToGpu (gpu_utility.c:432-600) */
+int  comd_dev_set_mass(ComdDev* dev, double massInternalUnits);
+int  comd_dev_set_lj(ComdDev* dev, double sigma, double epsilon, double cutoff);              /* LjPotentialGpu */
+int  comd_dev_set_eam(ComdDev* dev, double cutoff,
+                      const ComdTable* phi, const ComdTable* rho, const ComdTable* f);         /* EamPotentialGpu */
+
+/* ---- atoms in / out: CopyDataToGpu (gpu_utility.c:432), GetLocalAtomsFromGpu (:602) --
+ * Upload takes the rank's local atoms in any order (host pointers, SoA).  It bins
+ * them, builds the ghost shell and sorts (i.e. it ends with comd_dev_redistribute).
+ * Download returns LOCAL atoms in device order (cell-major in the reference's own box
+ * numbering is NOT implied; key by gid).  Any output pointer may be NULL. */
+int  comd_dev_upload_atoms(ComdDev* dev, int nLocal, const int* gid, const int* species,
+                           const double* rx, const double* ry, const double* rz,
+                           const double* px, const double* py, const double* pz);
+int  comd_dev_download_atoms(ComdDev* dev, int* nLocalOut, int capacity,
+                             int* gid, int* species, int* refBox,
+                             double* rx, double* ry, double* rz,
+                             double* px, double* py, double* pz,
+                             double* fx, double* fy, double* fz, double* U);
+int  comd_dev_num_local(ComdDev* dev, int* nLocal);        /* sumAtoms input (CoMD.c:442-457) */
+int  comd_dev_num_total(ComdDev* dev, int* nLocalPlusGhost);
+/* per-cell populations in the REFERENCE's box numbering (getBoxFromTuple,
+ * linkCells.c:299-346), nTotalBoxes entries: what CoMD.c:445 meant to copy back. */
+int  comd_dev_cell_counts(ComdDev* dev, int* nAtomsPerRefBox, int nTotalBoxes);
+/* all atoms incl. ghosts, for the halo parity tests */
+int  comd_dev_download_all(ComdDev* dev, int* nOut, int capacity, int* gid, int* refBox,
+                           double* rx, double* ry, double* rz);
+
+/* ---- binning + atom halo: updateLinkCellsGpu (gpu_kernels.cu:470), haloExchange of
+ * atoms (haloExchange.c:732; pack/unpack gpu_kernels.cu:507-638), buildAtomListGpu
+ * (:554), sortAtomsGpu (:1014): one call = redistributeAtoms (timestep.c:212-276). */
+int  comd_dev_redistribute(ComdDev* dev);
+
+/* ---- forces: ljForceGpu (gpu_kernels.cu:70), eamForce{1,2,3}Gpu (:282-325) with the
+ * F'(rho) halo exchange between pass 2 and 3 (eam.c:241). = pot->force(sim). */
+int  comd_dev_compute_force(ComdDev* dev);
+
+/* ---- integrator: advanceVelocityGpu / advancePositionGpu (gpu_kernels.cu:327-349) */
+int  comd_dev_advance_velocity(ComdDev* dev, double dt);
+int  comd_dev_advance_position(ComdDev* dev, double dt);
+/* computeEnergy (gpu_kernels.cu:1046): eLocal[0] = potential, eLocal[1] = kinetic (rank-local sums) */
+int  comd_dev_energy(ComdDev* dev, double eLocal[2]);
+/* nSteps of timestep() (timestep.c:48-100) without returning to the host in between:
+ * kick, drift, redistribute, force, kick.  Leaves r, p, f at t + nSteps*dt. */
+int  comd_dev_timestep(ComdDev* dev, int nSteps, double dt);
+
+/* ---- neighbour list (optional path): buildNeighborListGpu (gpu_kernels.cu:1981),
+ * neighborListUpdateRequiredGpu (:1461).  skin = relativeSkin * cutoff (CoMD.c:257-264).
+ * useNeighborList != 0 switches force + redistribute to the list variants. */
+int  comd_dev_set_neighbor_list(ComdDev* dev, int useNeighborList, double skinDistance);
+int  comd_dev_neighbor_stats(ComdDev* dev, long* nPairsStored, int* maxPerAtom, int* nBuilds);
+
+/* ---- multi-GPU: replaces the MPI wrappers of parallel.h:17-63 for the halo path and
+ * the libmp layer of comm.h:40-74.  The 128-byte id is made on rank 0 and handed to
+ * the other ranks by whatever launcher is in use (torchrun store, a file, a pipe). */
+#define COMD_COMM_ID_BYTES 128
+int  comd_comm_unique_id(unsigned char id[COMD_COMM_ID_BYTES]);
+int  comd_comm_init(ComdDev* dev, const unsigned char id[COMD_COMM_ID_BYTES], int rank, int nRanks);
+int  comd_comm_allreduce_sum(ComdDev* dev, double* inout, int n);   /* addRealParallel, parallel.c:130 */
+int  comd_comm_allreduce_sum_int(ComdDev* dev, long* inout, int n); /* addIntParallel,  parallel.c:120 */
+int  comd_comm_barrier(ComdDev* dev);                               /* barrierParallel, parallel.c:93  */
+
+/* ---- measurement hooks (bench.py / tests) ---------------------------------------- */
+int  comd_dev_sync(ComdDev* dev);
+/* Mean CUDA-event duration (ms) of the force calls (comd_dev_compute_force, also inside
+ * comd_dev_timestep) since the previous query, and the kernels launched since creation. */
+int  comd_dev_kernel_stats(ComdDev* dev, double* meanForceMs, long* nLaunches);
+/* CUDA-event stopwatch on the handle's stream: start syncs then records, stop records and syncs. */
+int  comd_dev_timer_start(ComdDev* dev);
+int  comd_dev_timer_stop(ComdDev* dev, double* ms);
+/* FP64 FMA-pipe peak of this GPU (DFMA microbenchmark, TFLOP/s): the roofline denominator
+ * for the force kernels; the driver's MEASURED_PEAKS.json has no FP64 entry. */
+int  comd_dev_fp64_peak(ComdDev* dev, double* tflops);
+/* End-to-end step through HOST buffers (bench.py `e2e`): one full timestep() whose inputs
+ * (gid, r, p, f at time t; SoA, any order, all local to this rank) start in host memory and
+ * whose results (gid, r, p, f, U at t+dt, in device order, *nOut of them) end there.
+ * H2D/D2H go through pinned staging inside the call. */
+int  comd_dev_step_host(ComdDev* dev, int nLocal, double dt,
+                        const int* gidIn, const double* rIn[3], const double* pIn[3], const double* fIn[3],
+                        int* nOut, int* gidOut, double* rOut[3], double* pOut[3], double* fOut[3], double* UOut,
+                        double eLocal[2]);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* COMD_B200_H */

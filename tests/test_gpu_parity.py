@@ -1,0 +1,265 @@
+"""GPU: the CUDA path (through the C ABI) against the CPU oracle on the same seeded inputs.
+
+Gates (BASELINE.json north_star / BASELINE.md section 4):
+  * cell assignment, per-cell counts, ghost sets, atom conservation ......... bit-exact, keyed by gid
+  * step-0 per-atom forces and energies (displaced lattice) .................. <= 1e-12 relative (max-norm)
+  * total energy after 100 steps ............................................. <= 1e-6 relative
+"""
+import os
+
+import numpy as np
+import pytest
+
+import pyoracle as po
+import pycomd
+from common import GOLDEN_DIR, LJ_EPS, by_gid, device_for, oracle_sim, rel_err
+
+pytestmark = pytest.mark.gpu
+
+KINDS = {"lj": po.POT_LJ, "funcfl": po.POT_FUNCFL, "setfl": po.POT_SETFL}
+FORCE_TOL = 1e-12      # north_star: step-0 per-atom forces and energies, FP64
+ENERGY100_TOL = 1e-6   # north_star: total energy at step 100
+
+
+def u_scale(kind):
+    # the CPU path keeps per-atom LJ energies in units of 4*epsilon (ljForce.c:256-261); the device stores eV
+    return 4.0 * LJ_EPS if kind == "lj" else 1.0
+
+
+@pytest.mark.parametrize("kind", list(KINDS))
+@pytest.mark.parametrize("n", [6, 10])
+def test_step0_forces_and_energies(kind, n):
+    orc = oracle_sim(KINDS[kind], n, delta=0.1, temperature=600.0)
+    a = orc.atoms()
+    dev, _ = device_for(orc, (n, n, n))
+    dev.upload(a["gid"], a["r"], a["p"])
+    dev.compute_force()
+    d = by_gid(dev.download())
+    o = by_gid(a)
+    assert np.array_equal(d["gid"], o["gid"])
+    assert np.array_equal(d["r"], o["r"])            # positions untouched by upload + redistribute
+    assert rel_err(d["f"], o["f"]) <= FORCE_TOL
+    assert rel_err(d["U"], o["U"] * u_scale(kind)) <= FORCE_TOL
+    ep_d, ek_d = dev.energy()
+    ep_o, ek_o = orc.energies()
+    assert abs(ep_d - ep_o) <= FORCE_TOL * abs(ep_o)
+    assert abs(ek_d - ek_o) <= FORCE_TOL * abs(ek_o)
+    dev.close()
+
+
+@pytest.mark.parametrize("kind", list(KINDS))
+def test_step0_forces_against_reference_golden(kind):
+    """Same gate against vectors the reference itself produced (tests/golden/make_golden.py)."""
+    g = np.load(os.path.join(GOLDEN_DIR, "forces_%s_n6.npz" % kind))
+    orc = po.Oracle(pot=KINDS[kind], nx=6, ny=6, nz=6, initial_force=False)   # only for tables / cutoff
+    dev, _ = device_for(orc, (6, 6, 6))
+    dev.upload(g["gid"], g["r"], g["p"])
+    dev.compute_force()
+    d = by_gid(dev.download())
+    o = by_gid({k: g[k] for k in ("gid", "r", "p", "f", "U")})
+    assert rel_err(d["f"], o["f"]) <= FORCE_TOL
+    assert rel_err(d["U"], o["U"] * u_scale(kind)) <= FORCE_TOL
+    ep, ek = dev.energy()
+    assert abs(ep - float(g["ePot"])) <= FORCE_TOL * abs(float(g["ePot"]))
+    assert abs(ek - float(g["eKin"])) <= FORCE_TOL * abs(float(g["eKin"]))
+    dev.close()
+
+
+@pytest.mark.parametrize("kind", list(KINDS))
+def test_known_answer_cohesive_energy(kind):
+    """Perfect lattice, step 0 (CoMD.c:896-900)."""
+    known = {"lj": -1.243619295058, "funcfl": -3.538079224691, "setfl": -3.539999969176}[kind]
+    n = 10
+    orc = oracle_sim(KINDS[kind], n)
+    a = orc.atoms()
+    dev, _ = device_for(orc, (n, n, n))
+    dev.upload(a["gid"], a["r"], a["p"])
+    dev.compute_force()
+    ep, ek = dev.energy()
+    assert abs(ep / len(a["gid"]) - known) < 5e-11
+    assert abs(ek / len(a["gid"]) / (8.6173324e-5 * 1.5) - 600.0) < 1e-9
+    dev.close()
+
+
+@pytest.mark.parametrize("kind", list(KINDS))
+def test_cells_counts_and_ghosts_bit_exact(kind):
+    """Binning + halo against the oracle on identical positions: owner cell of every local and
+    ghost atom (reference box numbering), per-cell counts, ghost gid multisets per halo cell."""
+    n = 8
+    # skin 0 makes the oracle size its link cells on the bare cutoff, like the device
+    orc = oracle_sim(KINDS[kind], n, delta=0.3, temperature=600.0, skin=0.0)
+    a = orc.atoms()
+    dev, geom = device_for(orc, (n, n, n))
+    dev.upload(a["gid"], a["r"], a["p"])
+    og = orc.geometry()
+    assert list(geom.gridSize) == list(og["grid"])
+    assert np.array_equal(np.array(geom.invBoxSize[:]), og["inv_box_size"])
+    d = by_gid(dev.download())
+    o = by_gid(a)
+    assert np.array_equal(d["gid"], o["gid"])
+    assert np.array_equal(d["box"], o["box"])
+    # every atom incl. ghosts: (box, gid) multiset and positions
+    da, oa = dev.download_all(), orc.all_atoms()
+    kd = np.lexsort((da["gid"], da["box"])); ko = np.lexsort((oa["gid"], oa["box"]))
+    assert len(kd) == len(ko)
+    assert np.array_equal(da["box"][kd], oa["box"][ko])
+    assert np.array_equal(da["gid"][kd], oa["gid"][ko])
+    assert np.array_equal(da["r"][kd], oa["r"][ko])        # PBC shift applied identically
+    counts = dev.cell_counts()
+    assert np.array_equal(counts, np.bincount(oa["box"], minlength=og["n_total_boxes"]))
+    # independent statement of the same rule
+    cells = po.OracleCells([n * orc.potential()["lat"]] * 3, orc.potential()["cutoff"])
+    bx, _ = cells.bin(da["r"])
+    assert np.array_equal(bx, da["box"])
+    dev.close()
+
+
+@pytest.mark.parametrize("kind", list(KINDS))
+def test_atoms_sorted_by_cell_then_gid(kind):
+    n = 6
+    orc = oracle_sim(KINDS[kind], n, delta=0.2)
+    a = orc.atoms()
+    dev, _ = device_for(orc, (n, n, n))
+    rng = np.random.default_rng(3)
+    perm = rng.permutation(len(a["gid"]))               # upload order must not matter
+    dev.upload(a["gid"][perm], a["r"][perm], a["p"][perm])
+    dev.compute_force()
+    d1 = dev.download()
+    dev.upload(a["gid"], a["r"], a["p"])
+    dev.compute_force()
+    d2 = dev.download()
+    for k in ("gid", "box", "r", "p", "f", "U"):
+        assert np.array_equal(d1[k], d2[k]), k          # bit-reproducible, order independent
+    dev.close()
+
+
+@pytest.mark.parametrize("kind", list(KINDS))
+def test_migration_and_conservation(kind):
+    """Hot, fast atoms cross cell and periodic boundaries: nobody is lost or duplicated and the
+    owner cell always equals the reference rule evaluated on the device's own positions."""
+    n = 6
+    orc = oracle_sim(KINDS[kind], n, delta=0.05, temperature=4000.0)
+    a = orc.atoms()
+    dev, _ = device_for(orc, (n, n, n))
+    dev.upload(a["gid"], a["r"], a["p"])
+    dev.compute_force()
+    cells = po.OracleCells([n * orc.potential()["lat"]] * 3, orc.potential()["cutoff"])
+    moved = 0
+    box0 = by_gid(dev.download())["box"]
+    for _ in range(6):
+        dev.timestep(25, 2.0)
+        da = dev.download_all()
+        bx, _ = cells.bin(da["r"])
+        assert np.array_equal(bx, da["box"])
+        d = by_gid(dev.download())
+        assert np.array_equal(d["gid"], np.sort(a["gid"]))          # all there, exactly once
+        assert dev.num_local() == len(a["gid"])
+        L = n * orc.potential()["lat"]
+        assert d["r"].min() >= 0.0 and d["r"].max() < L              # locals live inside the box
+        moved = max(moved, int(np.sum(d["box"] != box0)))
+    assert moved > 50                                                # the test did exercise migration
+    dev.close()
+
+
+@pytest.mark.parametrize("kind", list(KINDS))
+def test_timestep_matches_oracle_one_step(kind):
+    n = 6
+    orc = oracle_sim(KINDS[kind], n, delta=0.05, temperature=600.0)
+    a = orc.atoms()
+    dev, _ = device_for(orc, (n, n, n))
+    dev.upload(a["gid"], a["r"], a["p"])
+    dev.compute_force()
+    dev.timestep(1, 1.0)
+    orc.timestep(1)
+    d = by_gid(dev.download()); o = by_gid(orc.atoms())
+    assert rel_err(d["r"], o["r"]) <= 1e-15
+    assert rel_err(d["p"], o["p"]) <= FORCE_TOL
+    assert rel_err(d["f"], o["f"]) <= 1e-11
+    dev.close()
+
+
+@pytest.mark.parametrize("kind,n", [("lj", 20), ("funcfl", 20), ("setfl", 12)])
+def test_energy_after_100_steps(kind, n):
+    """BASELINE configs C1/C2 (20^3, 32 000 atoms, 100 steps, dt 1 fs) + a setfl case."""
+    orc = oracle_sim(KINDS[kind], n)
+    a = orc.atoms()
+    dev, _ = device_for(orc, (n, n, n))
+    dev.upload(a["gid"], a["r"], a["p"])
+    dev.compute_force()
+    e0 = sum(dev.energy())
+    for _ in range(10):
+        dev.timestep(10, 1.0)
+    ep, ek = dev.energy()
+    if n == 20:
+        g = np.load(os.path.join(GOLDEN_DIR, "trace_%s_n20.npz" % kind))["trace"]   # reference's own trace
+        ref0, ref100 = g[0].sum(), g[-1].sum()
+        assert abs(g[-1][0] - ep) <= ENERGY100_TOL * abs(g[-1][0])
+    else:
+        ref0 = sum(orc.energies())
+        orc.timestep(100)
+        ref100 = sum(orc.energies())
+    assert abs(e0 - ref0) <= 1e-12 * abs(ref0)
+    assert abs((ep + ek) - ref100) <= ENERGY100_TOL * abs(ref100)
+    assert dev.num_local() == len(a["gid"])
+    dev.close()
+
+
+def test_split_calls_equal_fused_timestep():
+    """advanceVelocity / advancePosition / redistributeAtoms / computeForce called one by one (the
+    reference's timestep.c:48-100 sequence) give bit-identical state to comd_dev_timestep."""
+    n = 6
+    orc = oracle_sim(po.POT_FUNCFL, n, delta=0.05)
+    a = orc.atoms()
+    out = []
+    for fused in (True, False):
+        dev, _ = device_for(orc, (n, n, n))
+        dev.upload(a["gid"], a["r"], a["p"])
+        dev.compute_force()
+        if fused:
+            dev.timestep(3, 1.0)
+        else:
+            for _ in range(3):
+                dev.advance_velocity(0.5); dev.advance_position(1.0); dev.redistribute()
+                dev.compute_force(); dev.advance_velocity(0.5)
+        out.append(by_gid(dev.download()))
+        dev.close()
+    for k in ("r", "p", "f", "U"):
+        assert np.array_equal(out[0][k], out[1][k]), k
+
+
+def test_step_host_round_trip():
+    n = 6
+    orc = oracle_sim(po.POT_LJ, n, delta=0.05)
+    a = orc.atoms()
+    dev, _ = device_for(orc, (n, n, n))
+    dev.upload(a["gid"], a["r"], a["p"])
+    dev.compute_force()
+    d0 = dev.download()
+    cols = lambda x: [np.ascontiguousarray(x[:, k]) for k in range(3)]
+    m, o, e = dev.step_host(1.0, np.ascontiguousarray(d0["gid"]), cols(d0["r"]), cols(d0["p"]), cols(d0["f"]))
+    assert m == len(a["gid"])
+    dev2, _ = device_for(orc, (n, n, n))
+    dev2.upload(a["gid"], a["r"], a["p"]); dev2.compute_force(); dev2.timestep(1, 1.0)
+    d1 = by_gid(dev2.download())
+    got = by_gid(dict(gid=o["gid"][:m], r=np.stack([x[:m] for x in o["r"]], 1), p=np.stack([x[:m] for x in o["p"]], 1),
+                      f=np.stack([x[:m] for x in o["f"]], 1), U=o["U"][:m]))
+    for k in ("r", "p", "f", "U"):
+        assert np.array_equal(got[k], d1[k]), k
+    assert e == dev2.energy()
+    dev.close(); dev2.close()
+
+
+def test_errors_are_returned_not_fatal():
+    orc = oracle_sim(po.POT_LJ, 6)
+    dev, _ = device_for(orc, (6, 6, 6))
+    a = orc.atoms()
+    with pytest.raises(pycomd.ComdError):
+        big = np.zeros((dev.capacity + 1, 3))
+        dev.upload(np.arange(dev.capacity + 1, dtype=np.int32), big)
+    geom = pycomd.make_geometry([6 * 3.615] * 3, 2.5 * 2.315)
+    d2 = pycomd.Device(geom, 4096)
+    with pytest.raises(pycomd.ComdError):
+        d2.compute_force()                       # no potential set
+    with pytest.raises(pycomd.ComdError):
+        d2.set_lj(cutoff=50.0)                   # cells smaller than the cutoff
+    d2.close(); dev.close()
