@@ -111,7 +111,7 @@ def cpu_reference_rate(pot, seconds_hint=15.0):
     if os.path.exists(exe):
         t0 = time.time()
         out = subprocess.run([exe, "-m", "cpu_nl", "-d", potdir, "-x", str(n), "-y", str(n), "-z", str(n), "-N", str(steps),
-                              "-n", str(steps)] + flags, cwd=os.path.join(ROOT, "oracle", "_ref"), capture_output=True, text=True).stdout
+                              "-n", str(steps)] + flags, cwd=os.path.join(ROOT, "oracle", "_ref"), capture_output=True).stdout.decode("utf-8", "replace")
         m = re.search(r"Average atom rate:\s+([0-9.eE+-]+) atoms/us", out)
         if m:
             return dict(value=float(m.group(1)) * 1e6, unit="atom-steps/s", cores=1, kind="reference", sample=sample,
@@ -194,7 +194,7 @@ def main():
     ghost_frac = 1.0
     for a in range(3):
         ghost_frac *= (geom.gridSize[a] + 2.0) / geom.gridSize[a]
-    cap = int(n_local * ghost_frac * 1.10) + 65536
+    cap = int(n_local * (2.0 * ghost_frac - 1.0) * 1.10) + 65536     # old ghosts + new ghosts coexist in the pool while redistributing
     dev = pycomd.Device(geom, cap, device_id=local_rank)
     dev.set_mass(potential["mass"])
     if pot == "lj":

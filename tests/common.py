@@ -30,7 +30,7 @@ def device_for(orc, nxyz, capacity_factor=3.0, proc_grid=(1, 1, 1), proc_coord=(
     gext = [nxyz[0] * lat, nxyz[1] * lat, nxyz[2] * lat]
     geom = pycomd.make_geometry(gext, pot["cutoff"], proc_grid, proc_coord)
     n_atoms = 4 * nxyz[0] * nxyz[1] * nxyz[2]
-    dev = pycomd.Device(geom, int(n_atoms * capacity_factor) + 4096)
+    dev = pycomd.Device(geom, int(n_atoms * capacity_factor) + 16384)
     dev.set_mass(pot["mass"])
     if orc.pot == po.POT_LJ:
         dev.set_lj(LJ_SIGMA, LJ_EPS, pot["cutoff"])
