@@ -257,7 +257,7 @@ k_scatter(const int* __restrict__ cellKey, const int* __restrict__ gid, const in
 // independent of atomics and identical on sender and receiver (what sortAtomsGpu /
 // sortAtomsInCell aim for, gpu_kernels.cu:1014, haloExchange.c:1926-1981).
 __global__ void __launch_bounds__(256)
-k_rank_gather(const int* __restrict__ tmpSrc, const int* __restrict__ tmpGid, const int* __restrict__ tmpCell,
+k_rank_gather(DevGeom geo, const int* __restrict__ tmpSrc, const int* __restrict__ tmpGid, const int* __restrict__ tmpCell,
               const int* __restrict__ cellStart, const unsigned char* __restrict__ cellType,
               AtomArrays src, AtomArrays dst, int* __restrict__ cnt)
 {
@@ -275,7 +275,9 @@ k_rank_gather(const int* __restrict__ tmpSrc, const int* __restrict__ tmpGid, co
          int rank = 0;
          for (int u = b; u < e; ++u) { const int gu = tmpGid[u]; rank += (gu < g) || (gu == g && u < t); }
          const int d = b + rank, s = tmpSrc[t];
-         dst.r[0][d] = src.r[0][s]; dst.r[1][d] = src.r[1][s]; dst.r[2][d] = src.r[2][s];
+         const double x = src.r[0][s], y = src.r[1][s], z = src.r[2][s];
+         dst.r[0][d] = x; dst.r[1][d] = y; dst.r[2][d] = z;
+         dst.rf[d] = make_float4((float)(x - geo.lMin[0]), (float)(y - geo.lMin[1]), (float)(z - geo.lMin[2]), 0.f);
          dst.p[0][d] = src.p[0][s]; dst.p[1][d] = src.p[1][s]; dst.p[2][d] = src.p[2][s];
          dst.gid[d] = g; dst.spec[d] = src.spec[s]; dst.cell[d] = c;
          isLocal = cellType[c] & CT_LOCAL;
@@ -391,20 +393,24 @@ k_energy_final(const double* __restrict__ partial, int nPart, double* __restrict
 // ------------------------------------------------------------------ host side
 static int allocAtoms(AtomArrays& a, long cap)
 {
+   const long capP = cap + COMD_PAD;
    for (int k = 0; k < 3; ++k)
    {
-      CUDA_TRY(cudaMalloc(&a.r[k], cap * sizeof(double)));
-      CUDA_TRY(cudaMalloc(&a.p[k], cap * sizeof(double)));
+      CUDA_TRY(cudaMalloc(&a.r[k], capP * sizeof(double)));
+      CUDA_TRY(cudaMalloc(&a.p[k], capP * sizeof(double)));
+      CUDA_TRY(cudaMemset(a.r[k], 0, capP * sizeof(double)));
    }
-   CUDA_TRY(cudaMalloc(&a.gid, cap * sizeof(int)));
-   CUDA_TRY(cudaMalloc(&a.spec, cap * sizeof(int)));
-   CUDA_TRY(cudaMalloc(&a.cell, cap * sizeof(int)));
+   CUDA_TRY(cudaMalloc(&a.gid, capP * sizeof(int)));
+   CUDA_TRY(cudaMalloc(&a.spec, capP * sizeof(int)));
+   CUDA_TRY(cudaMalloc(&a.cell, capP * sizeof(int)));
+   CUDA_TRY(cudaMalloc(&a.rf, capP * sizeof(float4)));
+   CUDA_TRY(cudaMemset(a.rf, 0, capP * sizeof(float4)));
    return COMD_OK;
 }
 static void freeAtoms(AtomArrays& a)
 {
    for (int k = 0; k < 3; ++k) { cudaFree(a.r[k]); cudaFree(a.p[k]); }
-   cudaFree(a.gid); cudaFree(a.spec); cudaFree(a.cell);
+   cudaFree(a.gid); cudaFree(a.spec); cudaFree(a.cell); cudaFree(a.rf);
 }
 
 extern "C" int comd_dev_create(ComdDev** out, int deviceId, const ComdGeometry* geom, long atomCapacity)
@@ -454,7 +460,7 @@ extern "C" int comd_dev_create(ComdDev** out, int deviceId, const ComdGeometry* 
    int rc;
    if ((rc = allocAtoms(d->A, cap)) != COMD_OK) return rc;
    if ((rc = allocAtoms(d->B, cap)) != COMD_OK) return rc;
-   for (int k = 0; k < 3; ++k) { CUDA_TRY(cudaMalloc(&d->f[k], cap * sizeof(double))); CUDA_TRY(cudaMemset(d->f[k], 0, cap * sizeof(double))); }
+   for (int k = 0; k < 3; ++k) { CUDA_TRY(cudaMalloc(&d->f[k], (cap + COMD_PAD) * sizeof(double))); CUDA_TRY(cudaMemset(d->f[k], 0, (cap + COMD_PAD) * sizeof(double))); }
    CUDA_TRY(cudaMalloc(&d->e, cap * sizeof(double))); CUDA_TRY(cudaMemset(d->e, 0, cap * sizeof(double)));
    CUDA_TRY(cudaMalloc(&d->cellStart, (g.nCells + 1) * sizeof(int)));
    CUDA_TRY(cudaMemset(d->cellStart, 0, (g.nCells + 1) * sizeof(int)));
@@ -473,9 +479,9 @@ extern "C" int comd_dev_create(ComdDev** out, int deviceId, const ComdGeometry* 
    CUDA_TRY(cudaMalloc(&d->redPartial, 2 * RED_BLOCKS * sizeof(double)));
    CUDA_TRY(cudaMalloc(&d->redOut, 2 * sizeof(double)));
    CUDA_TRY(cudaMallocHost(&d->hRed, 2 * sizeof(double)));
-   CUDA_TRY(cudaMalloc(&d->rhobar, cap * sizeof(double)));
-   CUDA_TRY(cudaMalloc(&d->dfEmbed, cap * sizeof(double)));
-   CUDA_TRY(cudaMemset(d->dfEmbed, 0, cap * sizeof(double)));
+   CUDA_TRY(cudaMalloc(&d->rhobar, (cap + COMD_PAD) * sizeof(double)));
+   CUDA_TRY(cudaMalloc(&d->dfEmbed, (cap + COMD_PAD) * sizeof(double)));
+   CUDA_TRY(cudaMemset(d->dfEmbed, 0, (cap + COMD_PAD) * sizeof(double)));
 
    // message capacity: the two largest planes of cells, generously populated
    // (bufCapacity, haloExchange.c:202-207, sized without MAXATOMS padding)
@@ -515,6 +521,10 @@ extern "C" int comd_dev_create(ComdDev** out, int deviceId, const ComdGeometry* 
    CUDA_TRY(cudaMemcpy(d->cellType, ct.data(), g.nCells, cudaMemcpyHostToDevice));
    d->approxAtoms = 0;
    d->mass = 1.0;
+   d->optForceVariant = 1;
+   d->optTileTx = 8;
+   if (const char* ev = getenv("COMD_FORCE_VARIANT")) d->optForceVariant = atoi(ev);
+   if (const char* ev = getenv("COMD_TILE_TX")) d->optTileTx = atoi(ev);
    *out = d;
    return COMD_OK;
 }
@@ -529,7 +539,7 @@ extern "C" int comd_dev_destroy(ComdDev* d)
    cudaFree(d->e); cudaFree(d->cellStart); cudaFree(d->cellCount); cudaFree(d->cellFill); cudaFree(d->cellType);
    cudaFree(d->cellKey); cudaFree(d->shell); cudaFree(d->tmpSrc); cudaFree(d->tmpGid); cudaFree(d->tmpCell);
    cudaFree(d->scanBlock); cudaFree(d->cnt); cudaFreeHost(d->hCnt); cudaFree(d->redPartial); cudaFree(d->redOut);
-   cudaFreeHost(d->hRed); cudaFree(d->rhobar); cudaFree(d->dfEmbed); cudaFree(d->tabMem); cudaFree(d->runOff);
+   cudaFreeHost(d->hRed); cudaFree(d->rhobar); cudaFree(d->dfEmbed); cudaFree(d->tabMem); cudaFree(d->tPRmem); cudaFree(d->runOff);
    cudaFree(d->nlList); cudaFree(d->nlCount);
    for (int k = 0; k < 2; ++k) { cudaFree(d->sendBuf[k]); cudaFree(d->recvBuf[k]); cudaFree(d->fpSend[k]); cudaFree(d->fpRecv[k]); }
    if (d->hStage) cudaFreeHost(d->hStage);
@@ -578,6 +588,19 @@ extern "C" int comd_dev_set_eam(ComdDev* d, double cutoff, const ComdTable* phi,
       out[k]->n = n; out[k]->x0 = t[k]->x0; out[k]->invDx = t[k]->invDx; out[k]->v = d->tabMem + off + 1;
       off += n + 3 + ((n + 3) & 1);      // keep every table 16-byte aligned
    }
+   // phi and rho on one grid (true for funcfl and setfl files, eam.c:743-757,853-872):
+   // interleave them so a pass-1 lookup is four 16-byte loads instead of eight 8-byte ones
+   if (d->tPRmem) { cudaFree(d->tPRmem); d->tPRmem = nullptr; }
+   d->tPR = nullptr;
+   if (phi->n == rho->n && phi->x0 == rho->x0 && phi->invDx == rho->invDx)
+   {
+      const int n = phi->n;
+      std::vector<double> h(2 * (size_t)(n + 3));
+      for (int i = -1; i < n + 2; ++i) { h[2 * (i + 1)] = phi->values[i]; h[2 * (i + 1) + 1] = rho->values[i]; }
+      CUDA_TRY(cudaMalloc(&d->tPRmem, h.size() * sizeof(double)));
+      CUDA_TRY(cudaMemcpy(d->tPRmem, h.data(), h.size() * sizeof(double), cudaMemcpyHostToDevice));
+      d->tPR = d->tPRmem + 1;
+   }
    d->potKind = 2; d->cutoff = cutoff;
    return COMD_OK;
 }
@@ -590,6 +613,7 @@ int comdCheckErrors(ComdDev* d, const char* where)
    if (e & ERRB_CAPACITY) { comdSetError("%s: atom or message capacity exceeded (capacity %ld atoms)", where, d->cap); return COMD_E_CAPACITY; }
    if (e & ERRB_ESCAPE) { comdSetError("%s: an atom moved more than one link cell beyond the local domain in one step", where); return COMD_E_STATE; }
    if (e & ERRB_FPMISMATCH) { comdSetError("%s: F' halo message does not match the ghost population", where); return COMD_E_MISMATCH; }
+   if (e & ERRB_TILE) { comdSetError("%s: a force tile exceeds its shared-memory staging capacity (density far above the lattice average)", where); return COMD_E_CAPACITY; }
    if (e & ERRB_NLFULL) { comdSetError("%s: neighbour-list row overflow", where); return COMD_E_CAPACITY; }
    comdSetError("%s: device error bits 0x%x", where, e);
    return COMD_E_STATE;
@@ -646,10 +670,11 @@ extern "C" int comd_dev_redistribute(ComdDev* d)
    k_scan_add<<<(g.nCells + 255) / 256, 256, 0, s>>>(d->cellStart, d->scanBlock, g.nCells); LAUNCH_CHECK(d);
    k_scatter<<<gridFor(nGuess, 256), 256, 0, s>>>(d->cellKey, A.gid, d->cellStart, d->cellFill, d->tmpSrc, d->tmpGid,
                                                    d->tmpCell, d->cnt, d->cap); LAUNCH_CHECK(d);
-   k_rank_gather<<<gridFor(nGuess, 256), 256, 0, s>>>(d->tmpSrc, d->tmpGid, d->tmpCell, d->cellStart, d->cellType,
+   k_rank_gather<<<gridFor(nGuess, 256), 256, 0, s>>>(g, d->tmpSrc, d->tmpGid, d->tmpCell, d->cellStart, d->cellType,
                                                        d->A, d->B, d->cnt); LAUNCH_CHECK(d);
    AtomArrays t = d->A; d->A = d->B; d->B = t;
    d->nlValid = 0;
+   d->posDirty = 0;
    return COMD_OK;
 }
 
@@ -789,6 +814,7 @@ extern "C" int comd_dev_advance_position(ComdDev* d, double dt)
    CUDA_TRY(cudaSetDevice(d->device));
    k_advance_position<<<gridFor(d->approxAtoms, 256), 256, 0, d->stream>>>(dt, 1.0 / d->mass, d->A.cell, d->cellType,
       d->A.r[0], d->A.r[1], d->A.r[2], d->A.p[0], d->A.p[1], d->A.p[2], d->cnt); LAUNCH_CHECK(d);
+   d->posDirty = 1;
    return COMD_OK;
 }
 
@@ -811,6 +837,7 @@ extern "C" int comd_dev_compute_force(ComdDev* d)
    if (d->potKind == 0) { comdSetError("comd_dev_compute_force: no potential set"); return COMD_E_STATE; }
    CUDA_TRY(cudaSetDevice(d->device));
    if (d->useNL) { int rc = comdNeighborBuildIfNeeded(d); if (rc != COMD_OK) return rc; }
+   if (d->posDirty) { int rc = comdRefreshShadow(d); if (rc != COMD_OK) return rc; }
    const int slot = d->nForceEv % 128;
    CUDA_TRY(cudaEventRecord(d->evForce[2 * slot], d->stream));
    int rc = d->potKind == 1 ? comdForceLJ(d) : comdForceEAM(d);
@@ -818,6 +845,32 @@ extern "C" int comd_dev_compute_force(ComdDev* d)
    CUDA_TRY(cudaEventRecord(d->evForce[2 * slot + 1], d->stream));
    d->nForceEv++;
    return COMD_OK;
+}
+
+// FP32 shadow positions after a drift that was not followed by a redistribute
+__global__ void __launch_bounds__(256)
+k_refresh_shadow(DevGeom g, const double* __restrict__ rx, const double* __restrict__ ry, const double* __restrict__ rz,
+                 float4* __restrict__ rf, const int* __restrict__ cnt)
+{
+   const int n = cnt[C_NATOMS];
+   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+      rf[i] = make_float4((float)(rx[i] - g.lMin[0]), (float)(ry[i] - g.lMin[1]), (float)(rz[i] - g.lMin[2]), 0.f);
+}
+int comdRefreshShadow(ComdDev* d)
+{
+   k_refresh_shadow<<<gridFor(d->approxAtoms, 256), 256, 0, d->stream>>>(d->g, d->A.r[0], d->A.r[1], d->A.r[2], d->A.rf, d->cnt);
+   LAUNCH_CHECK(d);
+   d->posDirty = 0;
+   return COMD_OK;
+}
+
+extern "C" int comd_dev_set_option(ComdDev* d, const char* key, long value)
+{
+   if (!d || !key) return COMD_E_ARG;
+   if (!strcmp(key, "force_variant")) { if (value < 0 || value > 1) { comdSetError("force_variant: 0 or 1"); return COMD_E_ARG; } d->optForceVariant = (int)value; return COMD_OK; }
+   if (!strcmp(key, "tile_tx")) { if (value < 1 || value > 16) { comdSetError("tile_tx: 1..16"); return COMD_E_ARG; } d->optTileTx = (int)value; return COMD_OK; }
+   comdSetError("comd_dev_set_option: unknown key '%s'", key);
+   return COMD_E_ARG;
 }
 
 extern "C" int comd_dev_timestep(ComdDev* d, int nSteps, double dt)
@@ -829,6 +882,7 @@ extern "C" int comd_dev_timestep(ComdDev* d, int nSteps, double dt)
    {
       k_kick_drift<<<gridFor(d->approxAtoms, 256), 256, 0, d->stream>>>(0.5 * dt, dt, 1.0 / d->mass, d->A.cell, d->cellType,
          d->A.r[0], d->A.r[1], d->A.r[2], d->A.p[0], d->A.p[1], d->A.p[2], d->f[0], d->f[1], d->f[2], d->cnt); LAUNCH_CHECK(d);
+      d->posDirty = 1;
       int rc = comd_dev_redistribute(d);
       if (rc != COMD_OK) return rc;
       rc = comd_dev_compute_force(d);

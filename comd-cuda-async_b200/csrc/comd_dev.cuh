@@ -39,6 +39,8 @@ enum {
 #define ERRB_CELLFULL  4   // a cell holds more than COMD_MAX_CELL_ATOMS atoms
 #define ERRB_FPMISMATCH 8  // F' halo: message length != ghost population
 #define ERRB_NLFULL    16  // neighbour list row overflow
+#define ERRB_TILE      32  // a force tile's stencil rows exceed the shared-memory staging capacity
+#define COMD_PAD       16  // slack elements behind every per-atom array (aligned TMA over-read)
 
 // cell type bits
 #define CT_LOCAL  1
@@ -59,6 +61,7 @@ struct AtomArrays
 {
    double *r[3], *p[3];
    int *gid, *spec, *cell;
+   float4 *rf;                  // FP32 shadow of r relative to localMin (filter stage of the force tiles)
 };
 
 struct ComdDev
@@ -94,6 +97,7 @@ struct ComdDev
    double ljSigma, ljEps, cutoff;
    DevTable tPhi, tRho, tF;
    double *tabMem;
+   double2 *tPRmem, *tPR;                // interleaved {phi,rho} when both tables share one grid (entry 0), else NULL
    double *rhobar, *dfEmbed;
    // neighbour list
    int useNL; double skin;
@@ -104,6 +108,11 @@ struct ComdDev
    cudaEvent_t evForce[2 * 128]; int nForceEv; cudaEvent_t evT0, evT1; double lastForceMs; long nLaunches;   // force-time ring (128 calls) + user timer
    // e2e staging
    double* hStage; long hStageDoubles;
+   // tuning knobs (comd_dev_set_option)
+   int optForceVariant;         // 0 = thread-per-atom stencil loop (v1), 1 = tiled TMA/filter/process engine
+   int optTileTx;               // target cells per tile along x
+   int posDirty;                // positions moved since the FP32 shadow was written
+   int tileSmemSet[4];
    // nccl
    void* nccl; void* ncclComm;
 };
@@ -170,6 +179,7 @@ static inline int gridFor(long n, int block, int maxBlocks = 148 * 16)
 
 // implemented across the translation units
 int comdForceLJ(ComdDev* d);
+int comdRefreshShadow(ComdDev* d);
 int comdForceEAM(ComdDev* d);
 int comdFprimeHalo(ComdDev* d);
 int comdNeighborBuildIfNeeded(ComdDev* d);

@@ -1,0 +1,430 @@
+// force_tile.cuh -- the tiled pair-force engine shared by the LJ and EAM kernels (sm_100a).
+//
+// One CTA owns a run of TX consecutive local cells along x at fixed (y,z).  Thanks to the
+// padded x-fastest cell order (comd_dev.cuh) the 27-cell stencils of all its atoms are covered
+// by 9 contiguous atom runs (one per (dy,dz) row, TX+2 cells long).  The CTA
+//   1. stages those 9 runs in shared memory with TMA bulk copies (cp.async.bulk, one
+//      mbarrier): FP64 x/y/z (+ F' for EAM pass 3) and the FP32 float4 shadow positions;
+//   2. FILTER: 8 lanes per atom scan the atom's 9 row segments in FP32 (FFMA pipe) against
+//      a slightly enlarged cutoff and append survivors to lane-private queues -- no
+//      FP64 work and no divergent pair maths in this loop;
+//   3. PROCESS: the queues of the 8 lanes are compacted and each lane then evaluates one
+//      surviving pair per round in FP64 (exact r2 re-test, so the FP32 filter never decides
+//      a result): dense FP64-pipe work instead of the ~14 % lane utilisation a
+//      thread-per-atom stencil loop gets;
+//   4. reduces the 8 partial sums with xor shuffles (fixed order => bit-reproducible).
+// Reference kernels replaced: LJ_Force_cta_cell (gpu_lj_cta_cell.h:31-122),
+// EAM_Force_cta_cell / warp_atom (gpu_eam_cta_cell.h:37-295, gpu_eam_warp_atom.h:33-181).
+#pragma once
+#include "comd_dev.cuh"
+
+#define FT_THREADS 256
+#define FT_WARPS   (FT_THREADS / 32)
+#define FT_TXMAX   16                 // cells per tile along x (upper bound)
+#define FT_G       8                  // lanes per atom
+#define FT_APW     (32 / FT_G)        // atoms per warp pass
+#define FT_QCAP    24                 // lane-private queue depth
+#define FT_CH      8                  // filter iterations between queue-room checks
+#define FT_DCAP    (FT_QCAP * FT_G)   // dense queue depth per atom
+#define FT_HDR     1024               // bytes reserved for TileHdr
+
+struct TileCfg
+{
+   int   tilesX;        // tiles along x
+   int   sMax;          // staged-atom capacity of the shared arrays
+   float rcf2;          // FP32 filter threshold (cutoff + rounding margin)^2
+};
+
+struct TileHdr
+{
+   unsigned long long mbar;
+   int rowGA[9];                      // global index (even) of the first staged atom of each row
+   int rowS[9];                       // shared index of that atom
+   int cs[9][FT_TXMAX + 3];           // shared index of every cell start of the row
+   int iBeg, iEnd;                    // global range of the tile's own atoms
+   int total;
+};
+static_assert(sizeof(TileHdr) <= FT_HDR, "TileHdr");
+
+// kinds of pair work
+#define PK_LJ   0
+#define PK_EAM1 1
+#define PK_EAM3 3
+
+struct PairParams
+{
+   // LJ
+   double s6, eps, eShift;
+   // both
+   double rc2;
+   // EAM
+   DevTable tPhi, tRho, tF;
+   const double2* tPR;                // interleaved {phi,rho} (same grid), entry 0; valid [-1, n+1]
+};
+
+// ---- PTX helpers: mbarrier + 1-D bulk copy (TMA engine, UBLKCP in SASS) -----------------
+__device__ __forceinline__ unsigned smemAddr(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbarInit(void* bar, int count)
+{
+   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smemAddr(bar)), "r"(count));
+   asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbarExpectTx(void* bar, unsigned bytes)
+{
+   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smemAddr(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbarWait(void* bar, unsigned phase)
+{
+   unsigned ok = 0;
+   while (!ok)
+      asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}\n"
+                   : "=r"(ok) : "r"(smemAddr(bar)), "r"(phase) : "memory");
+}
+__device__ __forceinline__ void bulkG2S(void* dst, const void* src, unsigned bytes, void* bar)
+{
+   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                ::"r"(smemAddr(dst)), "l"(src), "r"(bytes), "r"(smemAddr(bar)) : "memory");
+}
+
+// interpolate() of eam.c:557-579 on four already-loaded stencil values
+__device__ __forceinline__ void interpValue(double tm, double t0, double t1, double t, double& f)
+{
+   const double g1 = t1 - tm;
+   f = t0 + 0.5 * t * (g1 + t * (t1 + tm - 2.0 * t0));
+}
+__device__ __forceinline__ void interpDeriv(double tm, double t0, double t1, double t2, double t, double invDx, double& df)
+{
+   const double g1 = t1 - tm;
+   const double g2 = t2 - t0;
+   df = 0.5 * (g1 + t * (g2 - g1)) * invDx;
+}
+// index + fraction with the reference's one-sided clamps (eam.c:561-571)
+__device__ __forceinline__ int tableIndex(const DevTable& T, double r, double& t)
+{
+   if (r < T.x0) r = T.x0;
+   r = (r - T.x0) * T.invDx;
+   int ii = __double2int_rd(r);
+   if (ii > T.n) { ii = T.n; r = T.n / T.invDx; }
+   t = r - floor(r);
+   return ii;
+}
+__device__ __forceinline__ void tableLookupFull(const DevTable& T, double r, double& f, double& df)
+{
+   double t;
+   const int ii = tableIndex(T, r, t);
+   const double* __restrict__ v = T.v + ii;
+   const double tm = __ldg(v - 1), t0 = __ldg(v), t1 = __ldg(v + 1), t2 = __ldg(v + 2);
+   interpValue(tm, t0, t1, t, f);
+   interpDeriv(tm, t0, t1, t2, t, T.invDx, df);
+}
+
+// ---- one surviving pair, FP64 ---------------------------------------------------------
+// acc layout: [0..2] force, [3] energy part, [4] rhobar (EAM pass 1)
+template <int KIND>
+__device__ __forceinline__ void pairEval(const PairParams& P, double dx, double dy, double dz, double r2,
+                                         double dfi, double dfj, double* acc)
+{
+   if (KIND == PK_LJ)
+   {  // ljForce.c:207-233
+      const double ir2 = 1.0 / r2;
+      const double r6 = (P.s6 * ir2) * (ir2 * ir2);
+      acc[3] += r6 * (r6 - 1.0) - P.eShift;
+      const double fr = -4.0 * P.eps * r6 * ir2 * (12.0 * r6 - 6.0);
+      acc[0] -= dx * fr; acc[1] -= dy * fr; acc[2] -= dz * fr;
+   }
+   else if (KIND == PK_EAM1)
+   {  // eam.c:311-345
+      const double rinv = rsqrt(r2);
+      const double r = r2 * rinv;
+      double phi, dphi, rho;
+      if (P.tPR)
+      {
+         double t;
+         const int ii = tableIndex(P.tPhi, r, t);
+         const double2* __restrict__ v = P.tPR + ii;
+         const double2 vm = __ldg(v - 1), v0 = __ldg(v), v1 = __ldg(v + 1), v2 = __ldg(v + 2);
+         interpValue(vm.x, v0.x, v1.x, t, phi);
+         interpDeriv(vm.x, v0.x, v1.x, v2.x, t, P.tPhi.invDx, dphi);
+         interpValue(vm.y, v0.y, v1.y, t, rho);
+      }
+      else
+      {
+         double drho;
+         tableLookupFull(P.tPhi, r, phi, dphi);
+         tableLookupFull(P.tRho, r, rho, drho);
+      }
+      const double s = dphi * rinv;
+      acc[0] -= s * dx; acc[1] -= s * dy; acc[2] -= s * dz;
+      acc[3] += 0.5 * phi;
+      acc[4] += rho;
+   }
+   else
+   {  // eam.c:390-409
+      const double rinv = rsqrt(r2);
+      const double r = r2 * rinv;
+      double t, drho;
+      const int ii = tableIndex(P.tRho, r, t);
+      const double* __restrict__ v = P.tRho.v + ii;
+      const double tm = __ldg(v - 1), t0 = __ldg(v), t1 = __ldg(v + 1), t2 = __ldg(v + 2);
+      interpDeriv(tm, t0, t1, t2, t, P.tRho.invDx, drho);
+      const double s = (dfi + dfj) * drho * rinv;
+      acc[0] -= s * dx; acc[1] -= s * dy; acc[2] -= s * dz;
+   }
+}
+
+template <int KIND> struct PairTraits { static constexpr int NACC = KIND == PK_LJ ? 4 : (KIND == PK_EAM1 ? 5 : 3); };
+
+// shared-memory bytes for a given staging capacity
+template <int KIND>
+__host__ __device__ inline size_t tileSmemBytes(int sMax)
+{
+   size_t b = FT_HDR;
+   b += (size_t)sMax * 8 * (KIND == PK_EAM3 ? 4 : 3);      // x,y,z (+F')
+   b += (size_t)sMax * 16;                                 // float4 shadow
+   b += (size_t)FT_WARPS * FT_QCAP * 32 * 2;               // lane queues
+   b += (size_t)FT_WARPS * FT_APW * FT_DCAP * 2;           // dense queues
+   return b;
+}
+
+// ---- PROCESS: compact the 8 lane queues of every atom, then one pair per lane per round ----
+template <int KIND>
+__device__ __forceinline__ void processQueues(const PairParams& P, unsigned short* myQ, unsigned short* myD, int& qn,
+                                              int gl, int si, double xi, double yi, double zi, double dfi,
+                                              const double* sx, const double* sy, const double* sz, const double* sdf,
+                                              double* acc)
+{
+   const unsigned full = 0xffffffffu;
+   int incl = qn;
+   #pragma unroll
+   for (int o = 1; o < FT_G; o <<= 1) { const int u = __shfl_up_sync(full, incl, o, FT_G); if (gl >= o) incl += u; }
+   const int total = __shfl_sync(full, incl, FT_G - 1, FT_G);
+   const int w0 = incl - qn;
+   for (int k = 0; k < qn; ++k) myD[w0 + k] = myQ[k * 32];
+   __syncwarp();
+   const int rounds = (__reduce_max_sync(full, total) + FT_G - 1) / FT_G;
+   for (int rd = 0; rd < rounds; ++rd)
+   {
+      const int k = rd * FT_G + gl;
+      if (k < total)
+      {
+         const int j = myD[k];
+         const double dx = xi - sx[j], dy = yi - sy[j], dz = zi - sz[j];
+         const double r2 = dx * dx + dy * dy + dz * dz;
+         const bool in = (KIND == PK_EAM3) ? (r2 < P.rc2) : (r2 <= P.rc2);     // eam.c:317 vs :397
+         if (in && j != si) pairEval<KIND>(P, dx, dy, dz, r2, dfi, KIND == PK_EAM3 ? sdf[j] : 0.0, acc);
+      }
+   }
+   __syncwarp();
+   qn = 0;
+}
+
+template <int KIND>
+__global__ void __launch_bounds__(FT_THREADS, 2)
+k_force_tile(DevGeom g, TileCfg cfg, PairParams P,
+             const double* __restrict__ rx, const double* __restrict__ ry, const double* __restrict__ rz,
+             const float4* __restrict__ rf, const int* __restrict__ cell, const int* __restrict__ cellStart,
+             const double* __restrict__ dfIn,
+             double* __restrict__ fx, double* __restrict__ fy, double* __restrict__ fz, double* __restrict__ e,
+             double* __restrict__ rhobar, double* __restrict__ dfOut, int* __restrict__ cnt)
+{
+   extern __shared__ __align__(128) unsigned char smem[];
+   constexpr int NACC = PairTraits<KIND>::NACC;
+   const unsigned full = 0xffffffffu;
+   TileHdr& H = *reinterpret_cast<TileHdr*>(smem);
+   const int sMax = cfg.sMax;
+   double* sx = reinterpret_cast<double*>(smem + FT_HDR);
+   double* sy = sx + sMax;
+   double* sz = sy + sMax;
+   double* sdf = sz + sMax;
+   unsigned char* q = reinterpret_cast<unsigned char*>(KIND == PK_EAM3 ? sdf + sMax : sdf);
+   float4* sf = reinterpret_cast<float4*>(q); q += (size_t)sMax * 16;
+   unsigned short* qLane = reinterpret_cast<unsigned short*>(q); q += FT_WARPS * FT_QCAP * 32 * 2;
+   unsigned short* qDense = reinterpret_cast<unsigned short*>(q);
+
+   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+   int tile = blockIdx.x;
+   const int tx = tile % cfg.tilesX; tile /= cfg.tilesX;
+   const int iy = tile % g.n[1], iz = tile / g.n[1];
+   const int cx0 = (int)((long)tx * g.n[0] / cfg.tilesX), cx1 = (int)((long)(tx + 1) * g.n[0] / cfg.tilesX);
+   const int Tx = cx1 - cx0, nk = Tx + 3;
+
+   if (tid == 0) mbarInit(&H.mbar, 1);
+   for (int t = tid; t < 9 * nk; t += FT_THREADS)
+   {
+      const int r = t / nk, k = t - r * nk;
+      H.cs[r][k] = cellStart[cellIndex(g, cx0 - 1, iy + (r % 3) - 1, iz + (r / 3) - 1) + k];
+   }
+   __syncthreads();
+   if (warp == 0)
+   {  // row layout + TMA issue: lane r < 9 owns row r
+      int gs = 0, ge = 0;
+      if (lane < 9) { gs = H.cs[lane][0]; ge = H.cs[lane][nk - 1]; }
+      const int ga = gs & ~1, cntR = ((ge + 1) & ~1) - ga;        // 16-byte aligned ends for the FP64 arrays
+      int incl = cntR;
+      #pragma unroll
+      for (int o = 1; o < 16; o <<= 1) { const int u = __shfl_up_sync(full, incl, o); if (lane >= o) incl += u; }
+      const int excl = incl - cntR;
+      const int total = __shfl_sync(full, incl, 8);
+      if (lane < 9) { H.rowGA[lane] = ga; H.rowS[lane] = excl; }
+      if (lane == 0) { H.total = total; H.iBeg = H.cs[4][1]; H.iEnd = H.cs[4][Tx + 1]; }
+      if (total <= sMax)
+      {
+         constexpr unsigned perAtom = 8u * (KIND == PK_EAM3 ? 4 : 3) + 16u;
+         if (lane == 0) mbarExpectTx(&H.mbar, (unsigned)total * perAtom);
+         __syncwarp();
+         if (lane < 9 && cntR > 0)
+         {
+            const unsigned nb = (unsigned)cntR * 8u;
+            bulkG2S(sx + excl, rx + ga, nb, &H.mbar);
+            bulkG2S(sy + excl, ry + ga, nb, &H.mbar);
+            bulkG2S(sz + excl, rz + ga, nb, &H.mbar);
+            if (KIND == PK_EAM3) bulkG2S(sdf + excl, dfIn + ga, nb, &H.mbar);
+            bulkG2S(sf + excl, rf + ga, nb * 2u, &H.mbar);
+         }
+      }
+   }
+   __syncthreads();
+   if (H.total > sMax)
+   {
+      if (tid == 0) atomicOr(&cnt[C_ERR], ERRB_TILE);
+      return;
+   }
+   for (int t = tid; t < 9 * nk; t += FT_THREADS)
+   {
+      const int r = t / nk, k = t - r * nk;
+      H.cs[r][k] = H.rowS[r] + (H.cs[r][k] - H.rowGA[r]);
+   }
+   __syncthreads();
+   mbarWait(&H.mbar, 0);
+
+   const int g4 = lane / FT_G, gl = lane % FT_G;
+   const int iBeg = H.iBeg, nI = H.iEnd - iBeg;
+   const int sI0 = H.rowS[4] + (iBeg - H.rowGA[4]);
+   const int cellBase = cellIndex(g, cx0, iy, iz);
+   unsigned short* myQ = qLane + warp * FT_QCAP * 32 + lane;
+   unsigned short* myD = qDense + (warp * FT_APW + g4) * FT_DCAP;
+   const float rcf2 = cfg.rcf2;
+
+   for (int quad = warp; FT_APW * quad < nI; quad += FT_WARPS)
+   {
+      const int il = FT_APW * quad + g4;
+      const bool act = il < nI;
+      const int si = sI0 + il;
+      int cxl = 0;
+      float xif = 0.f, yif = 0.f, zif = 0.f;
+      double xi = 0.0, yi = 0.0, zi = 0.0, dfi = 0.0;
+      if (act)
+      {
+         cxl = cell[iBeg + il] - cellBase;
+         const float4 v = sf[si];
+         xif = v.x; yif = v.y; zif = v.z;
+         xi = sx[si]; yi = sy[si]; zi = sz[si];
+         if (KIND == PK_EAM3) dfi = sdf[si];
+      }
+      double acc[5] = { 0.0, 0.0, 0.0, 0.0, 0.0 };
+      int qn = 0;
+      #pragma unroll 1
+      for (int r = 0; r < 9; ++r)
+      {
+         int jb = 0, je = 0;
+         if (act) { jb = H.cs[r][cxl]; je = H.cs[r][cxl + 3]; }
+         const int maxlen = __reduce_max_sync(full, je - jb);
+         #pragma unroll 1
+         for (int base = 0; base < maxlen; base += FT_G * FT_CH)
+         {
+            if (__any_sync(full, qn > FT_QCAP - FT_CH))
+               processQueues<KIND>(P, myQ, myD, qn, gl, si, xi, yi, zi, dfi, sx, sy, sz, sdf, acc);
+            const int left = (maxlen - base + FT_G - 1) / FT_G;
+            const int itEnd = left < FT_CH ? left : FT_CH;
+            int k = jb + base + gl;
+            for (int it = 0; it < itEnd; ++it, k += FT_G)
+            {
+               if (k < je)
+               {
+                  const float4 v = sf[k];
+                  const float ddx = xif - v.x, ddy = yif - v.y, ddz = zif - v.z;
+                  const float r2 = ddx * ddx + ddy * ddy + ddz * ddz;
+                  if (r2 <= rcf2) { myQ[qn * 32] = (unsigned short)k; ++qn; }
+               }
+            }
+         }
+      }
+      processQueues<KIND>(P, myQ, myD, qn, gl, si, xi, yi, zi, dfi, sx, sy, sz, sdf, acc);
+      #pragma unroll
+      for (int a = 0; a < NACC; ++a)
+      {
+         #pragma unroll
+         for (int o = FT_G / 2; o > 0; o >>= 1) acc[a] += __shfl_xor_sync(full, acc[a], o);
+      }
+      if (act && gl == 0)
+      {
+         const int i = iBeg + il;
+         if (KIND == PK_LJ)
+         {
+            fx[i] = acc[0]; fy[i] = acc[1]; fz[i] = acc[2];
+            e[i] = (0.5 * acc[3]) * (4.0 * P.eps);            // ljForce.c:256-261
+         }
+         else if (KIND == PK_EAM1)
+         {
+            double fe, dfe;
+            tableLookupFull(P.tF, acc[4], fe, dfe);            // eam.c:352-371 (pass 2 fused)
+            fx[i] = acc[0]; fy[i] = acc[1]; fz[i] = acc[2];
+            e[i] = acc[3] + fe;
+            rhobar[i] = acc[4];
+            dfOut[i] = dfe;
+         }
+         else
+         {
+            fx[i] += acc[0]; fy[i] += acc[1]; fz[i] += acc[2];
+         }
+      }
+   }
+}
+
+// ---- host launcher ----------------------------------------------------------------------
+#include <cmath>
+template <int KIND>
+static int launchForceTile(ComdDev* d, PairParams P, const double* dfIn)
+{
+   const DevGeom& g = d->g;
+   int txT = d->optTileTx;
+   if (txT > FT_TXMAX) txT = FT_TXMAX;
+   if (txT > g.n[0]) txT = g.n[0];
+   if (txT < 1) txT = 1;
+   // mean population of a cell, from whichever count the host last saw (with or without ghosts)
+   const double perCell = (double)(d->approxAtoms > 0 ? d->approxAtoms : d->cap) / ((double)g.n[0] * g.n[1] * g.n[2]);
+   int sMax; size_t bytes;
+   for (;;)
+   {  // staging capacity: the 9 rows at 1.25x the mean density + slack; two CTAs per SM if possible
+      sMax = (int)(9.0 * (txT + 2) * perCell * 1.25) + 9 * 2 + 96;
+      sMax = (sMax + 1) & ~1;
+      bytes = tileSmemBytes<KIND>(sMax);
+      if (bytes <= 113 * 1024 || txT == 1) break;
+      --txT;
+   }
+   if (bytes > 227 * 1024 || sMax > 65534)
+   { comdSetError("force tile: %d staged atoms (%zu B) do not fit in shared memory", sMax, bytes); return COMD_E_CAPACITY; }
+   TileCfg cfg;
+   cfg.tilesX = (g.n[0] + txT - 1) / txT;
+   cfg.sMax = sMax;
+   double ext = 0.0;
+   for (int a = 0; a < 3; ++a)
+   {
+      const double e = (g.lMax[a] - g.lMin[a]) + 2.0 / g.inv[a];
+      if (e > ext) ext = e;
+   }
+   const double rc = sqrt(P.rc2);
+   const double rcf = rc + 4.0 * sqrt(3.0) * ext * ldexp(1.0, -24);       // FP32 rounding of both shadow positions, doubled
+   cfg.rcf2 = nextafterf((float)(rcf * rcf * (1.0 + 1e-6)), INFINITY);
+   const int slot = KIND == PK_EAM3 ? 2 : KIND;
+   if ((size_t)d->tileSmemSet[slot] < bytes)
+   {
+      CUDA_TRY(cudaFuncSetAttribute(k_force_tile<KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+      d->tileSmemSet[slot] = (int)bytes;
+   }
+   const int grid = cfg.tilesX * g.n[1] * g.n[2];
+   k_force_tile<KIND><<<grid, FT_THREADS, bytes, d->stream>>>(g, cfg, P, d->A.r[0], d->A.r[1], d->A.r[2], d->A.rf, d->A.cell,
+      d->cellStart, dfIn, d->f[0], d->f[1], d->f[2], d->e, d->rhobar, d->dfEmbed, d->cnt);
+   LAUNCH_CHECK(d);
+   return COMD_OK;
+}

@@ -47,6 +47,7 @@ ABI_SYMBOLS = [
     "comd_dev_set_neighbor_list", "comd_dev_neighbor_stats", "comd_comm_unique_id", "comd_comm_init",
     "comd_comm_allreduce_sum", "comd_comm_allreduce_sum_int", "comd_comm_barrier", "comd_dev_sync",
     "comd_dev_kernel_stats", "comd_dev_step_host", "comd_dev_fp64_peak", "comd_dev_timer_start", "comd_dev_timer_stop",
+    "comd_dev_set_option",
 ]
 
 _lib = None
@@ -87,6 +88,7 @@ def lib():
         L.comd_comm_allreduce_sum_int.argtypes = [C.c_void_p, C.POINTER(C.c_long), C.c_int]
         L.comd_comm_barrier.argtypes = [C.c_void_p]
         L.comd_dev_sync.argtypes = [C.c_void_p]
+        L.comd_dev_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_long]
         L.comd_dev_kernel_stats.argtypes = [C.c_void_p, _dp, C.POINTER(C.c_long)]
         L.comd_dev_fp64_peak.argtypes = [C.c_void_p, _dp]
         L.comd_dev_timer_start.argtypes = [C.c_void_p]
@@ -240,6 +242,9 @@ class Device:
 
     def sync(self):
         _chk(lib().comd_dev_sync(self.h))
+
+    def set_option(self, key, value):
+        _chk(lib().comd_dev_set_option(self.h, key.encode(), int(value)))
 
     def set_neighbor_list(self, use, skin):
         _chk(lib().comd_dev_set_neighbor_list(self.h, 1 if use else 0, skin))

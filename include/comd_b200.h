@@ -140,6 +140,12 @@ int  comd_comm_allreduce_sum(ComdDev* dev, double* inout, int n);   /* addRealPa
 int  comd_comm_allreduce_sum_int(ComdDev* dev, long* inout, int n); /* addIntParallel,  parallel.c:120 */
 int  comd_comm_barrier(ComdDev* dev);                               /* barrierParallel, parallel.c:93  */
 
+/* ---- tuning knobs (no reference counterpart; defaults are the measured-best settings):
+ *   "force_variant"  1 = tiled TMA-staged filter/process kernels (default), 0 = thread-per-atom
+ *                    stencil loop (the shape of LJ_Force_thread_atom, gpu_lj_thread_atom.h:31-143)
+ *   "tile_tx"        target cells per force tile along x (1..16) */
+int  comd_dev_set_option(ComdDev* dev, const char* key, long value);
+
 /* ---- measurement hooks (bench.py / tests) ---------------------------------------- */
 int  comd_dev_sync(ComdDev* dev);
 /* Mean CUDA-event duration (ms) of the force calls (comd_dev_compute_force, also inside

@@ -263,3 +263,28 @@ def test_errors_are_returned_not_fatal():
     with pytest.raises(pycomd.ComdError):
         d2.set_lj(cutoff=50.0)                   # cells smaller than the cutoff
     d2.close(); dev.close()
+
+
+@pytest.mark.parametrize("kind", list(KINDS))
+@pytest.mark.parametrize("tx", [1, 3, 8])
+def test_tiled_kernels_match_thread_atom_kernels(kind, tx):
+    """The tiled TMA/filter/process engine and the plain stencil loop are two summation orders of
+    the same pair set: same forces to round-off, and both within tolerance of the oracle."""
+    n = 8
+    orc = oracle_sim(KINDS[kind], n, delta=0.12, temperature=900.0)
+    a = orc.atoms()
+    o = by_gid(a)
+    res = []
+    for variant in (0, 1):
+        dev, _ = device_for(orc, (n, n, n))
+        dev.set_option("force_variant", variant)
+        dev.set_option("tile_tx", tx)
+        dev.upload(a["gid"], a["r"], a["p"])
+        dev.compute_force()
+        d = by_gid(dev.download())
+        assert rel_err(d["f"], o["f"]) <= FORCE_TOL
+        assert rel_err(d["U"], o["U"] * u_scale(kind)) <= FORCE_TOL
+        res.append(d)
+        dev.close()
+    assert rel_err(res[1]["f"], res[0]["f"]) <= 1e-13
+    assert rel_err(res[1]["U"], res[0]["U"]) <= 1e-13
