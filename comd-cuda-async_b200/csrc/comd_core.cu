@@ -623,7 +623,7 @@ static int syncCounters(ComdDev* d, const char* where)
 {
    CUDA_TRY(cudaMemcpyAsync(d->hCnt, d->cnt, C_COUNT * sizeof(int), cudaMemcpyDeviceToHost, d->stream));
    CUDA_TRY(cudaStreamSynchronize(d->stream));
-   d->approxAtoms = d->hCnt[C_NATOMS];
+   d->approxAtoms = d->hCnt[C_NATOMS]; d->approxHasGhosts = 1;
    return comdCheckErrors(d, where);
 }
 
@@ -704,7 +704,7 @@ extern "C" int comd_dev_upload_atoms(ComdDev* d, int n, const int* gid, const in
    k_set_int<<<gridFor(n, 256), 256, 0, s>>>(A.cell, cellIndex(d->g, 0, 0, 0), n); LAUNCH_CHECK(d);
    k_set_int<<<1, 1, 0, s>>>(d->cnt + C_NATOMS, n, 1); LAUNCH_CHECK(d);
    k_set_int<<<1, 1, 0, s>>>(d->cnt + C_ERR, 0, 1); LAUNCH_CHECK(d);
-   d->approxAtoms = n;
+   d->approxAtoms = n; d->approxHasGhosts = 0;
    int rc = comd_dev_redistribute(d);
    if (rc != COMD_OK) return rc;
    return syncCounters(d, "comd_dev_upload_atoms");
@@ -976,7 +976,7 @@ extern "C" int comd_dev_step_host(ComdDev* d, int n, double dt,
    CUDA_TRY(cudaMemsetAsync(A.spec, 0, n * sizeof(int), s));
    k_set_int<<<gridFor(n, 256), 256, 0, s>>>(A.cell, cellIndex(d->g, 0, 0, 0), n); LAUNCH_CHECK(d);
    k_set_int<<<1, 1, 0, s>>>(d->cnt + C_NATOMS, n, 1); LAUNCH_CHECK(d);
-   d->approxAtoms = n;
+   d->approxAtoms = n; d->approxHasGhosts = 0;
    int rc = comd_dev_timestep(d, 1, dt);
    if (rc != COMD_OK) return rc;
    rc = comd_dev_energy(d, eLocal);          // syncs, refreshes hCnt

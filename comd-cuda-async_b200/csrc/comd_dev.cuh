@@ -86,6 +86,7 @@ struct ComdDev
    int *cnt;                    // C_COUNT device counters
    int *hCnt;                   // pinned mirror
    int approxAtoms;             // host-side estimate for grid sizing only
+   int approxHasGhosts;         // approxAtoms counts ghosts too (set from the device counter) or only locals (set from an upload)
    // messages
    long msgCap;                 // atoms per face message
    double *sendBuf[2], *recvBuf[2];

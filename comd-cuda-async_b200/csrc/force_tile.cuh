@@ -392,7 +392,8 @@ static int launchForceTile(ComdDev* d, PairParams P, const double* dfIn)
    if (txT > g.n[0]) txT = g.n[0];
    if (txT < 1) txT = 1;
    // mean population of a cell, from whichever count the host last saw (with or without ghosts)
-   const double perCell = (double)(d->approxAtoms > 0 ? d->approxAtoms : d->cap) / ((double)g.n[0] * g.n[1] * g.n[2]);
+   const double cellsCounted = d->approxHasGhosts ? (double)g.nCells : (double)g.n[0] * g.n[1] * g.n[2];
+   const double perCell = (double)(d->approxAtoms > 0 ? d->approxAtoms : d->cap) / cellsCounted;
    int sMax; size_t bytes;
    for (;;)
    {  // staging capacity: the 9 rows at 1.25x the mean density + slack; two CTAs per SM if possible

@@ -138,10 +138,13 @@ def test_migration_and_conservation(kind):
     """Hot, fast atoms cross cell and periodic boundaries: nobody is lost or duplicated and the
     owner cell always equals the reference rule evaluated on the device's own positions."""
     n = 6
-    orc = oracle_sim(KINDS[kind], n, delta=0.05, temperature=4000.0)
+    orc = oracle_sim(KINDS[kind], n, delta=0.05, temperature=1500.0)
     a = orc.atoms()
     dev, _ = device_for(orc, (n, n, n))
-    dev.upload(a["gid"], a["r"], a["p"])
+    # a uniform drift (forces are Galilean invariant) carries the whole crystal through cell and
+    # periodic boundaries: 0.02 A/fs * 300 fs = 6 A along x, half that along y, a quarter along z
+    drift = orc.potential()["mass"] * np.array([0.02, 0.01, -0.005])
+    dev.upload(a["gid"], a["r"], a["p"] + drift)
     dev.compute_force()
     cells = po.OracleCells([n * orc.potential()["lat"]] * 3, orc.potential()["cutoff"])
     moved = 0
@@ -157,7 +160,7 @@ def test_migration_and_conservation(kind):
         L = n * orc.potential()["lat"]
         assert d["r"].min() >= 0.0 and d["r"].max() < L              # locals live inside the box
         moved = max(moved, int(np.sum(d["box"] != box0)))
-    assert moved > (50 if kind != "lj" else 5)                                                # the test did exercise migration
+    assert moved > len(a["gid"]) // 4                                # the test did exercise migration
     dev.close()
 
 
@@ -198,7 +201,9 @@ def test_energy_after_100_steps(kind, n):
         ref0 = sum(orc.energies())
         orc.timestep(100)
         ref100 = sum(orc.energies())
-    assert abs(e0 - ref0) <= 1e-12 * abs(ref0)
+    # a sum over 32 000 atoms: the reference's own serial summation carries ~N*eps/2 of round-off,
+    # so the SUM is gated at 1e-11 (per-atom energies are gated at 1e-12 in the step-0 tests above)
+    assert abs(e0 - ref0) <= 1e-11 * abs(ref0)
     assert abs((ep + ek) - ref100) <= ENERGY100_TOL * abs(ref100)
     assert dev.num_local() == len(a["gid"])
     dev.close()
