@@ -156,6 +156,8 @@ def main():
     ap.add_argument("--workload", default="eam_strong", choices=sorted(WORKLOADS))
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--neighbor-list", type=int, default=int(os.environ.get("COMD_NL", "0")),
+                    help="1: neighbour-list force path (skin 0.1*cutoff, mycommand.c:210), 0: link-cell path")
     args = ap.parse_args()
     pot, ncell, scaling, label = WORKLOADS[args.workload]
 
@@ -185,7 +187,10 @@ def main():
     lat = potential["lat"]
     gext = [n_cells[a] * lat for a in range(3)]
     coord = (rank % grid[0], (rank // grid[0]) % grid[1], rank // (grid[0] * grid[1]))
-    geom = pycomd.make_geometry(gext, potential["cutoff"], grid, coord)
+    skin = 0.1 * potential["cutoff"] if args.neighbor_list else 0.0
+    geom = pycomd.make_geometry(gext, potential["cutoff"] + skin, grid, coord)
+    if args.neighbor_list:
+        label = label.replace("link-cell", "neighbour-list skin 0.1") if "link-cell" in label else label + ", neighbour-list skin 0.1"
     lmin = [geom.localMin[a] for a in range(3)]; lmax = [geom.localMax[a] for a in range(3)]
     gid, r = P.fcc_block(n_cells, lat, lmin, lmax)
     n_local = len(gid)
@@ -201,6 +206,8 @@ def main():
         dev.set_lj(potential["sigma"], potential["epsilon"], potential["cutoff"])
     else:
         dev.set_eam(potential["cutoff"], potential["phi"], potential["rho"], potential["f"])
+    if args.neighbor_list:
+        dev.set_neighbor_list(True, skin)
     if world > 1:
         import torch
         uid = torch.zeros(128, dtype=torch.uint8, device="cuda")

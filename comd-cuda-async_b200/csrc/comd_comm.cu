@@ -164,3 +164,21 @@ int comdExchangeFprimePhase(ComdDev* d, int ax)
 {
    return exchangePhase(d, ax, d->fpSend, d->fpRecv, C_FPSEND0, C_FPGOT0, 1);
 }
+
+// ghost refresh between neighbour-list rebuilds: same atoms, same order as the last full atom
+// exchange, positions only (the in-place update of unloadAtomsBuffer's hash-table branch,
+// haloExchange.c:1673-1683)
+int comdExchangeRefreshPhase(ComdDev* d, int ax)
+{
+   return exchangePhase(d, ax, d->sendBuf, d->recvBuf, C_SEND0, C_RECV0, 3);
+}
+
+// "if one process has to rebuild its neighbour list, all have to" (neighborList.c:236-244)
+int comdAllreduceMaxFlag(ComdDev* d, int* flag)
+{
+   if (d->nRanks == 1 || !d->ncclComm) return COMD_OK;
+   long v = *flag ? 1 : 0;
+   int rc = comd_comm_allreduce_sum_int(d, &v, 1);
+   *flag = v > 0;
+   return rc;
+}

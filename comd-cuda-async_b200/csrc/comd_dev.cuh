@@ -103,6 +103,12 @@ struct ComdDev
    // neighbour list
    int useNL; double skin;
    int *nlList; int *nlCount; int nlStride; int nlMax; double* nlLastR[3]; int nlBuilds; int nlValid;
+   long nlRows;                 // rows allocated in nlList
+   int nlRefreshes;             // steps served by a ghost refresh instead of a rebuild
+   unsigned long long* nlStat;  // device: [0] stored pairs, [1] max per atom
+   // ghost refresh between rebuilds: per face, sorted-array index of every atom sent / received by the
+   // last full atom exchange (recorded as pool indices, mapped through poolToSorted after the sort)
+   int *sendIdx[6], *recvIdx[6], *poolToSorted;
    // reductions
    double *redPartial; double *redOut; double *hRed;
    // stats
@@ -187,3 +193,7 @@ int comdNeighborBuildIfNeeded(ComdDev* d);
 int comdCheckErrors(ComdDev* d, const char* where);
 int comdExchangeAtomsPhase(ComdDev* d, int axis);       // comm.cu: moves send buffers to recv buffers (self or NCCL)
 int comdExchangeFprimePhase(ComdDev* d, int axis);
+int comdExchangeRefreshPhase(ComdDev* d, int axis);     // 3 doubles per atom, counts of the last full exchange
+int comdNeighborRefreshOrRebuild(ComdDev* d, int* didRefresh);   // neighbor.cu: the redistributeAtomsGpuNL decision
+int comdNeighborAfterSort(ComdDev* d);                  // neighbor.cu: map recorded pool indices to sorted indices
+int comdAllreduceMaxFlag(ComdDev* d, int* flag);        // comm.cu: OR of a host flag over the ranks

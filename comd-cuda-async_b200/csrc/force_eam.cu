@@ -9,7 +9,7 @@
 //   pass 2  per local atom     : (F,F') = interp(F, rhobar_i) ; U_i += F ; dfEmbed_i = F'
 //   halo    F' of ghost atoms  : three axis phases, plane by plane (haloExchange.c:1712-1860)
 //   pass 3  per pair r2 <  rc2 : f_i -= (F'_i + F'_j) rho' dr/r
-#include "force_tile.cuh"
+#include "force_nl.cuh"
 
 // interpolate(), eam.c:557-579, incl. its one-sided clamps
 __device__ __forceinline__ void tableLookup(const DevTable& t, double r, double& f, double& df)
@@ -259,15 +259,15 @@ int comdForceEAM(ComdDev* d)
 {
    const double rc2 = d->cutoff * d->cutoff;
    cudaStream_t s = d->stream;
-   if (d->optForceVariant == 1)
+   if (d->useNL || d->optForceVariant == 1)
    {
       PairParams Q = {};
       Q.rc2 = rc2; Q.tPhi = d->tPhi; Q.tRho = d->tRho; Q.tF = d->tF; Q.tPR = d->tPR;
-      int rc = launchForceTile<PK_EAM1>(d, Q, nullptr);
+      int rc = d->useNL ? launchForceNL<PK_EAM1>(d, Q, nullptr) : launchForceTile<PK_EAM1>(d, Q, nullptr);
       if (rc != COMD_OK) return rc;
       rc = comdFprimeHalo(d);
       if (rc != COMD_OK) return rc;
-      return launchForceTile<PK_EAM3>(d, Q, d->dfEmbed);
+      return d->useNL ? launchForceNL<PK_EAM3>(d, Q, d->dfEmbed) : launchForceTile<PK_EAM3>(d, Q, d->dfEmbed);
    }
    const int grid = gridFor(d->approxAtoms, 128, 148 * 64);
    k_eam_pass1<<<grid, 128, 0, s>>>(d->g, d->tPhi, d->tRho, d->tF, rc2, d->A.r[0], d->A.r[1], d->A.r[2], d->A.cell, d->cellType,

@@ -7,7 +7,7 @@
 //    fr = -4*eps*r6*ir2*(12*r6-6); f_i -= dr*fr; U_i += eLocal       (U in units of 4 eps, halved at the end)
 // Full-neighbour ("gather") form: every local atom accumulates its own force, so no
 // atomics and a fixed summation order (cell-major, gid-minor).
-#include "force_tile.cuh"
+#include "force_nl.cuh"
 
 struct LjParams { double s6, eps, rc2, eShift; };
 
@@ -66,11 +66,11 @@ int comdForceLJ(ComdDev* d)
    P.rc2 = d->cutoff * d->cutoff;
    const double rc6 = P.s6 / (P.rc2 * P.rc2 * P.rc2);
    P.eShift = 1.0 * rc6 * (rc6 - 1.0);                 // POT_SHIFT 1.0, ljForce.c:83,173-174
-   if (d->optForceVariant == 1)
+   if (d->useNL || d->optForceVariant == 1)
    {
       PairParams Q = {};
       Q.s6 = P.s6; Q.eps = P.eps; Q.eShift = P.eShift; Q.rc2 = P.rc2;
-      return launchForceTile<PK_LJ>(d, Q, nullptr);
+      return d->useNL ? launchForceNL<PK_LJ>(d, Q, nullptr) : launchForceTile<PK_LJ>(d, Q, nullptr);
    }
    k_lj_force_rows<<<gridFor(d->approxAtoms, 128, 148 * 64), 128, 0, d->stream>>>(d->g, P, d->A.r[0], d->A.r[1], d->A.r[2],
       d->A.cell, d->cellType, d->cellStart, d->cnt, d->f[0], d->f[1], d->f[2], d->e);

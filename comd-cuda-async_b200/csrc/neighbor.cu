@@ -1,22 +1,255 @@
-// neighbor.cu -- optional neighbour-list path (buildNeighborListGpu, gpu_kernels.cu:1981;
-// rebuild criterion neighborList.c:212-247).  Filled in after the link-cell path.
+// neighbor.cu -- the optional neighbour-list path (sm_100a): list build over the 27-cell
+// stencil with radius cutoff + skin, the max-displacement rebuild criterion, and the in-place
+// ghost refresh that replaces re-binning on the steps between rebuilds.
+//
+// Reference behaviour being replaced (file:line into /root/reference/src-mpi):
+//   buildNeighborListGpu / buildNeighborListKernel_warp   gpu_kernels.cu:1981-2019, 1494-1693
+//   buildNeighborListCpu (list radius, lastR snapshot)    neighborList.c:101-191
+//   neighborListUpdateRequired{Cpu,Gpu}                   neighborList.c:212-247, gpu_kernels.cu:1461-1480
+//   redistributeAtomsGpuNL (rebuild-or-refresh decision)  timestep.c:278-354
+//   unloadAtomsBuffer, in-place ghost update              haloExchange.c:1673-1683
+// The list is FULL (every local atom lists all its neighbours, like the reference's GPU lists),
+// row-major with a fixed stride, entries are indices into the sorted atom arrays (ghosts
+// included) in ascending order, i.e. cell-major / gid-minor: summation order stays canonical.
 #include "comd_dev.cuh"
+#include <cmath>
 
-int comdNeighborBuildIfNeeded(ComdDev* d) { (void)d; return COMD_OK; }
+#define NL_G 8                  // lanes per atom in the build and force kernels
+
+// ---- build -------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+k_nl_build(DevGeom g, double rl2,
+           const double* __restrict__ rx, const double* __restrict__ ry, const double* __restrict__ rz,
+           const int* __restrict__ cell, const unsigned char* __restrict__ cellType, const int* __restrict__ cellStart,
+           int* __restrict__ cnt, int* __restrict__ list, int* __restrict__ count, int stride, long rows,
+           double* __restrict__ lx, double* __restrict__ ly, double* __restrict__ lz, unsigned long long* __restrict__ stat)
+{
+   const unsigned full = 0xffffffffu;
+   const int n = cnt[C_NATOMS];
+   const int lane = threadIdx.x & 31, g4 = lane / NL_G, gl = lane % NL_G;
+   const int warpsPerGrid = gridDim.x * (blockDim.x >> 5);
+   const int rowY = g.P[0], rowZ = g.P[0] * g.P[1];
+   const int nQuads = (n + 3) >> 2;
+   for (int q = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); q < nQuads; q += warpsPerGrid)
+   {
+      const int i = 4 * q + g4;
+      int c = 0;
+      bool act = false;
+      if (i < n) { c = cell[i]; act = (cellType[c] & CT_LOCAL) != 0 && i < rows; }
+      if (!__any_sync(full, act)) continue;
+      double xi = 0.0, yi = 0.0, zi = 0.0;
+      if (act) { xi = rx[i]; yi = ry[i]; zi = rz[i]; }
+      int nn = 0;
+      int* row = list + (long)(act ? i : 0) * stride;
+      #pragma unroll 1
+      for (int r = 0; r < 9; ++r)
+      {
+         int jb = 0, je = 0;
+         if (act)
+         {
+            const int rc = c + ((r % 3) - 1) * rowY + ((r / 3) - 1) * rowZ;
+            jb = cellStart[rc - 1]; je = cellStart[rc + 2];
+         }
+         const int maxlen = __reduce_max_sync(full, je - jb);
+         for (int base = 0; base < maxlen; base += NL_G)
+         {
+            const int j = jb + base + gl;
+            bool ok = false;
+            if (j < je && j != i)
+            {
+               const double dx = xi - rx[j], dy = yi - ry[j], dz = zi - rz[j];
+               ok = dx * dx + dy * dy + dz * dz <= rl2;
+            }
+            const unsigned m = (__ballot_sync(full, ok) >> (g4 * NL_G)) & ((1u << NL_G) - 1u);
+            const int pos = nn + __popc(m & ((1u << gl) - 1u));
+            if (ok && pos < stride) row[pos] = j;
+            nn += __popc(m);
+         }
+      }
+      if (act && gl == 0)
+      {
+         count[i] = nn < stride ? nn : stride;
+         if (nn > stride) atomicOr(&cnt[C_ERR], ERRB_NLFULL);
+         lx[i] = xi; ly[i] = yi; lz[i] = zi;                 // lastR snapshot (neighborList.c:176-183)
+      }
+      // statistics: one atomic per warp
+      int tot = (act && gl == 0) ? nn : 0, mx = tot;
+      #pragma unroll
+      for (int o = 16; o > 0; o >>= 1) { tot += __shfl_xor_sync(full, tot, o); mx = max(mx, __shfl_xor_sync(full, mx, o)); }
+      if (lane == 0) { atomicAdd(&stat[0], (unsigned long long)tot); atomicMax(&stat[1], (unsigned long long)mx); }
+   }
+}
+
+// ---- rebuild criterion: any local atom moved more than skin/2 since the last build --------
+__global__ void __launch_bounds__(256)
+k_nl_check(double half2, const double* __restrict__ rx, const double* __restrict__ ry, const double* __restrict__ rz,
+           const double* __restrict__ lx, const double* __restrict__ ly, const double* __restrict__ lz,
+           const int* __restrict__ cell, const unsigned char* __restrict__ cellType, int* __restrict__ cnt)
+{
+   const int n = cnt[C_NATOMS];
+   bool hit = false;
+   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+   {
+      if (!(cellType[cell[i]] & CT_LOCAL)) continue;
+      const double dx = lx[i] - rx[i], dy = ly[i] - ry[i], dz = lz[i] - rz[i];
+      hit |= dx * dx + dy * dy + dz * dz > half2;
+   }
+   if (__any_sync(0xffffffffu, hit) && (threadIdx.x & 31) == 0) cnt[C_NLREBUILD] = 1;   // every writer stores the same value
+}
+
+// ---- index bookkeeping after the sort: pool index -> sorted index ---------------------------
+struct IdxLists { int* p[12]; };
+__global__ void __launch_bounds__(256)
+k_nl_map_idx(IdxLists L, const int* __restrict__ poolToSorted, const int* __restrict__ cnt)
+{
+   const int which = blockIdx.y;                                    // 0..5 send faces, 6..11 recv faces
+   const int n = cnt[(which < 6 ? C_SEND0 : C_RECV0 - 6) + which];
+   int* a = L.p[which];
+   for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) a[k] = poolToSorted[a[k]];
+}
+
+// ---- ghost refresh: positions only, the atoms and the order of the last full exchange -------
+__global__ void __launch_bounds__(256)
+k_nl_refresh_pack(int axis, const double* __restrict__ rx, const double* __restrict__ ry, const double* __restrict__ rz,
+                  const int* __restrict__ idxM, const int* __restrict__ idxP, const int* __restrict__ cnt,
+                  double* __restrict__ bufM, double* __restrict__ bufP,
+                  double shMx, double shMy, double shMz, double shPx, double shPy, double shPz)
+{
+   const int d = blockIdx.y;
+   const int n = cnt[C_SEND0 + 2 * axis + d];
+   const int* idx = d ? idxP : idxM;
+   double* out = d ? bufP : bufM;
+   const double sx = d ? shPx : shMx, sy = d ? shPy : shMy, sz = d ? shPz : shMz;
+   for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x)
+   {
+      const int i = idx[k];
+      out[3 * (long)k + 0] = rx[i] + sx;                            // same add as loadAtomsBuffer (haloExchange.c:1603-1605)
+      out[3 * (long)k + 1] = ry[i] + sy;
+      out[3 * (long)k + 2] = rz[i] + sz;
+   }
+}
+__global__ void __launch_bounds__(256)
+k_nl_refresh_unpack(int axis, double* __restrict__ rx, double* __restrict__ ry, double* __restrict__ rz,
+                    const int* __restrict__ idxM, const int* __restrict__ idxP, const int* __restrict__ cnt,
+                    const double* __restrict__ bufM, const double* __restrict__ bufP)
+{
+   const int d = blockIdx.y;
+   const int n = cnt[C_RECV0 + 2 * axis + d];
+   const int* idx = d ? idxP : idxM;
+   const double* in = d ? bufP : bufM;
+   for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x)
+   {
+      const int i = idx[k];
+      rx[i] = in[3 * (long)k + 0]; ry[i] = in[3 * (long)k + 1]; rz[i] = in[3 * (long)k + 2];
+   }
+}
+
+// ------------------------------------------------------------------ host side
+static int nlAllocate(ComdDev* d)
+{
+   // expected neighbours inside the list radius from the mean density of the local domain
+   const DevGeom& g = d->g;
+   double vol = 1.0;
+   for (int a = 0; a < 3; ++a) vol *= (g.lMax[a] - g.lMin[a]);
+   const int nLocal = d->hCnt[C_NLOCAL] > 0 ? d->hCnt[C_NLOCAL] : d->approxAtoms;
+   const double rl = d->cutoff + d->skin;
+   const double expect = 4.0 / 3.0 * 3.14159265358979323846 * rl * rl * rl * (double)nLocal / vol;
+   int stride = (int)(expect * 1.35) + 16;
+   stride = (stride + NL_G - 1) / NL_G * NL_G;
+   const long rows = d->cap;
+   if (d->nlList && d->nlStride >= stride && d->nlRows >= rows) return COMD_OK;
+   if (d->nlList) { cudaFree(d->nlList); cudaFree(d->nlCount); for (int k = 0; k < 3; ++k) cudaFree(d->nlLastR[k]); }
+   d->nlList = nullptr;
+   CUDA_TRY(cudaMalloc(&d->nlList, (size_t)rows * stride * sizeof(int)));
+   CUDA_TRY(cudaMalloc(&d->nlCount, rows * sizeof(int)));
+   CUDA_TRY(cudaMemset(d->nlCount, 0, rows * sizeof(int)));
+   for (int k = 0; k < 3; ++k) CUDA_TRY(cudaMalloc(&d->nlLastR[k], rows * sizeof(double)));
+   d->nlStride = stride; d->nlRows = rows;
+   return COMD_OK;
+}
+
+int comdNeighborBuildIfNeeded(ComdDev* d)
+{
+   if (!d->useNL || d->nlValid) return COMD_OK;
+   const double rl = d->cutoff + d->skin;
+   for (int a = 0; a < 3; ++a)
+      if (d->hostGeom.boxSize[a] < rl)
+      { comdSetError("neighbour list: cell size %g < cutoff + skin %g on axis %d (size the link cells on cutoff+skin, CoMD.c:257-268)",
+                     d->hostGeom.boxSize[a], rl, a); return COMD_E_ARG; }
+   int rc = nlAllocate(d);
+   if (rc != COMD_OK) return rc;
+   cudaStream_t s = d->stream;
+   CUDA_TRY(cudaMemsetAsync(d->nlStat, 0, 2 * sizeof(unsigned long long), s));
+   const int n = d->approxAtoms > 0 ? d->approxAtoms : (int)d->cap;
+   k_nl_build<<<gridFor((n + 3) / 4, 8, 148 * 8), 256, 0, s>>>(d->g, rl * rl, d->A.r[0], d->A.r[1], d->A.r[2], d->A.cell, d->cellType,
+      d->cellStart, d->cnt, d->nlList, d->nlCount, d->nlStride, d->nlRows, d->nlLastR[0], d->nlLastR[1], d->nlLastR[2], d->nlStat);
+   LAUNCH_CHECK(d);
+   d->nlValid = 1;
+   d->nlBuilds++;
+   return COMD_OK;
+}
+
+int comdNeighborAfterSort(ComdDev* d)
+{
+   IdxLists L;
+   for (int f = 0; f < 6; ++f) { L.p[f] = d->sendIdx[f]; L.p[6 + f] = d->recvIdx[f]; }
+   dim3 grid(64, 12);
+   k_nl_map_idx<<<grid, 256, 0, d->stream>>>(L, d->poolToSorted, d->cnt); LAUNCH_CHECK(d);
+   return COMD_OK;
+}
+
+// redistributeAtomsGpuNL (timestep.c:278-354): when no local atom has moved more than skin/2 the
+// atoms stay where they are in memory and only the ghost positions are renewed (three axis
+// phases, same atoms and order as the last full exchange); otherwise the caller re-bins.
+int comdNeighborRefreshOrRebuild(ComdDev* d, int* didRefresh)
+{
+   cudaStream_t s = d->stream;
+   *didRefresh = 0;
+   CUDA_TRY(cudaMemsetAsync(d->cnt + C_NLREBUILD, 0, sizeof(int), s));
+   const double h = 0.5 * d->skin;
+   k_nl_check<<<gridFor(d->approxAtoms, 256, 148 * 8), 256, 0, s>>>(h * h, d->A.r[0], d->A.r[1], d->A.r[2],
+      d->nlLastR[0], d->nlLastR[1], d->nlLastR[2], d->A.cell, d->cellType, d->cnt); LAUNCH_CHECK(d);
+   CUDA_TRY(cudaMemcpyAsync(d->hCnt + C_NLREBUILD, d->cnt + C_NLREBUILD, sizeof(int), cudaMemcpyDeviceToHost, s));
+   CUDA_TRY(cudaStreamSynchronize(s));
+   int flag = d->hCnt[C_NLREBUILD];
+   int rc = comdAllreduceMaxFlag(d, &flag);
+   if (rc != COMD_OK) return rc;
+   if (flag) return COMD_OK;                       // caller runs the full re-bin + exchange
+   for (int ax = 0; ax < 3; ++ax)
+   {
+      const int fM = 2 * ax, fP = fM + 1;
+      dim3 grid(148, 2);
+      k_nl_refresh_pack<<<grid, 256, 0, s>>>(ax, d->A.r[0], d->A.r[1], d->A.r[2], d->sendIdx[fM], d->sendIdx[fP], d->cnt,
+         d->sendBuf[0], d->sendBuf[1], d->shift[fM][0], d->shift[fM][1], d->shift[fM][2],
+         d->shift[fP][0], d->shift[fP][1], d->shift[fP][2]); LAUNCH_CHECK(d);
+      rc = comdExchangeRefreshPhase(d, ax);
+      if (rc != COMD_OK) return rc;
+      k_nl_refresh_unpack<<<grid, 256, 0, s>>>(ax, d->A.r[0], d->A.r[1], d->A.r[2], d->recvIdx[fM], d->recvIdx[fP], d->cnt,
+         d->recvBuf[0], d->recvBuf[1]); LAUNCH_CHECK(d);
+   }
+   d->nlRefreshes++;
+   *didRefresh = 1;
+   return COMD_OK;
+}
 
 extern "C" int comd_dev_set_neighbor_list(ComdDev* d, int useNeighborList, double skinDistance)
 {
-   if (!d) return COMD_E_ARG;
-   if (useNeighborList) { comdSetError("comd_dev_set_neighbor_list: neighbour-list path not available in this build"); return COMD_E_STATE; }
-   d->useNL = 0; d->skin = skinDistance;
+   if (!d || skinDistance < 0.0) { comdSetError("comd_dev_set_neighbor_list: bad argument"); return COMD_E_ARG; }
+   d->useNL = useNeighborList ? 1 : 0;
+   d->skin = skinDistance;
+   d->nlValid = 0;
    return COMD_OK;
 }
 
 extern "C" int comd_dev_neighbor_stats(ComdDev* d, long* nPairsStored, int* maxPerAtom, int* nBuilds)
 {
    if (!d) return COMD_E_ARG;
-   if (nPairsStored) *nPairsStored = 0;
-   if (maxPerAtom) *maxPerAtom = 0;
+   CUDA_TRY(cudaSetDevice(d->device));
+   unsigned long long st[2] = { 0, 0 };
+   CUDA_TRY(cudaStreamSynchronize(d->stream));
+   CUDA_TRY(cudaMemcpy(st, d->nlStat, sizeof st, cudaMemcpyDeviceToHost));
+   if (nPairsStored) *nPairsStored = (long)st[0];
+   if (maxPerAtom) *maxPerAtom = (int)st[1];
    if (nBuilds) *nBuilds = d->nlBuilds;
    return COMD_OK;
 }

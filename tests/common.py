@@ -23,12 +23,14 @@ def oracle_sim(pot, n, delta=0.0, temperature=600.0, skin=0.1, nxyz=None, lj_cut
                      lj_cut_mult=lj_cut_mult)
 
 
-def device_for(orc, nxyz, capacity_factor=3.0, proc_grid=(1, 1, 1), proc_coord=(0, 0, 0)):
-    """A device context with the link cells sized on the bare cutoff, potential taken from the oracle."""
+def device_for(orc, nxyz, capacity_factor=3.0, proc_grid=(1, 1, 1), proc_coord=(0, 0, 0), nl_skin=None):
+    """A device context with the link cells sized on the bare cutoff (on cutoff + skin with the
+    neighbour-list path, CoMD.c:257-268), potential taken from the oracle."""
     pot = orc.potential()
     lat = pot["lat"]
     gext = [nxyz[0] * lat, nxyz[1] * lat, nxyz[2] * lat]
-    geom = pycomd.make_geometry(gext, pot["cutoff"], proc_grid, proc_coord)
+    skin = pot["cutoff"] * nl_skin if nl_skin is not None else 0.0
+    geom = pycomd.make_geometry(gext, pot["cutoff"] + skin, proc_grid, proc_coord)
     n_atoms = 4 * nxyz[0] * nxyz[1] * nxyz[2]
     dev = pycomd.Device(geom, int(n_atoms * capacity_factor) + 16384)
     dev.set_mass(pot["mass"])
@@ -36,6 +38,8 @@ def device_for(orc, nxyz, capacity_factor=3.0, proc_grid=(1, 1, 1), proc_coord=(
         dev.set_lj(LJ_SIGMA, LJ_EPS, pot["cutoff"])
     else:
         dev.set_eam(pot["cutoff"], orc.table(0), orc.table(1), orc.table(2))
+    if nl_skin is not None:
+        dev.set_neighbor_list(True, skin)
     return dev, geom
 
 

@@ -293,3 +293,71 @@ def test_tiled_kernels_match_thread_atom_kernels(kind, tx):
         dev.close()
     assert rel_err(res[1]["f"], res[0]["f"]) <= 1e-13
     assert rel_err(res[1]["U"], res[0]["U"]) <= 1e-13
+
+
+# ---------------------------------------------------------------- neighbour-list path
+@pytest.mark.parametrize("kind", list(KINDS))
+def test_neighbor_list_step0_forces(kind):
+    n = 8
+    orc = oracle_sim(KINDS[kind], n, delta=0.1, temperature=600.0)
+    a = orc.atoms()
+    dev, _ = device_for(orc, (n, n, n), nl_skin=0.1)
+    dev.upload(a["gid"], a["r"], a["p"])
+    dev.compute_force()
+    d = by_gid(dev.download()); o = by_gid(a)
+    assert rel_err(d["f"], o["f"]) <= FORCE_TOL
+    assert rel_err(d["U"], o["U"] * u_scale(kind)) <= FORCE_TOL
+    st = dev.neighbor_stats()
+    assert st["builds"] == 1
+    # full list: every in-range pair is stored twice; brute-force count on the oracle's positions
+    L = n * orc.potential()["lat"]
+    rl = orc.potential()["cutoff"] * 1.1
+    r = o["r"]
+    pairs = 0
+    for i0 in range(0, len(r), 256):
+        dr = r[i0:i0 + 256, None, :] - r[None, :, :]
+        dr -= L * np.round(dr / L)
+        r2 = np.sum(dr * dr, axis=2)
+        pairs += int(np.sum(r2 <= rl * rl)) - len(r[i0:i0 + 256])
+    assert st["pairs"] == pairs
+    dev.close()
+
+
+@pytest.mark.parametrize("kind", list(KINDS))
+def test_neighbor_list_trajectory_matches_link_cell_path(kind):
+    """60 steps with refreshes and rebuilds: the list path and the link-cell path integrate the same
+    pair set, so energies agree to round-off; the list is rebuilt a few times, not every step."""
+    n = 8
+    orc = oracle_sim(KINDS[kind], n, delta=0.0, temperature=1200.0)
+    a = orc.atoms()
+    res = []
+    for skin in (None, 0.1):
+        dev, _ = device_for(orc, (n, n, n), nl_skin=skin)
+        dev.upload(a["gid"], a["r"], a["p"])
+        dev.compute_force()
+        dev.timestep(60, 1.0)
+        res.append((by_gid(dev.download()), dev.energy(), dev.neighbor_stats() if skin else None, dev.num_local()))
+        dev.close()
+    (d0, e0, _, n0), (d1, e1, st, n1) = res
+    assert n0 == n1 == len(a["gid"])
+    assert 1 < st["builds"] < 30
+    assert abs(sum(e1) - sum(e0)) <= 1e-9 * abs(sum(e0))
+    assert rel_err(d1["r"], d0["r"]) <= 1e-9
+    assert rel_err(d1["f"], d0["f"]) <= 1e-7
+
+
+def test_neighbor_list_energy_after_100_steps_vs_reference():
+    """C2 (EAM Cu_u6 20^3, 100 steps) through the list path against the reference's own trace (-m cpu_nl)."""
+    n = 20
+    orc = oracle_sim(po.POT_FUNCFL, n)
+    a = orc.atoms()
+    dev, _ = device_for(orc, (n, n, n), nl_skin=0.1)
+    dev.upload(a["gid"], a["r"], a["p"])
+    dev.compute_force()
+    dev.timestep(100, 1.0)
+    ep, ek = dev.energy()
+    g = np.load(os.path.join(GOLDEN_DIR, "trace_funcfl_n20.npz"))["trace"]
+    assert abs((ep + ek) - g[-1].sum()) <= ENERGY100_TOL * abs(g[-1].sum())
+    assert abs(ep - g[-1][0]) <= ENERGY100_TOL * abs(g[-1][0])
+    assert dev.num_local() == len(a["gid"])
+    dev.close()

@@ -13,7 +13,9 @@ pot = sys.argv[1]; n = int(sys.argv[2]); K = int(sys.argv[3]) if len(sys.argv) >
 steps = int(sys.argv[4]) if len(sys.argv) > 4 else 0
 potential = P.load(pot)
 lat = potential["lat"]
-geom = pycomd.make_geometry([n * lat] * 3, potential["cutoff"])
+NL = int(os.environ.get("COMD_NL", "0"))
+skin = 0.1 * potential["cutoff"] if NL else 0.0
+geom = pycomd.make_geometry([n * lat] * 3, potential["cutoff"] + skin)
 gid, r = P.fcc_block([n] * 3, lat, [0.0] * 3, [n * lat] * 3)
 p = P.maxwell_momenta(len(gid), potential["mass"], 600.0, seed=7)
 dev = pycomd.Device(geom, int(len(gid) * 1.6) + 65536)
@@ -22,6 +24,8 @@ if pot == "lj":
     dev.set_lj(potential["sigma"], potential["epsilon"], potential["cutoff"])
 else:
     dev.set_eam(potential["cutoff"], potential["phi"], potential["rho"], potential["f"])
+if NL:
+    dev.set_neighbor_list(True, skin)
 dev.upload(gid, r, p)
 dev.compute_force()
 dev.timestep(3, 1.0)          # thermalise a little: realistic hit patterns
@@ -35,4 +39,6 @@ print("%s n=%d atoms=%d force %.4f ms  (%.1f ps/atom)  E/atom %.9f" % (pot, n, l
 if steps:
     dev.timer_start(); dev.timestep(steps, 1.0); t = dev.timer_stop()
     print("step %.4f ms" % (t / steps))
+if NL:
+    print("neighbour list:", dev.neighbor_stats())
 dev.close()
