@@ -283,6 +283,7 @@ k_rank_gather(DevGeom geo, const int* __restrict__ tmpSrc, const int* __restrict
          const double x = src.r[0][s], y = src.r[1][s], z = src.r[2][s];
          dst.r[0][d] = x; dst.r[1][d] = y; dst.r[2][d] = z;
          dst.rf[d] = make_float4((float)(x - geo.lMin[0]), (float)(y - geo.lMin[1]), (float)(z - geo.lMin[2]), 0.f);
+         dst.rq[d] = make_double4(x, y, z, 0.0);
          dst.p[0][d] = src.p[0][s]; dst.p[1][d] = src.p[1][s]; dst.p[2][d] = src.p[2][s];
          dst.gid[d] = g; dst.spec[d] = src.spec[s]; dst.cell[d] = c;
          isLocal = cellType[c] & CT_LOCAL;
@@ -314,15 +315,17 @@ __global__ void __launch_bounds__(256)
 k_advance_position(double dt, double invMass, const int* __restrict__ cell, const unsigned char* __restrict__ cellType,
                    double* __restrict__ rx, double* __restrict__ ry, double* __restrict__ rz,
                    const double* __restrict__ px, const double* __restrict__ py, const double* __restrict__ pz,
-                   const int* __restrict__ cnt)
+                   const int* __restrict__ cnt, double4* __restrict__ rq)
 {
    const int n = cnt[C_NATOMS];
    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
    {
       if (!(cellType[cell[i]] & CT_LOCAL)) continue;
-      rx[i] = __dadd_rn(rx[i], __dmul_rn(__dmul_rn(dt, px[i]), invMass));
-      ry[i] = __dadd_rn(ry[i], __dmul_rn(__dmul_rn(dt, py[i]), invMass));
-      rz[i] = __dadd_rn(rz[i], __dmul_rn(__dmul_rn(dt, pz[i]), invMass));
+      const double x = __dadd_rn(rx[i], __dmul_rn(__dmul_rn(dt, px[i]), invMass));
+      const double y = __dadd_rn(ry[i], __dmul_rn(__dmul_rn(dt, py[i]), invMass));
+      const double z = __dadd_rn(rz[i], __dmul_rn(__dmul_rn(dt, pz[i]), invMass));
+      rx[i] = x; ry[i] = y; rz[i] = z;
+      rq[i] = make_double4(x, y, z, 0.0);
    }
 }
 // first half of a step in one pass: p += dt/2 f ; r += dt p / m
@@ -331,7 +334,7 @@ k_kick_drift(double dtHalf, double dt, double invMass, const int* __restrict__ c
              double* __restrict__ rx, double* __restrict__ ry, double* __restrict__ rz,
              double* __restrict__ px, double* __restrict__ py, double* __restrict__ pz,
              const double* __restrict__ fx, const double* __restrict__ fy, const double* __restrict__ fz,
-             const int* __restrict__ cnt)
+             const int* __restrict__ cnt, double4* __restrict__ rq)
 {
    const int n = cnt[C_NATOMS];
    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
@@ -341,9 +344,11 @@ k_kick_drift(double dtHalf, double dt, double invMass, const int* __restrict__ c
       const double b = __dadd_rn(py[i], __dmul_rn(dtHalf, fy[i]));
       const double c = __dadd_rn(pz[i], __dmul_rn(dtHalf, fz[i]));
       px[i] = a; py[i] = b; pz[i] = c;
-      rx[i] = __dadd_rn(rx[i], __dmul_rn(__dmul_rn(dt, a), invMass));
-      ry[i] = __dadd_rn(ry[i], __dmul_rn(__dmul_rn(dt, b), invMass));
-      rz[i] = __dadd_rn(rz[i], __dmul_rn(__dmul_rn(dt, c), invMass));
+      const double x = __dadd_rn(rx[i], __dmul_rn(__dmul_rn(dt, a), invMass));
+      const double y = __dadd_rn(ry[i], __dmul_rn(__dmul_rn(dt, b), invMass));
+      const double z = __dadd_rn(rz[i], __dmul_rn(__dmul_rn(dt, c), invMass));
+      rx[i] = x; ry[i] = y; rz[i] = z;
+      rq[i] = make_double4(x, y, z, 0.0);
    }
 }
 
@@ -410,12 +415,14 @@ static int allocAtoms(AtomArrays& a, long cap)
    CUDA_TRY(cudaMalloc(&a.cell, capP * sizeof(int)));
    CUDA_TRY(cudaMalloc(&a.rf, capP * sizeof(float4)));
    CUDA_TRY(cudaMemset(a.rf, 0, capP * sizeof(float4)));
+   CUDA_TRY(cudaMalloc(&a.rq, capP * sizeof(double4)));
+   CUDA_TRY(cudaMemset(a.rq, 0, capP * sizeof(double4)));
    return COMD_OK;
 }
 static void freeAtoms(AtomArrays& a)
 {
    for (int k = 0; k < 3; ++k) { cudaFree(a.r[k]); cudaFree(a.p[k]); }
-   cudaFree(a.gid); cudaFree(a.spec); cudaFree(a.cell); cudaFree(a.rf);
+   cudaFree(a.gid); cudaFree(a.spec); cudaFree(a.cell); cudaFree(a.rf); cudaFree(a.rq);
 }
 
 extern "C" int comd_dev_create(ComdDev** out, int deviceId, const ComdGeometry* geom, long atomCapacity)
@@ -552,8 +559,8 @@ extern "C" int comd_dev_destroy(ComdDev* d)
    cudaFree(d->e); cudaFree(d->cellStart); cudaFree(d->cellCount); cudaFree(d->cellFill); cudaFree(d->cellType);
    cudaFree(d->cellKey); cudaFree(d->shell); cudaFree(d->tmpSrc); cudaFree(d->tmpGid); cudaFree(d->tmpCell);
    cudaFree(d->scanBlock); cudaFree(d->cnt); cudaFreeHost(d->hCnt); cudaFree(d->redPartial); cudaFree(d->redOut);
-   cudaFreeHost(d->hRed); cudaFree(d->rhobar); cudaFree(d->dfEmbed); cudaFree(d->tabMem); cudaFree(d->tPRmem); cudaFree(d->runOff);
-   cudaFree(d->nlList); cudaFree(d->nlCount); cudaFree(d->poolToSorted); cudaFree(d->nlStat);
+   cudaFreeHost(d->hRed); cudaFree(d->rhobar); cudaFree(d->dfEmbed); cudaFree(d->tabMem); cudaFree(d->tPRmem); cudaFree(d->tW[0]); cudaFree(d->tW[1]); cudaFree(d->tDR); cudaFree(d->runOff);
+   cudaFree(d->nlList); cudaFree(d->nlCount); cudaFree(d->nlCountHit); cudaFree(d->poolToSorted); cudaFree(d->nlStat);
    for (int f = 0; f < 6; ++f) { cudaFree(d->sendIdx[f]); cudaFree(d->recvIdx[f]); }
    for (int k = 0; k < 2; ++k) { cudaFree(d->sendBuf[k]); cudaFree(d->recvBuf[k]); cudaFree(d->fpSend[k]); cudaFree(d->fpRecv[k]); }
    if (d->hStage) cudaFreeHost(d->hStage);
@@ -614,6 +621,35 @@ extern "C" int comd_dev_set_eam(ComdDev* d, double cutoff, const ComdTable* phi,
       CUDA_TRY(cudaMalloc(&d->tPRmem, h.size() * sizeof(double)));
       CUDA_TRY(cudaMemcpy(d->tPRmem, h.data(), h.size() * sizeof(double), cudaMemcpyHostToDevice));
       d->tPR = d->tPRmem + 1;
+      // shifted copies: tW[0][k] = entry k-1, tW[1][k] = entry k; entries past n+1 repeat the last one
+      for (int c = 0; c < 2; ++c)
+      {
+         if (d->tW[c]) { cudaFree(d->tW[c]); d->tW[c] = nullptr; }
+         const int len = n + 8;
+         std::vector<double> w(2 * (size_t)len);
+         for (int k = 0; k < len; ++k)
+         {
+            int e = k - 1 + c; if (e > n + 1) e = n + 1;
+            w[2 * k] = phi->values[e]; w[2 * k + 1] = rho->values[e];
+         }
+         CUDA_TRY(cudaMalloc(&d->tW[c], w.size() * sizeof(double)));
+         CUDA_TRY(cudaMemcpy(d->tW[c], w.data(), w.size() * sizeof(double), cudaMemcpyHostToDevice));
+      }
+   }
+   {  // pass-3 records: g1 = T[i+1]-T[i-1], q = (T[i+2]-T[i]) - g1, the two differences interpolate()
+      // (eam.c:573-578) forms for the derivative, in the same IEEE operations
+      if (d->tDR) { cudaFree(d->tDR); d->tDR = nullptr; }
+      const int n = rho->n;
+      std::vector<double> w(2 * (size_t)(n + 2));
+      for (int i = 0; i <= n; ++i)
+      {
+         const double tm = rho->values[i - 1], t0 = rho->values[i], t1 = rho->values[i + 1];
+         const double t2 = rho->values[i + 2 > n + 1 ? n + 1 : i + 2];
+         const double g1 = t1 - tm, g2 = t2 - t0;
+         w[2 * i] = g1; w[2 * i + 1] = g2 - g1;
+      }
+      CUDA_TRY(cudaMalloc(&d->tDR, w.size() * sizeof(double)));
+      CUDA_TRY(cudaMemcpy(d->tDR, w.data(), w.size() * sizeof(double), cudaMemcpyHostToDevice));
    }
    d->potKind = 2; d->cutoff = cutoff;
    return COMD_OK;
@@ -837,7 +873,7 @@ extern "C" int comd_dev_advance_position(ComdDev* d, double dt)
    if (!d) return COMD_E_ARG;
    CUDA_TRY(cudaSetDevice(d->device));
    k_advance_position<<<gridFor(d->approxAtoms, 256), 256, 0, d->stream>>>(dt, 1.0 / d->mass, d->A.cell, d->cellType,
-      d->A.r[0], d->A.r[1], d->A.r[2], d->A.p[0], d->A.p[1], d->A.p[2], d->cnt); LAUNCH_CHECK(d);
+      d->A.r[0], d->A.r[1], d->A.r[2], d->A.p[0], d->A.p[1], d->A.p[2], d->cnt, d->A.rq); LAUNCH_CHECK(d);
    d->posDirty = 1;
    return COMD_OK;
 }
@@ -905,7 +941,7 @@ extern "C" int comd_dev_timestep(ComdDev* d, int nSteps, double dt)
    for (int it = 0; it < nSteps; ++it)
    {
       k_kick_drift<<<gridFor(d->approxAtoms, 256), 256, 0, d->stream>>>(0.5 * dt, dt, 1.0 / d->mass, d->A.cell, d->cellType,
-         d->A.r[0], d->A.r[1], d->A.r[2], d->A.p[0], d->A.p[1], d->A.p[2], d->f[0], d->f[1], d->f[2], d->cnt); LAUNCH_CHECK(d);
+         d->A.r[0], d->A.r[1], d->A.r[2], d->A.p[0], d->A.p[1], d->A.p[2], d->f[0], d->f[1], d->f[2], d->cnt, d->A.rq); LAUNCH_CHECK(d);
       d->posDirty = 1;
       int rc = comd_dev_redistribute(d);
       if (rc != COMD_OK) return rc;

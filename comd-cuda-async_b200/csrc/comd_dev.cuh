@@ -62,6 +62,7 @@ struct AtomArrays
    double *r[3], *p[3];
    int *gid, *spec, *cell;
    float4 *rf;                  // FP32 shadow of r relative to localMin (filter stage of the force tiles)
+   double4 *rq;                 // gather copy {x, y, z, F'(rho)}: one 32-byte sector per neighbour visit (list kernels)
 };
 
 struct ComdDev
@@ -99,11 +100,15 @@ struct ComdDev
    DevTable tPhi, tRho, tF;
    double *tabMem;
    double2 *tPRmem, *tPR;                // interleaved {phi,rho} when both tables share one grid (entry 0), else NULL
+   double2 *tW[2];                       // two copies of the interleaved table, the second shifted by one entry: the 64-byte
+                                         // window [i-1, i+2] of any lookup is 32-byte aligned in one of them (two 256-bit loads)
+   double2 *tDR;                         // pass 3: {g1, g2-g1} of rho per interval (one 128-bit load), entry 0
    double *rhobar, *dfEmbed;
    // neighbour list
    int useNL; double skin;
    int *nlList; int *nlCount; int nlStride; int nlMax; double* nlLastR[3]; int nlBuilds; int nlValid;
    long nlRows;                 // rows allocated in nlList
+   int *nlCountHit;             // per atom: list prefix that held every in-cutoff entry in the last pass 1
    int nlRefreshes;             // steps served by a ghost refresh instead of a rebuild
    unsigned long long* nlStat;  // device: [0] stored pairs, [1] max per atom
    // ghost refresh between rebuilds: per face, sorted-array index of every atom sent / received by the

@@ -218,7 +218,7 @@ k_fp_pack(DevGeom g, int axis, const int* __restrict__ runTab, int runStride, co
 __global__ void __launch_bounds__(256)
 k_fp_unpack(DevGeom g, int axis, const int* __restrict__ runTab, int runStride, double* __restrict__ dfEmbed,
             const double* __restrict__ bufFromM, const double* __restrict__ bufFromP,
-            const int* __restrict__ nFromM, const int* __restrict__ nFromP, int* __restrict__ cnt)
+            const int* __restrict__ nFromM, const int* __restrict__ nFromP, int* __restrict__ cnt, double4* __restrict__ rq)
 {
    const int d = blockIdx.y, face = 2 * axis + d;
    const FpFace F = fpFace(g, face, 1);
@@ -231,7 +231,9 @@ k_fp_unpack(DevGeom g, int axis, const int* __restrict__ runTab, int runStride, 
    for (int m = blockIdx.x * blockDim.x + threadIdx.x; m < total; m += gridDim.x * blockDim.x)
    {
       const int k = fpLocate(runOff, F.nRuns, m);
-      dfEmbed[runStart[k] + (m - runOff[k])] = in[m];
+      const int a = runStart[k] + (m - runOff[k]);
+      dfEmbed[a] = in[m];
+      if (rq) rq[a].w = in[m];
    }
 }
 
@@ -250,7 +252,7 @@ int comdFprimeHalo(ComdDev* d)
       int rc = comdExchangeFprimePhase(d, ax);
       if (rc != COMD_OK) return rc;
       k_fp_unpack<<<grid, 256, 0, s>>>(g, ax, d->runOff, runStride, d->dfEmbed, d->fpRecv[0], d->fpRecv[1],
-                                       d->cnt + C_FPGOT0 + 2 * ax, d->cnt + C_FPGOT0 + 2 * ax + 1, d->cnt); LAUNCH_CHECK(d);
+                                       d->cnt + C_FPGOT0 + 2 * ax, d->cnt + C_FPGOT0 + 2 * ax + 1, d->cnt, d->useNL ? d->A.rq : nullptr); LAUNCH_CHECK(d);
    }
    return COMD_OK;
 }
@@ -262,7 +264,7 @@ int comdForceEAM(ComdDev* d)
    if (d->useNL || d->optForceVariant == 1)
    {
       PairParams Q = {};
-      Q.rc2 = rc2; Q.tPhi = d->tPhi; Q.tRho = d->tRho; Q.tF = d->tF; Q.tPR = d->tPR;
+      Q.rc2 = rc2; Q.tPhi = d->tPhi; Q.tRho = d->tRho; Q.tF = d->tF; Q.tPR = d->tPR; Q.tW0 = d->tPR ? d->tW[0] : nullptr; Q.tW1 = d->tW[1]; Q.tDR = d->tDR;
       int rc = d->useNL ? launchForceNL<PK_EAM1>(d, Q, nullptr) : launchForceTile<PK_EAM1>(d, Q, nullptr);
       if (rc != COMD_OK) return rc;
       rc = comdFprimeHalo(d);

@@ -60,6 +60,8 @@ struct PairParams
    // EAM
    DevTable tPhi, tRho, tF;
    const double2* tPR;                // interleaved {phi,rho} (same grid), entry 0; valid [-1, n+1]
+   const double2* tW0; const double2* tW1;   // shifted copies of tPR for 256-bit window loads (comd_dev.cuh), or NULL
+   const double2* tDR;                // pass 3: {g1, g2-g1} of rho per interval
 };
 
 // ---- PTX helpers: mbarrier + 1-D bulk copy (TMA engine, UBLKCP in SASS) -----------------
@@ -84,6 +86,12 @@ __device__ __forceinline__ void bulkG2S(void* dst, const void* src, unsigned byt
 {
    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                 ::"r"(smemAddr(dst)), "l"(src), "r"(bytes), "r"(smemAddr(bar)) : "memory");
+}
+
+// one 256-bit read-only load (LDG.E.256 on sm_100a): two adjacent double2, 32-byte aligned
+__device__ __forceinline__ void ldg256(const double2* p, double2& a, double2& b)
+{
+   asm volatile("ld.global.nc.v4.f64 {%0, %1, %2, %3}, [%4];" : "=d"(a.x), "=d"(a.y), "=d"(b.x), "=d"(b.y) : "l"(p));
 }
 
 // interpolate() of eam.c:557-579 on four already-loaded stencil values
@@ -137,7 +145,18 @@ __device__ __forceinline__ void pairEval(const PairParams& P, double dx, double 
       const double rinv = rsqrt(r2);
       const double r = r2 * rinv;
       double phi, dphi, rho;
-      if (P.tPR)
+      if (P.tW0)
+      {
+         double t;
+         const int ii = tableIndex(P.tPhi, r, t);
+         const double2* v = ((ii & 1) ? P.tW1 : P.tW0) + (ii & ~1);          // entries ii-1 .. ii+2, 32-byte aligned
+         double2 vm, v0, v1, v2;
+         ldg256(v, vm, v0); ldg256(v + 2, v1, v2);
+         interpValue(vm.x, v0.x, v1.x, t, phi);
+         interpDeriv(vm.x, v0.x, v1.x, v2.x, t, P.tPhi.invDx, dphi);
+         interpValue(vm.y, v0.y, v1.y, t, rho);
+      }
+      else if (P.tPR)
       {
          double t;
          const int ii = tableIndex(P.tPhi, r, t);
@@ -164,9 +183,17 @@ __device__ __forceinline__ void pairEval(const PairParams& P, double dx, double 
       const double r = r2 * rinv;
       double t, drho;
       const int ii = tableIndex(P.tRho, r, t);
-      const double* __restrict__ v = P.tRho.v + ii;
-      const double tm = __ldg(v - 1), t0 = __ldg(v), t1 = __ldg(v + 1), t2 = __ldg(v + 2);
-      interpDeriv(tm, t0, t1, t2, t, P.tRho.invDx, drho);
+      if (P.tDR)
+      {
+         const double2 gq = __ldg(P.tDR + ii);
+         drho = 0.5 * (gq.x + t * gq.y) * P.tRho.invDx;
+      }
+      else
+      {
+         const double* __restrict__ v = P.tRho.v + ii;
+         const double tm = __ldg(v - 1), t0 = __ldg(v), t1 = __ldg(v + 1), t2 = __ldg(v + 2);
+         interpDeriv(tm, t0, t1, t2, t, P.tRho.invDx, drho);
+      }
       const double s = (dfi + dfj) * drho * rinv;
       acc[0] -= s * dx; acc[1] -= s * dy; acc[2] -= s * dz;
    }

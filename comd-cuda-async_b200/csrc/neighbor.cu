@@ -18,7 +18,7 @@
 
 // ---- build -------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
-k_nl_build(DevGeom g, double rl2,
+k_nl_build(DevGeom g, double rc2, double rl2,
            const double* __restrict__ rx, const double* __restrict__ ry, const double* __restrict__ rz,
            const int* __restrict__ cell, const unsigned char* __restrict__ cellType, const int* __restrict__ cellStart,
            int* __restrict__ cnt, int* __restrict__ list, int* __restrict__ count, int stride, long rows,
@@ -41,13 +41,18 @@ k_nl_build(DevGeom g, double rl2,
       if (act) { xi = rx[i]; yi = ry[i]; zi = rz[i]; }
       int nn = 0;
       int* row = list + (long)(act ? i : 0) * stride;
+      // two sweeps: pairs inside the cutoff first, the skin shell (rc, rc+skin] behind them, both
+      // in ascending index order -- the force kernels then meet rounds that are all hits followed
+      // by rounds that are all misses instead of a 70 % mixture in every round
       #pragma unroll 1
-      for (int r = 0; r < 9; ++r)
+      for (int r = 0; r < 18; ++r)
       {
+         const bool far = r >= 9;
+         const int rr = far ? r - 9 : r;
          int jb = 0, je = 0;
          if (act)
          {
-            const int rc = c + ((r % 3) - 1) * rowY + ((r / 3) - 1) * rowZ;
+            const int rc = c + ((rr % 3) - 1) * rowY + ((rr / 3) - 1) * rowZ;
             jb = cellStart[rc - 1]; je = cellStart[rc + 2];
          }
          const int maxlen = __reduce_max_sync(full, je - jb);
@@ -58,7 +63,8 @@ k_nl_build(DevGeom g, double rl2,
             if (j < je && j != i)
             {
                const double dx = xi - rx[j], dy = yi - ry[j], dz = zi - rz[j];
-               ok = dx * dx + dy * dy + dz * dz <= rl2;
+               const double r2 = dx * dx + dy * dy + dz * dz;
+               ok = far ? (r2 > rc2 && r2 <= rl2) : (r2 <= rc2);
             }
             const unsigned m = (__ballot_sync(full, ok) >> (g4 * NL_G)) & ((1u << NL_G) - 1u);
             const int pos = nn + __popc(m & ((1u << gl) - 1u));
@@ -131,7 +137,7 @@ k_nl_refresh_pack(int axis, const double* __restrict__ rx, const double* __restr
 __global__ void __launch_bounds__(256)
 k_nl_refresh_unpack(int axis, double* __restrict__ rx, double* __restrict__ ry, double* __restrict__ rz,
                     const int* __restrict__ idxM, const int* __restrict__ idxP, const int* __restrict__ cnt,
-                    const double* __restrict__ bufM, const double* __restrict__ bufP)
+                    const double* __restrict__ bufM, const double* __restrict__ bufP, double4* __restrict__ rq)
 {
    const int d = blockIdx.y;
    const int n = cnt[C_RECV0 + 2 * axis + d];
@@ -140,7 +146,9 @@ k_nl_refresh_unpack(int axis, double* __restrict__ rx, double* __restrict__ ry, 
    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x)
    {
       const int i = idx[k];
-      rx[i] = in[3 * (long)k + 0]; ry[i] = in[3 * (long)k + 1]; rz[i] = in[3 * (long)k + 2];
+      const double x = in[3 * (long)k + 0], y = in[3 * (long)k + 1], z = in[3 * (long)k + 2];
+      rx[i] = x; ry[i] = y; rz[i] = z;
+      rq[i] = make_double4(x, y, z, 0.0);
    }
 }
 
@@ -158,11 +166,13 @@ static int nlAllocate(ComdDev* d)
    stride = (stride + NL_G - 1) / NL_G * NL_G;
    const long rows = d->cap;
    if (d->nlList && d->nlStride >= stride && d->nlRows >= rows) return COMD_OK;
-   if (d->nlList) { cudaFree(d->nlList); cudaFree(d->nlCount); for (int k = 0; k < 3; ++k) cudaFree(d->nlLastR[k]); }
+   if (d->nlList) { cudaFree(d->nlList); cudaFree(d->nlCount); cudaFree(d->nlCountHit); for (int k = 0; k < 3; ++k) cudaFree(d->nlLastR[k]); }
    d->nlList = nullptr;
    CUDA_TRY(cudaMalloc(&d->nlList, (size_t)rows * stride * sizeof(int)));
    CUDA_TRY(cudaMalloc(&d->nlCount, rows * sizeof(int)));
    CUDA_TRY(cudaMemset(d->nlCount, 0, rows * sizeof(int)));
+   CUDA_TRY(cudaMalloc(&d->nlCountHit, rows * sizeof(int)));
+   CUDA_TRY(cudaMemset(d->nlCountHit, 0, rows * sizeof(int)));
    for (int k = 0; k < 3; ++k) CUDA_TRY(cudaMalloc(&d->nlLastR[k], rows * sizeof(double)));
    d->nlStride = stride; d->nlRows = rows;
    return COMD_OK;
@@ -181,7 +191,7 @@ int comdNeighborBuildIfNeeded(ComdDev* d)
    cudaStream_t s = d->stream;
    CUDA_TRY(cudaMemsetAsync(d->nlStat, 0, 2 * sizeof(unsigned long long), s));
    const int n = d->approxAtoms > 0 ? d->approxAtoms : (int)d->cap;
-   k_nl_build<<<gridFor((n + 3) / 4, 8, 148 * 8), 256, 0, s>>>(d->g, rl * rl, d->A.r[0], d->A.r[1], d->A.r[2], d->A.cell, d->cellType,
+   k_nl_build<<<gridFor((n + 3) / 4, 8, 148 * 8), 256, 0, s>>>(d->g, d->cutoff * d->cutoff, rl * rl, d->A.r[0], d->A.r[1], d->A.r[2], d->A.cell, d->cellType,
       d->cellStart, d->cnt, d->nlList, d->nlCount, d->nlStride, d->nlRows, d->nlLastR[0], d->nlLastR[1], d->nlLastR[2], d->nlStat);
    LAUNCH_CHECK(d);
    d->nlValid = 1;
@@ -225,7 +235,7 @@ int comdNeighborRefreshOrRebuild(ComdDev* d, int* didRefresh)
       rc = comdExchangeRefreshPhase(d, ax);
       if (rc != COMD_OK) return rc;
       k_nl_refresh_unpack<<<grid, 256, 0, s>>>(ax, d->A.r[0], d->A.r[1], d->A.r[2], d->recvIdx[fM], d->recvIdx[fP], d->cnt,
-         d->recvBuf[0], d->recvBuf[1]); LAUNCH_CHECK(d);
+         d->recvBuf[0], d->recvBuf[1], d->A.rq); LAUNCH_CHECK(d);
    }
    d->nlRefreshes++;
    *didRefresh = 1;
