@@ -1,0 +1,57 @@
+"""GPU: the CoMD-compatible C driver (host/CoMD.c -> C ABI -> sm_100a kernels) next to the
+reference's own executable (oracle/_ref/CoMD-ref, built from /root/reference's sources, -m cpu_nl)
+on the BASELINE configs C1 / C2: same command line, same printed energy trace."""
+import os
+import re
+import subprocess
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+PKG = os.path.join(ROOT, "comd-cuda-async_b200")
+REF = os.path.join(ROOT, "oracle", "_ref", "CoMD-ref")
+POTS = os.path.join(ROOT, "pots")
+LINE = re.compile(r"^\s+(\d+)\s+([0-9.]+)\s+(-?[0-9.]+)\s+(-?[0-9.]+)\s+([0-9.]+)\s+([0-9.]+)\s+([0-9.]+)\s+(\d+)\s*$")
+
+
+def trace(out):
+    rows = []
+    for ln in out.splitlines():
+        m = LINE.match(ln)
+        if m:
+            rows.append((int(m.group(1)), float(m.group(3)), float(m.group(4)), float(m.group(5)), int(m.group(8))))
+    return rows
+
+
+def run(exe, args, cwd):
+    res = subprocess.run([exe] + args, cwd=cwd, capture_output=True, text=True, timeout=600)
+    assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-2000:]
+    return res.stdout
+
+
+@pytest.mark.parametrize("flags,method", [([], "thread_atom"), (["-e"], "thread_atom"), (["-e"], "thread_atom_nl"), (["-e", "-t", "setfl"], "warp_atom_nl")])
+def test_driver_trace_matches_reference_executable(tmp_path, flags, method):
+    if not os.path.exists(REF):
+        pytest.skip("oracle/_ref/CoMD-ref not built (needs /root/reference at build time)")
+    subprocess.check_call(["make", "-s", "-C", PKG, "host"])
+    n = "12" if "setfl" in flags else "20"
+    common = ["-x", n, "-y", n, "-z", n, "-N", "100", "-n", "10", "-d", POTS] + flags
+    ours = trace(run(os.path.join(PKG, "CoMD-b200"), common + ["-m", method], tmp_path))
+    ref = trace(run(REF, common + ["-m", "cpu_nl"], tmp_path))
+    assert len(ours) == len(ref) == 11
+    for (s0, et0, eu0, ek0, n0), (s1, et1, eu1, ek1, n1) in zip(ours, ref):
+        assert s0 == s1 and n0 == n1 == 4 * int(n) ** 3
+        tol = 2e-12 if s0 == 0 else 1e-6                       # printed with 12 decimals; 1e-6 over 100 steps (north_star)
+        assert abs(et0 - et1) <= tol * abs(et1) + 1.5e-12, (s0, et0, et1)
+        assert abs(eu0 - eu1) <= tol * abs(eu1) + 1.5e-12, (s0, eu0, eu1)
+        assert abs(ek0 - ek1) <= max(tol, 1e-6 if s0 else 0) * abs(ek1) + 1.5e-12, (s0, ek0, ek1)
+
+
+def test_driver_async_flag_gives_the_same_trace(tmp_path):
+    subprocess.check_call(["make", "-s", "-C", PKG, "host"])
+    args = ["-x", "10", "-y", "10", "-z", "10", "-N", "30", "-n", "10", "-e", "-d", POTS]
+    a = trace(run(os.path.join(PKG, "CoMD-b200"), args, tmp_path))
+    b = trace(run(os.path.join(PKG, "CoMD-b200"), args + ["-a", "1"], tmp_path))
+    assert a == b and len(a) == 4

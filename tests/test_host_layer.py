@@ -1,0 +1,95 @@
+"""CPU: the plain-C host layer (comd-cuda-async_b200/host/) against the oracle -- initial state
+(lattice, gid-seeded momenta at exactly T, random displacements), link-cell geometry and box
+numbering, the option table, and the 2-rank shared-memory collectives (fork, no MPI, no GPU)."""
+import os
+import struct
+import subprocess
+
+import numpy as np
+import pytest
+
+import pyoracle as po
+from common import oracle_sim
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+PKG = os.path.join(ROOT, "comd-cuda-async_b200")
+POTS = os.path.join(ROOT, "pots")
+
+
+@pytest.fixture(scope="module")
+def tools():
+    subprocess.check_call(["make", "-s", "-C", PKG, "host"])
+    return {k: os.path.join(PKG, k) for k in ("host_dump", "comd-launch", "CoMD-b200")}
+
+
+def read_dump(path):
+    with open(path, "rb") as fh:
+        raw = fh.read()
+    n, n_global, gx, gy, gz, n_boxes = struct.unpack_from("6i", raw, 0)
+    dh = np.frombuffer(raw, np.float64, 15, 24)
+    off = 24 + 15 * 8
+    gid = np.frombuffer(raw, np.int32, n, off); off += 4 * n
+    box = np.frombuffer(raw, np.int32, n, off); off += 4 * n
+    r = np.frombuffer(raw, np.float64, 3 * n, off).reshape(3, n).T; off += 24 * n
+    p = np.frombuffer(raw, np.float64, 3 * n, off).reshape(3, n).T
+    return dict(n=n, n_global=n_global, grid=(gx, gy, gz), n_boxes=n_boxes, cutoff=dh[0], mass=dh[1], lat=dh[2], box_size=dh[3:6],
+                inv_box_size=dh[6:9], local_min=dh[9:12], local_max=dh[12:15], gid=gid, box=box, r=r, p=p)
+
+
+FLAGS = {"lj": [], "funcfl": ["-e"], "setfl": ["-e", "-t", "setfl"]}
+KINDS = {"lj": po.POT_LJ, "funcfl": po.POT_FUNCFL, "setfl": po.POT_SETFL}
+
+
+@pytest.mark.parametrize("kind", list(KINDS))
+def test_initial_state_is_bit_identical_to_the_oracle(tools, tmp_path, kind):
+    n = 7
+    out = str(tmp_path / "d.bin")
+    subprocess.check_call([tools["host_dump"], out, "-x", str(n), "-y", str(n), "-z", str(n), "-r", "0.07", "-T", "450", "-d", POTS] + FLAGS[kind],
+                          cwd=tmp_path, stdout=subprocess.DEVNULL)
+    d = read_dump(out)
+    orc = oracle_sim(KINDS[kind], n, delta=0.07, temperature=450.0, skin=0.0)
+    a = orc.atoms()
+    pot = orc.potential()
+    assert d["n"] == d["n_global"] == 4 * n ** 3 == len(a["gid"])
+    assert d["cutoff"] == pot["cutoff"] and d["mass"] == pot["mass"] and d["lat"] == pot["lat"]     # readers, unit conversion
+    g = orc.geometry()
+    assert tuple(g["grid"]) == d["grid"] and g["n_total_boxes"] == d["n_boxes"]
+    assert np.array_equal(g["inv_box_size"], d["inv_box_size"]) and np.array_equal(g["box_size"], d["box_size"])
+    o = np.argsort(a["gid"]); h = np.argsort(d["gid"])
+    assert np.array_equal(d["gid"][h], a["gid"][o])
+    assert np.array_equal(d["r"][h], a["r"][o])                   # lattice + gid-seeded displacement
+    assert np.array_equal(d["p"][h], a["p"][o])                   # gid-seeded momenta, COM removal, rescale to T: same sums, same order
+    assert np.array_equal(d["box"][h], a["box"][o])               # getBoxFromCoord / getBoxFromTuple
+
+
+def test_two_ranks_partition_the_same_lattice(tools, tmp_path):
+    out = str(tmp_path / "d.bin")
+    subprocess.check_call([tools["comd-launch"], "-n", "2", tools["host_dump"], out, "-x", "10", "-y", "6", "-z", "6", "-i", "2", "-r", "0.03",
+                           "-e", "-d", POTS], cwd=tmp_path, stdout=subprocess.DEVNULL, timeout=120)
+    parts = [read_dump("%s.%d" % (out, r)) for r in range(2)]
+    orc = po.Oracle(pot=po.POT_FUNCFL, nx=10, ny=6, nz=6, delta=0.03, temperature=600.0, skin=0.0)
+    a = orc.atoms()
+    gid = np.concatenate([p["gid"] for p in parts]); r = np.concatenate([p["r"] for p in parts]); mom = np.concatenate([p["p"] for p in parts])
+    assert parts[0]["n_global"] == parts[1]["n_global"] == len(a["gid"]) == len(gid)
+    o = np.argsort(a["gid"]); h = np.argsort(gid)
+    assert np.array_equal(gid[h], a["gid"][o])                    # every atom on exactly one rank
+    assert np.array_equal(r[h], a["r"][o])
+    # the centre-of-mass and temperature sums are reduced rank by rank here, box by box there: round-off only
+    assert np.max(np.abs(mom[h] - a["p"][o])) <= 1e-13 * np.max(np.abs(a["p"]))
+    for rank, p in enumerate(parts):                              # ownership = position inside the rank's brick
+        assert np.all(p["r"][:, 0] >= p["local_min"][0] - 0.03) and np.all(p["r"][:, 0] < p["local_max"][0] + 0.03)
+        assert p["local_min"][0] == rank * parts[0]["local_max"][0]
+
+
+def test_driver_refuses_to_run_without_a_gpu_and_keeps_the_option_table(tools, tmp_path, gpu_available):
+    res = subprocess.run([tools["CoMD-b200"], "--help"], cwd=tmp_path, capture_output=True, text=True)
+    assert res.returncode == 2
+    for opt in ("--potDir", "--potName", "--potType", "--doeam", "--nx", "--xproc", "--nSteps", "--printRate", "--dt", "--lat", "--temp",
+                "--delta", "--hilbert", "--skinDistance", "--method", "--gpuAsync", "--gpuProfile", "--ljInterpolation", "--spline",
+                "--usePairlist"):
+        assert opt in res.stdout, opt
+    res = subprocess.run([tools["CoMD-b200"], "-m", "cpu_nl", "-x", "6", "-y", "6", "-z", "6"], cwd=tmp_path, capture_output=True, text=True)
+    assert res.returncode != 0 and "no CPU force path" in res.stdout
+    if not gpu_available:
+        res = subprocess.run([tools["CoMD-b200"], "-x", "6", "-y", "6", "-z", "6"], cwd=tmp_path, capture_output=True, text=True)
+        assert res.returncode != 0 and "no CUDA device" in res.stderr      # fails loudly, no CPU fallback
