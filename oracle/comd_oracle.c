@@ -18,7 +18,7 @@
  *   - redistributeAtomsCpuNL, advanceVelocity/PositionCpu,
  *     kineticEnergy, timestep                                          timestep.c:48-197, 356-405
  *
- * Parity status: PINNED.  tests/test_oracle_vs_ref.py checks this file against the
+ * Parity status: PINNED.  tests/test_oracle.py checks this file against the
  * reference itself (oracle/_ref/libcomd_ref.so, built from the reference's own sources
  * by oracle/ref_build/Makefile) bit-for-bit: cell ids, RNG streams, initial r and p,
  * tables, per-atom f and U at step 0 and the energy trace over time steps; and against
