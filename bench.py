@@ -41,6 +41,8 @@ PROC_GRIDS = {1: (1, 1, 1), 2: (2, 1, 1), 4: (2, 2, 1), 8: (2, 2, 2)}
 FLOP_PER_ATOM_STEP = {"lj": 78 * 27 + 22, "setfl": 54 * (56 + 37) + 20 + 22, "funcfl": 42 * 93 + 42}
 HBM_B_PER_ATOM_STEP = {"lj": 96, "setfl": 192, "funcfl": 192}
 # the force kernels' share of that work (what roofline.achieved counts per force launch set)
+# DRAM bytes per atom per force evaluation measured by ncu (sum over the force kernels): (potential, list path?) -> B/atom
+NCU_DRAM_B_PER_ATOM_FORCE = {("setfl", 1): (412.36 + 59.84 + 422.44 + 20.15) * 1e6 / 864000.0}
 FORCE_FLOP_PER_ATOM = {"lj": 78 * 27, "setfl": 54 * (56 + 37) + 20, "funcfl": 42 * 93 + 20}
 
 
@@ -156,7 +158,7 @@ def main():
     ap.add_argument("--workload", default="eam_strong", choices=sorted(WORKLOADS))
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--neighbor-list", type=int, default=int(os.environ.get("COMD_NL", "0")),
+    ap.add_argument("--neighbor-list", type=int, default=int(os.environ.get("COMD_NL", "1")),
                     help="1: neighbour-list force path (skin 0.1*cutoff, mycommand.c:210), 0: link-cell path")
     args = ap.parse_args()
     pot, ncell, scaling, label = WORKLOADS[args.workload]
@@ -288,9 +290,11 @@ def main():
         "dtype": "f64", "data": "synthetic FCC Cu lattice (a=3.615 A), numpy-seeded Maxwell-Boltzmann momenta at 600 K, dt=1 fs",
         "config": {"workload": label, "atoms": n_global, "atoms_per_gpu": n_local, "proc_grid": "%dx%dx%d" % grid,
                    "cells_per_gpu": "%dx%dx%d" % tuple(geom.gridSize[:]), "parallelism": "3-D spatial domain decomposition, 1 rank/GPU",
+                   "force_path": "neighbour list (skin 0.1*cutoff, rebuilt when an atom moved > skin/2)" if args.neighbor_list else "link cells (re-binned every step)",
                    "l2": "working set %.0f MB per GPU > 126 MB L2 (no flush needed)" % (n_local * 200e-6) if n_local * 200 > 126e6
                          else "working set fits L2: small-config line, not the headline"},
-        "roofline": {"bound": "fp64", "kernel": "force (%s)" % ("k_lj_force" if pot == "lj" else "k_eam_pass1 + F' halo + k_eam_pass3"),
+        "roofline": {"bound": "fp64", "kernel": "force (%s)" % (("k_force_nl<LJ>" if pot == "lj" else "k_force_nl<EAM1> + F' halo + k_force_nl<EAM3>") if args.neighbor_list
+                                                                 else ("k_force_tile<LJ>" if pot == "lj" else "k_force_tile<EAM1> + F' halo + k_force_tile<EAM3>")),
                      "achieved": achieved_tf, "peak": fp64_peak, "unit": "TFLOP/s",
                      "frac": (achieved_tf / fp64_peak) if achieved_tf else None,
                      "peak_source": "DFMA microbenchmark run in this process (comd_dev_fp64_peak); MEASURED_PEAKS.json has no FP64 entry",
@@ -298,7 +302,9 @@ def main():
                      "step_frac_fp64": value / world * FLOP_PER_ATOM_STEP[pot] * 1e-12 / fp64_peak,
                      "hbm": {"achieved": hbm_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": hbm_gbs / peaks["hbm_gbs"],
                              "peak_source": peaks["source"], "algorithmic_bytes_per_atom_step": HBM_B_PER_ATOM_STEP[pot]},
-                     "traffic": None},
+                     "traffic": (NCU_DRAM_B_PER_ATOM_FORCE.get((pot, int(bool(args.neighbor_list)))) or 0) * n_local or None,
+                     "traffic_source": "dram__bytes_read+write per force evaluation from ncu --set full at 864k atoms (profiles/r1_v3_nl_ncu_full_eam60.txt), scaled per atom"
+                                       if NCU_DRAM_B_PER_ATOM_FORCE.get((pot, int(bool(args.neighbor_list)))) else None},
         "e2e": {"value": n_global * args.e2e_steps / t_e2e, "unit": "atom-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "steps": args.e2e_steps},
         "gpu_launches": int(l1 - l0),
