@@ -564,6 +564,7 @@ extern "C" int comd_dev_destroy(ComdDev* d)
    for (int f = 0; f < 6; ++f) { cudaFree(d->sendIdx[f]); cudaFree(d->recvIdx[f]); }
    for (int k = 0; k < 2; ++k) { cudaFree(d->sendBuf[k]); cudaFree(d->recvBuf[k]); cudaFree(d->fpSend[k]); cudaFree(d->fpRecv[k]); }
    if (d->hStage) cudaFreeHost(d->hStage);
+   cudaFree(d->rowTab); cudaFree(d->e2eScratch);
    for (int k = 0; k < 256; ++k) cudaEventDestroy(d->evForce[k]);
    cudaEventDestroy(d->evT0); cudaEventDestroy(d->evT1);
    cudaStreamDestroy(d->stream);
@@ -998,9 +999,90 @@ extern "C" int comd_dev_timer_stop(ComdDev* d, double* ms)
    return COMD_OK;
 }
 
+// ---- local atoms, compacted on the device -------------------------------------------------
+// Local atoms of one (y,z) row of cells are one contiguous run of the sorted arrays; an exclusive
+// scan over the ny*nz run lengths gives every run its place in a dense, ghost-free copy.
+__global__ void __launch_bounds__(1024)
+k_local_rows(DevGeom g, const int* __restrict__ cellStart, int* __restrict__ rowBeg, int* __restrict__ rowOff)
+{
+   __shared__ int warpSum[32];
+   __shared__ int carry;
+   const int nRows = g.n[1] * g.n[2];
+   const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+   if (t == 0) carry = 0;
+   __syncthreads();
+   for (int base = 0; base < nRows; base += 1024)
+   {
+      const int k = base + t;
+      int len = 0, b = 0;
+      if (k < nRows)
+      {
+         const int c0 = cellIndex(g, 0, k % g.n[1], k / g.n[1]);
+         b = cellStart[c0]; len = cellStart[c0 + g.n[0]] - b;
+      }
+      int incl = len;
+      #pragma unroll
+      for (int o = 1; o < 32; o <<= 1) { int u = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += u; }
+      if (lane == 31) warpSum[w] = incl;
+      __syncthreads();
+      if (w == 0)
+      {
+         int s = warpSum[lane], si = s;
+         #pragma unroll
+         for (int o = 1; o < 32; o <<= 1) { int u = __shfl_up_sync(0xffffffffu, si, o); if (lane >= o) si += u; }
+         warpSum[lane] = si - s;
+      }
+      __syncthreads();
+      const int excl = incl - len + warpSum[w] + carry;
+      if (k < nRows) { rowBeg[k] = b; rowOff[k] = excl; }
+      __syncthreads();
+      if (t == 1023) carry = excl + len;
+      __syncthreads();
+   }
+   if (t == 0) rowOff[nRows] = carry;
+}
+
+struct CompactArrays { const double* in[10]; double* out[10]; const int* gidIn; int* gidOut; };
+__global__ void __launch_bounds__(256)
+k_compact_local(CompactArrays A, const int* __restrict__ rowBeg, const int* __restrict__ rowOff, int nRows)
+{
+   for (int row = blockIdx.x; row < nRows; row += gridDim.x)
+   {
+      const int b = rowBeg[row], o = rowOff[row], len = rowOff[row + 1] - o;
+      for (int t = threadIdx.x; t < len; t += blockDim.x)
+      {
+         #pragma unroll
+         for (int k = 0; k < 10; ++k) A.out[k][o + t] = A.in[k][b + t];
+         A.gidOut[o + t] = A.gidIn[b + t];
+      }
+   }
+}
+
+static bool isPinned(const void* p)
+{
+   cudaPointerAttributes at;
+   if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return false; }
+   return at.type == cudaMemoryTypeHost;
+}
+
+// pinned host memory for callers that want their step_host buffers copied without staging
+extern "C" int comd_host_alloc(void** p, size_t bytes)
+{
+   if (!p) return COMD_E_ARG;
+   CUDA_TRY(cudaMallocHost(p, bytes));
+   return COMD_OK;
+}
+extern "C" int comd_host_free(void* p)
+{
+   if (p) CUDA_TRY(cudaFreeHost(p));
+   return COMD_OK;
+}
+
 // End-to-end step through HOST buffers: one full timestep() whose inputs (gid, r, p, f at
-// time t) start in host memory and whose results (gid, r, p, f, U at t+dt, device order)
-// end there.  bench.py times this as `e2e`; staging goes through pinned memory.
+// time t) start in host memory and whose results (gid, r, p, f, U at t+dt, device order, local
+// atoms only) end there.  bench.py times this as `e2e`.  Buffers obtained from comd_host_alloc
+// (pinned) are copied directly; pageable ones go through a pinned staging area.  The ghost-free
+// result is compacted on the device, so only local atoms cross PCIe.
 extern "C" int comd_dev_step_host(ComdDev* d, int n, double dt,
                                   const int* gidIn, const double* rIn[3], const double* pIn[3], const double* fIn[3],
                                   int* nOut, int* gidOut, double* rOut[3], double* pOut[3], double* fOut[3], double* UOut,
@@ -1011,69 +1093,84 @@ extern "C" int comd_dev_step_host(ComdDev* d, int n, double dt,
    if (d->potKind == 0) { comdSetError("comd_dev_step_host: no potential set"); return COMD_E_STATE; }
    CUDA_TRY(cudaSetDevice(d->device));
    cudaStream_t s = d->stream;
-   // pinned staging: 10 doubles per atom (r,p,f + gid/U slots)
-   const long need = (long)d->cap * 11;
-   if (d->hStageDoubles < need)
-   {
-      if (d->hStage) cudaFreeHost(d->hStage);
-      CUDA_TRY(cudaMallocHost(&d->hStage, need * sizeof(double)));
-      d->hStageDoubles = need;
-   }
-   double* st = d->hStage;
    const long cap = d->cap;
    AtomArrays& A = d->A;
-   for (int k = 0; k < 3; ++k)
-   {
-      memcpy(st + (0 + k) * cap, rIn[k], n * sizeof(double));
-      memcpy(st + (3 + k) * cap, pIn[k], n * sizeof(double));
-      memcpy(st + (6 + k) * cap, fIn[k], n * sizeof(double));
-      CUDA_TRY(cudaMemcpyAsync(A.r[k], st + (0 + k) * cap, n * sizeof(double), cudaMemcpyHostToDevice, s));
-      CUDA_TRY(cudaMemcpyAsync(A.p[k], st + (3 + k) * cap, n * sizeof(double), cudaMemcpyHostToDevice, s));
-      CUDA_TRY(cudaMemcpyAsync(d->f[k], st + (6 + k) * cap, n * sizeof(double), cudaMemcpyHostToDevice, s));
+   const double* in[9] = { rIn[0], rIn[1], rIn[2], pIn[0], pIn[1], pIn[2], fIn[0], fIn[1], fIn[2] };
+   double* devIn[9] = { A.r[0], A.r[1], A.r[2], A.p[0], A.p[1], A.p[2], d->f[0], d->f[1], d->f[2] };
+   bool pinnedIn = isPinned(gidIn);
+   for (int k = 0; k < 9; ++k) pinnedIn = pinnedIn && isPinned(in[k]);
+   double* outPtr[10] = { rOut ? rOut[0] : nullptr, rOut ? rOut[1] : nullptr, rOut ? rOut[2] : nullptr,
+                          pOut ? pOut[0] : nullptr, pOut ? pOut[1] : nullptr, pOut ? pOut[2] : nullptr,
+                          fOut ? fOut[0] : nullptr, fOut ? fOut[1] : nullptr, fOut ? fOut[2] : nullptr, UOut };
+   bool pinnedOut = !gidOut || isPinned(gidOut);
+   for (int k = 0; k < 10; ++k) pinnedOut = pinnedOut && (!outPtr[k] || isPinned(outPtr[k]));
+   if (!pinnedIn || !pinnedOut)
+   {  // pinned staging: 11 slabs of `cap` doubles
+      const long need = cap * 11;
+      if (d->hStageDoubles < need)
+      {
+         if (d->hStage) cudaFreeHost(d->hStage);
+   cudaFree(d->rowTab); cudaFree(d->e2eScratch);
+         d->hStage = nullptr; d->hStageDoubles = 0;
+         CUDA_TRY(cudaMallocHost(&d->hStage, need * sizeof(double)));
+         d->hStageDoubles = need;
+      }
    }
-   memcpy(st + 9 * cap, gidIn, n * sizeof(int));
-   CUDA_TRY(cudaMemcpyAsync(A.gid, st + 9 * cap, n * sizeof(int), cudaMemcpyHostToDevice, s));
+   double* st = d->hStage;
+   // ---- inputs
+   for (int k = 0; k < 9; ++k)
+   {
+      const double* src = in[k];
+      if (!pinnedIn) { memcpy(st + k * cap, in[k], n * sizeof(double)); src = st + k * cap; }
+      CUDA_TRY(cudaMemcpyAsync(devIn[k], src, n * sizeof(double), cudaMemcpyHostToDevice, s));
+   }
+   {
+      const int* src = gidIn;
+      if (!pinnedIn) { memcpy(st + 9 * cap, gidIn, n * sizeof(int)); src = reinterpret_cast<const int*>(st + 9 * cap); }
+      CUDA_TRY(cudaMemcpyAsync(A.gid, src, n * sizeof(int), cudaMemcpyHostToDevice, s));
+   }
    CUDA_TRY(cudaMemsetAsync(A.spec, 0, n * sizeof(int), s));
    k_set_int<<<gridFor(n, 256), 256, 0, s>>>(A.cell, cellIndex(d->g, 0, 0, 0), n); LAUNCH_CHECK(d);
    k_set_int<<<1, 1, 0, s>>>(d->cnt + C_NATOMS, n, 1); LAUNCH_CHECK(d);
    d->approxAtoms = n; d->approxHasGhosts = 0;
+   d->nlValid = 0;                                 // new atoms: the list path must re-bin and rebuild
    int rc = comd_dev_timestep(d, 1, dt);
    if (rc != COMD_OK) return rc;
-   rc = comd_dev_energy(d, eLocal);          // syncs, refreshes hCnt
+   // ---- results: compact the local atoms on the device (B is free scratch after the sort)
+   const int nRows = d->g.n[1] * d->g.n[2];
+   if (!d->rowTab) CUDA_TRY(cudaMalloc(&d->rowTab, (2 * (size_t)nRows + 2) * sizeof(int)));
+   if (!d->e2eScratch) CUDA_TRY(cudaMalloc(&d->e2eScratch, (size_t)cap * 4 * sizeof(double)));
+   int* rowBeg = d->rowTab; int* rowOff = d->rowTab + nRows;
+   k_local_rows<<<1, 1024, 0, s>>>(d->g, d->cellStart, rowBeg, rowOff); LAUNCH_CHECK(d);
+   CompactArrays C;
+   AtomArrays& B = d->B;
+   const double* cin[10] = { d->A.r[0], d->A.r[1], d->A.r[2], d->A.p[0], d->A.p[1], d->A.p[2], d->f[0], d->f[1], d->f[2], d->e };
+   double* cout[10] = { B.r[0], B.r[1], B.r[2], B.p[0], B.p[1], B.p[2], d->e2eScratch, d->e2eScratch + cap, d->e2eScratch + 2 * cap,
+                        d->e2eScratch + 3 * cap };
+   for (int k = 0; k < 10; ++k) { C.in[k] = cin[k]; C.out[k] = cout[k]; }
+   C.gidIn = d->A.gid; C.gidOut = B.gid;
+   k_compact_local<<<gridFor(nRows, 1, 148 * 8), 256, 0, s>>>(C, rowBeg, rowOff, nRows); LAUNCH_CHECK(d);
+   rc = comd_dev_energy(d, eLocal);                // syncs, refreshes hCnt
    if (rc != COMD_OK) return rc;
-   // results: local atoms are interleaved with ghosts in device order; bring everything
-   // back through pinned staging and compact on the host.
-   const int nAll = d->hCnt[C_NATOMS];
-   std::vector<int> cell(nAll);
-   std::vector<unsigned char> ct(d->g.nCells);
-   CUDA_TRY(cudaMemcpyAsync(st + 9 * cap, d->A.gid, nAll * sizeof(int), cudaMemcpyDeviceToHost, s));
-   for (int k = 0; k < 3; ++k)
-   {
-      CUDA_TRY(cudaMemcpyAsync(st + (0 + k) * cap, d->A.r[k], nAll * sizeof(double), cudaMemcpyDeviceToHost, s));
-      CUDA_TRY(cudaMemcpyAsync(st + (3 + k) * cap, d->A.p[k], nAll * sizeof(double), cudaMemcpyDeviceToHost, s));
-      CUDA_TRY(cudaMemcpyAsync(st + (6 + k) * cap, d->f[k], nAll * sizeof(double), cudaMemcpyDeviceToHost, s));
-   }
-   CUDA_TRY(cudaMemcpyAsync(st + 10 * cap, d->e, nAll * sizeof(double), cudaMemcpyDeviceToHost, s));
-   CUDA_TRY(cudaMemcpyAsync(cell.data(), d->A.cell, nAll * sizeof(int), cudaMemcpyDeviceToHost, s));
-   CUDA_TRY(cudaMemcpyAsync(ct.data(), d->cellType, d->g.nCells, cudaMemcpyDeviceToHost, s));
-   CUDA_TRY(cudaStreamSynchronize(s));
-   const int* gAll = reinterpret_cast<const int*>(st + 9 * cap);
-   int m = 0;
-   for (int i = 0; i < nAll; ++i)
-   {
-      if (!(ct[cell[i]] & CT_LOCAL)) continue;
-      if (m >= n + (int)(d->cap - n)) break;
-      if (gidOut) gidOut[m] = gAll[i];
-      for (int k = 0; k < 3; ++k)
-      {
-         if (rOut) rOut[k][m] = st[(0 + k) * cap + i];
-         if (pOut) pOut[k][m] = st[(3 + k) * cap + i];
-         if (fOut) fOut[k][m] = st[(6 + k) * cap + i];
-      }
-      if (UOut) UOut[m] = st[10 * cap + i];
-      ++m;
-   }
+   const int m = d->hCnt[C_NLOCAL];
    if (nOut) *nOut = m;
+   for (int k = 0; k < 10; ++k)
+   {
+      if (!outPtr[k]) continue;
+      double* dst = pinnedOut ? outPtr[k] : st + k * cap;
+      CUDA_TRY(cudaMemcpyAsync(dst, cout[k], m * sizeof(double), cudaMemcpyDeviceToHost, s));
+   }
+   if (gidOut)
+   {
+      int* dst = pinnedOut ? gidOut : reinterpret_cast<int*>(st + 10 * cap);
+      CUDA_TRY(cudaMemcpyAsync(dst, B.gid, m * sizeof(int), cudaMemcpyDeviceToHost, s));
+   }
+   CUDA_TRY(cudaStreamSynchronize(s));
+   if (!pinnedOut)
+   {
+      for (int k = 0; k < 10; ++k) if (outPtr[k]) memcpy(outPtr[k], st + k * cap, m * sizeof(double));
+      if (gidOut) memcpy(gidOut, st + 10 * cap, m * sizeof(int));
+   }
    return COMD_OK;
 }
 

@@ -120,6 +120,7 @@ struct ComdDev
    cudaEvent_t evForce[2 * 128]; int nForceEv; cudaEvent_t evT0, evT1; double lastForceMs; long nLaunches;   // force-time ring (128 calls) + user timer
    // e2e staging
    double* hStage; long hStageDoubles;
+   int* rowTab; double* e2eScratch;      // local-row table and f/U scratch of the device-side compaction
    // tuning knobs (comd_dev_set_option)
    int optForceVariant;         // 0 = thread-per-atom stencil loop (v1), 1 = tiled TMA/filter/process engine
    int optTileTx;               // target cells per tile along x

@@ -17,66 +17,78 @@
 #define NL_G 8                  // lanes per atom in the build and force kernels
 
 // ---- build -------------------------------------------------------------------------------
+// One sweep over the 9 stencil rows, 8 lanes per atom, positions from the AoS gather copy (8 lanes
+// read 256 contiguous bytes).  Pairs inside the cutoff go straight to the front of the row; pairs
+// in the skin shell (rc, rc+skin] are parked in shared memory and appended behind them, both parts
+// in ascending index order -- the force kernels then meet rounds that are all hits followed by
+// rounds that are all misses instead of a 70 % mixture in every round.
+#define NL_FARCAP 64            // skin-shell entries parked per atom
 __global__ void __launch_bounds__(256)
-k_nl_build(DevGeom g, double rc2, double rl2,
-           const double* __restrict__ rx, const double* __restrict__ ry, const double* __restrict__ rz,
+k_nl_build(DevGeom g, double rc2, double rl2, const double4* __restrict__ rq,
            const int* __restrict__ cell, const unsigned char* __restrict__ cellType, const int* __restrict__ cellStart,
            int* __restrict__ cnt, int* __restrict__ list, int* __restrict__ count, int stride, long rows,
            double* __restrict__ lx, double* __restrict__ ly, double* __restrict__ lz, unsigned long long* __restrict__ stat)
 {
+   __shared__ int farBuf[8][4][NL_FARCAP];
    const unsigned full = 0xffffffffu;
    const int n = cnt[C_NATOMS];
-   const int lane = threadIdx.x & 31, g4 = lane / NL_G, gl = lane % NL_G;
+   const int lane = threadIdx.x & 31, g4 = lane / NL_G, gl = lane % NL_G, w = threadIdx.x >> 5;
    const int warpsPerGrid = gridDim.x * (blockDim.x >> 5);
    const int rowY = g.P[0], rowZ = g.P[0] * g.P[1];
    const int nQuads = (n + 3) >> 2;
-   for (int q = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); q < nQuads; q += warpsPerGrid)
+   int* myFar = farBuf[w][g4];
+   for (int q = blockIdx.x * (blockDim.x >> 5) + w; q < nQuads; q += warpsPerGrid)
    {
       const int i = 4 * q + g4;
       int c = 0;
       bool act = false;
       if (i < n) { c = cell[i]; act = (cellType[c] & CT_LOCAL) != 0 && i < rows; }
       if (!__any_sync(full, act)) continue;
-      double xi = 0.0, yi = 0.0, zi = 0.0;
-      if (act) { xi = rx[i]; yi = ry[i]; zi = rz[i]; }
-      int nn = 0;
+      double4 pi = make_double4(0.0, 0.0, 0.0, 0.0);
+      if (act) pi = rq[i];
+      int nNear = 0, nFar = 0;
       int* row = list + (long)(act ? i : 0) * stride;
-      // two sweeps: pairs inside the cutoff first, the skin shell (rc, rc+skin] behind them, both
-      // in ascending index order -- the force kernels then meet rounds that are all hits followed
-      // by rounds that are all misses instead of a 70 % mixture in every round
       #pragma unroll 1
-      for (int r = 0; r < 18; ++r)
+      for (int r = 0; r < 9; ++r)
       {
-         const bool far = r >= 9;
-         const int rr = far ? r - 9 : r;
          int jb = 0, je = 0;
          if (act)
          {
-            const int rc = c + ((rr % 3) - 1) * rowY + ((rr / 3) - 1) * rowZ;
+            const int rc = c + ((r % 3) - 1) * rowY + ((r / 3) - 1) * rowZ;
             jb = cellStart[rc - 1]; je = cellStart[rc + 2];
          }
          const int maxlen = __reduce_max_sync(full, je - jb);
          for (int base = 0; base < maxlen; base += NL_G)
          {
             const int j = jb + base + gl;
-            bool ok = false;
+            bool near = false, far = false;
             if (j < je && j != i)
             {
-               const double dx = xi - rx[j], dy = yi - ry[j], dz = zi - rz[j];
+               const double4 pj = rq[j];
+               const double dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
                const double r2 = dx * dx + dy * dy + dz * dz;
-               ok = far ? (r2 > rc2 && r2 <= rl2) : (r2 <= rc2);
+               near = r2 <= rc2;
+               far = !near && r2 <= rl2;
             }
-            const unsigned m = (__ballot_sync(full, ok) >> (g4 * NL_G)) & ((1u << NL_G) - 1u);
-            const int pos = nn + __popc(m & ((1u << gl) - 1u));
-            if (ok && pos < stride) row[pos] = j;
-            nn += __popc(m);
+            const unsigned below = (1u << gl) - 1u, grp = (1u << NL_G) - 1u;
+            const unsigned mN = (__ballot_sync(full, near) >> (g4 * NL_G)) & grp;
+            const unsigned mF = (__ballot_sync(full, far) >> (g4 * NL_G)) & grp;
+            if (near) { const int pos = nNear + __popc(mN & below); if (pos < stride) row[pos] = j; }
+            if (far) { const int pos = nFar + __popc(mF & below); if (pos < NL_FARCAP) myFar[pos] = j; }
+            nNear += __popc(mN);
+            nFar += __popc(mF);
          }
       }
+      __syncwarp();
+      const int nn = nNear + nFar;
+      const bool over = nn > stride || nFar > NL_FARCAP;
+      if (act && !over) for (int k = gl; k < nFar; k += NL_G) row[nNear + k] = myFar[k];
+      __syncwarp();
       if (act && gl == 0)
       {
-         count[i] = nn < stride ? nn : stride;
-         if (nn > stride) atomicOr(&cnt[C_ERR], ERRB_NLFULL);
-         lx[i] = xi; ly[i] = yi; lz[i] = zi;                 // lastR snapshot (neighborList.c:176-183)
+         count[i] = over ? 0 : nn;
+         if (over) atomicOr(&cnt[C_ERR], ERRB_NLFULL);
+         lx[i] = pi.x; ly[i] = pi.y; lz[i] = pi.z;            // lastR snapshot (neighborList.c:176-183)
       }
       // statistics: one atomic per warp
       int tot = (act && gl == 0) ? nn : 0, mx = tot;
@@ -191,7 +203,7 @@ int comdNeighborBuildIfNeeded(ComdDev* d)
    cudaStream_t s = d->stream;
    CUDA_TRY(cudaMemsetAsync(d->nlStat, 0, 2 * sizeof(unsigned long long), s));
    const int n = d->approxAtoms > 0 ? d->approxAtoms : (int)d->cap;
-   k_nl_build<<<gridFor((n + 3) / 4, 8, 148 * 8), 256, 0, s>>>(d->g, d->cutoff * d->cutoff, rl * rl, d->A.r[0], d->A.r[1], d->A.r[2], d->A.cell, d->cellType,
+   k_nl_build<<<gridFor((n + 3) / 4, 8, 148 * 8), 256, 0, s>>>(d->g, d->cutoff * d->cutoff, rl * rl, d->A.rq, d->A.cell, d->cellType,
       d->cellStart, d->cnt, d->nlList, d->nlCount, d->nlStride, d->nlRows, d->nlLastR[0], d->nlLastR[1], d->nlLastR[2], d->nlStat);
    LAUNCH_CHECK(d);
    d->nlValid = 1;

@@ -47,7 +47,7 @@ ABI_SYMBOLS = [
     "comd_dev_set_neighbor_list", "comd_dev_neighbor_stats", "comd_comm_unique_id", "comd_comm_init",
     "comd_comm_allreduce_sum", "comd_comm_allreduce_sum_int", "comd_comm_barrier", "comd_dev_sync",
     "comd_dev_kernel_stats", "comd_dev_step_host", "comd_dev_fp64_peak", "comd_dev_timer_start", "comd_dev_timer_stop",
-    "comd_dev_set_option",
+    "comd_dev_set_option", "comd_host_alloc", "comd_host_free",
 ]
 
 _lib = None
@@ -95,8 +95,35 @@ def lib():
         L.comd_dev_timer_stop.argtypes = [C.c_void_p, _dp]
         L.comd_dev_step_host.argtypes = [C.c_void_p, C.c_int, C.c_double, _ip, C.POINTER(_dp), C.POINTER(_dp), C.POINTER(_dp),
                                          _ip, _ip, C.POINTER(_dp), C.POINTER(_dp), C.POINTER(_dp), _dp, _dp]
+        L.comd_host_alloc.argtypes = [C.POINTER(C.c_void_p), C.c_size_t]
+        L.comd_host_free.argtypes = [C.c_void_p]
         _lib = L
     return _lib
+
+
+class PinnedArray:
+    """A numpy view of page-locked host memory (comd_host_alloc): step_host copies such buffers
+    without staging.  Keep the object alive as long as the array is in use."""
+
+    def __init__(self, n, dtype=np.float64):
+        self.nbytes = int(n) * np.dtype(dtype).itemsize
+        self.ptr = C.c_void_p()
+        _chk(lib().comd_host_alloc(C.byref(self.ptr), max(self.nbytes, 8)))
+        buf = (C.c_char * max(self.nbytes, 8)).from_address(self.ptr.value)
+        self.array = np.frombuffer(buf, dtype=dtype, count=int(n))
+
+    def free(self):
+        if self.ptr:
+            self.array = None
+            lib().comd_host_free(self.ptr)
+            self.ptr = None
+
+
+def pinned_like(a):
+    """Copy a numpy array into pinned host memory; returns (PinnedArray, view)."""
+    pa = PinnedArray(a.size, a.dtype)
+    pa.array[:] = a.ravel()
+    return pa, pa.array
 
 
 def _chk(rc):
@@ -279,8 +306,9 @@ class Device:
         P3 = _dp * 3
         rin = P3(*[_d(a) for a in r]); pin = P3(*[_d(a) for a in p]); fin = P3(*[_d(a) for a in f])
         if not hasattr(self, "_out"):
-            self._out = dict(gid=np.zeros(cap, np.int32), r=[np.zeros(cap) for _ in range(3)],
-                             p=[np.zeros(cap) for _ in range(3)], f=[np.zeros(cap) for _ in range(3)], U=np.zeros(cap))
+            self._pin = [PinnedArray(cap, np.int32)] + [PinnedArray(cap) for _ in range(10)]
+            v = [q.array for q in self._pin]
+            self._out = dict(gid=v[0], r=v[1:4], p=v[4:7], f=v[7:10], U=v[10])
         o = self._out
         rout = P3(*[_d(a) for a in o["r"]]); pout = P3(*[_d(a) for a in o["p"]]); fout = P3(*[_d(a) for a in o["f"]])
         e = np.zeros(2)

@@ -25,6 +25,7 @@
 #ifndef COMD_B200_H
 #define COMD_B200_H
 
+#include <stddef.h>
 #ifdef __cplusplus
 extern "C" {
 #endif
@@ -160,7 +161,10 @@ int  comd_dev_fp64_peak(ComdDev* dev, double* tflops);
 /* End-to-end step through HOST buffers (bench.py `e2e`): one full timestep() whose inputs
  * (gid, r, p, f at time t; SoA, any order, all local to this rank) start in host memory and
  * whose results (gid, r, p, f, U at t+dt, in device order, *nOut of them) end there.
- * H2D/D2H go through pinned staging inside the call. */
+ * Buffers from comd_host_alloc (pinned) are copied directly, pageable ones through pinned staging
+ * inside the call; the ghost-free result is compacted on the device before it crosses PCIe. */
+int  comd_host_alloc(void** p, size_t bytes);      /* cudaMallocHost; any rank, any time after comd_dev_create */
+int  comd_host_free(void* p);
 int  comd_dev_step_host(ComdDev* dev, int nLocal, double dt,
                         const int* gidIn, const double* rIn[3], const double* pIn[3], const double* fIn[3],
                         int* nOut, int* gidOut, double* rOut[3], double* pOut[3], double* fOut[3], double* UOut,
