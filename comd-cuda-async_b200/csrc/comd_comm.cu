@@ -116,7 +116,11 @@ template <typename T> static inline void swapPtr(T*& a, T*& b) { T* t = a; a = b
 
 // Generic two-message phase: sendBuf[0] -> rank nbrM, sendBuf[1] -> rank nbrP;
 // recvBuf[0] <- nbrM (its + face message), recvBuf[1] <- nbrP (its - face message).
-static int exchangePhase(ComdDev* d, int ax, double* sendBuf[2], double* recvBuf[2], int sendBase, int recvBase, int doublesPerItem)
+// `cache`: 12 host ints (6 send counts, 6 receive counts) of this message family.  When `useCache`
+// is set the counts are the ones of the previous exchange (list mode between rebuilds: same atoms,
+// same order), so neither the count messages nor the host synchronisation are needed.
+static int exchangePhase(ComdDev* d, int ax, double* sendBuf[2], double* recvBuf[2], int sendBase, int recvBase, int doublesPerItem,
+                         int* cache = nullptr, bool useCache = false)
 {
    const int fM = 2 * ax, fP = fM + 1;
    cudaStream_t s = d->stream;
@@ -130,6 +134,17 @@ static int exchangePhase(ComdDev* d, int ax, double* sendBuf[2], double* recvBuf
    if (!d->ncclComm) { comdSetError("halo exchange across ranks needs comd_comm_init first"); return COMD_E_STATE; }
    ncclComm_t comm = (ncclComm_t)d->ncclComm;
    const int nbrM = d->nbrRank[fM], nbrP = d->nbrRank[fP];
+   if (cache && useCache)
+   {
+      const long nSM = cache[fM], nSP = cache[fP], nRM = cache[6 + fM], nRP = cache[6 + fP];
+      NCCL_TRY(g_nccl.GroupStart());
+      if (nSP) NCCL_TRY(g_nccl.Send(sendBuf[1], nSP * doublesPerItem, ncclFloat64, nbrP, comm, s));
+      if (nSM) NCCL_TRY(g_nccl.Send(sendBuf[0], nSM * doublesPerItem, ncclFloat64, nbrM, comm, s));
+      if (nRM) NCCL_TRY(g_nccl.Recv(recvBuf[0], nRM * doublesPerItem, ncclFloat64, nbrM, comm, s));
+      if (nRP) NCCL_TRY(g_nccl.Recv(recvBuf[1], nRP * doublesPerItem, ncclFloat64, nbrP, comm, s));
+      NCCL_TRY(g_nccl.GroupEnd());
+      return COMD_OK;
+   }
    // 1. counts travel first (the receiver must size its ncclRecv; the reference leans on
    //    MPI_Get_count, parallel.c:109).  Order matters when nbrM == nbrP (two ranks on the
    //    axis): sends to one peer match its receives in issue order.
@@ -145,6 +160,7 @@ static int exchangePhase(ComdDev* d, int ax, double* sendBuf[2], double* recvBuf
    const long nRM = d->hCnt[recvBase + fM], nRP = d->hCnt[recvBase + fP];
    if (nRM > d->msgCap || nRP > d->msgCap || nSM > d->msgCap || nSP > d->msgCap)
    { comdSetError("halo message of %ld items exceeds capacity %ld", nRM > nRP ? nRM : nRP, d->msgCap); return COMD_E_CAPACITY; }
+   if (cache) { cache[fM] = (int)nSM; cache[fP] = (int)nSP; cache[6 + fM] = (int)nRM; cache[6 + fP] = (int)nRP; }
    // 2. payload
    NCCL_TRY(g_nccl.GroupStart());
    if (nSP) NCCL_TRY(g_nccl.Send(sendBuf[1], nSP * doublesPerItem, ncclFloat64, nbrP, comm, s));
@@ -157,12 +173,18 @@ static int exchangePhase(ComdDev* d, int ax, double* sendBuf[2], double* recvBuf
 
 int comdExchangeAtomsPhase(ComdDev* d, int ax)
 {
-   return exchangePhase(d, ax, d->sendBuf, d->recvBuf, C_SEND0, C_RECV0, COMD_MSG_DOUBLES);
+   d->fpCntValid = 0;                                        // a full atom exchange changes the ghost population
+   return exchangePhase(d, ax, d->sendBuf, d->recvBuf, C_SEND0, C_RECV0, COMD_MSG_DOUBLES, d->hAtomCnt, false);
 }
 
 int comdExchangeFprimePhase(ComdDev* d, int ax)
 {
-   return exchangePhase(d, ax, d->fpSend, d->fpRecv, C_FPSEND0, C_FPGOT0, 1);
+   // list mode: the arrays do not move between rebuilds, so the F' message sizes of the first exchange
+   // after a rebuild hold until the next one
+   const bool cached = d->useNL && (d->fpCntValid & (1 << ax));
+   int rc = exchangePhase(d, ax, d->fpSend, d->fpRecv, C_FPSEND0, C_FPGOT0, 1, d->hFpCnt, cached);
+   if (rc == COMD_OK && d->useNL) d->fpCntValid |= 1 << ax;
+   return rc;
 }
 
 // ghost refresh between neighbour-list rebuilds: same atoms, same order as the last full atom
@@ -170,7 +192,7 @@ int comdExchangeFprimePhase(ComdDev* d, int ax)
 // haloExchange.c:1673-1683)
 int comdExchangeRefreshPhase(ComdDev* d, int ax)
 {
-   return exchangePhase(d, ax, d->sendBuf, d->recvBuf, C_SEND0, C_RECV0, 3);
+   return exchangePhase(d, ax, d->sendBuf, d->recvBuf, C_SEND0, C_RECV0, 3, d->hAtomCnt, true);
 }
 
 // "if one process has to rebuild its neighbour list, all have to" (neighborList.c:236-244)
@@ -181,4 +203,12 @@ int comdAllreduceMaxFlag(ComdDev* d, int* flag)
    int rc = comd_comm_allreduce_sum_int(d, &v, 1);
    *flag = v > 0;
    return rc;
+}
+
+// the same on a device-resident int32 flag, in place, no host round trip (sum of 0/1 flags)
+int comdAllreduceFlagDevice(ComdDev* d, int* devFlag)
+{
+   if (d->nRanks == 1 || !d->ncclComm) return COMD_OK;
+   NCCL_TRY(g_nccl.AllReduce(devFlag, devFlag, 1, ncclInt32, ncclSum, (ncclComm_t)d->ncclComm, d->stream));
+   return COMD_OK;
 }

@@ -126,6 +126,7 @@ struct ComdDev
    int optTileTx;               // target cells per tile along x
    int posDirty;                // positions moved since the FP32 shadow was written
    int tileSmemSet[4];
+   int hAtomCnt[12], hFpCnt[12], fpCntValid;   // host copies of the last message sizes (send 6 | recv 6); F' cache validity per axis
    // nccl
    void* nccl; void* ncclComm;
 };
@@ -202,4 +203,5 @@ int comdExchangeFprimePhase(ComdDev* d, int axis);
 int comdExchangeRefreshPhase(ComdDev* d, int axis);     // 3 doubles per atom, counts of the last full exchange
 int comdNeighborRefreshOrRebuild(ComdDev* d, int* didRefresh);   // neighbor.cu: the redistributeAtomsGpuNL decision
 int comdNeighborAfterSort(ComdDev* d);                  // neighbor.cu: map recorded pool indices to sorted indices
-int comdAllreduceMaxFlag(ComdDev* d, int* flag);        // comm.cu: OR of a host flag over the ranks
+int comdAllreduceMaxFlag(ComdDev* d, int* flag);
+int comdAllreduceFlagDevice(ComdDev* d, int* devFlag); // comm.cu: in-place sum of a device-resident 0/1 flag over the ranks        // comm.cu: OR of a host flag over the ranks

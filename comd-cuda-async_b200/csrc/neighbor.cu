@@ -231,12 +231,11 @@ int comdNeighborRefreshOrRebuild(ComdDev* d, int* didRefresh)
    const double h = 0.5 * d->skin;
    k_nl_check<<<gridFor(d->approxAtoms, 256, 148 * 8), 256, 0, s>>>(h * h, d->A.r[0], d->A.r[1], d->A.r[2],
       d->nlLastR[0], d->nlLastR[1], d->nlLastR[2], d->A.cell, d->cellType, d->cnt); LAUNCH_CHECK(d);
+   int rc = comdAllreduceFlagDevice(d, d->cnt + C_NLREBUILD);     // "if one rebuilds, all rebuild"
+   if (rc != COMD_OK) return rc;
    CUDA_TRY(cudaMemcpyAsync(d->hCnt + C_NLREBUILD, d->cnt + C_NLREBUILD, sizeof(int), cudaMemcpyDeviceToHost, s));
    CUDA_TRY(cudaStreamSynchronize(s));
-   int flag = d->hCnt[C_NLREBUILD];
-   int rc = comdAllreduceMaxFlag(d, &flag);
-   if (rc != COMD_OK) return rc;
-   if (flag) return COMD_OK;                       // caller runs the full re-bin + exchange
+   if (d->hCnt[C_NLREBUILD]) return COMD_OK;       // caller runs the full re-bin + exchange
    for (int ax = 0; ax < 3; ++ax)
    {
       const int fM = 2 * ax, fP = fM + 1;

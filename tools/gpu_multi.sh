@@ -3,8 +3,8 @@
 set -u
 N=${1:-2}; TAG=${2:-multi}
 mkdir -p gpurun_out
-for wl in eam_60 eam_strong lj_weak; do
-  for nl in 0 1; do
+for wl in ${WLS:-eam_60 eam_strong lj_weak}; do
+  for nl in ${NLS:-0 1}; do
     COMD_NL=$nl timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 \
        bench.py --gpus $N --steps 10 --warmup 3 --workload $wl --no-cpu-baseline > gpurun_out/${TAG}_n${N}_${wl}_nl${nl}.log 2>&1
     echo "$wl nl=$nl N=$N rc=$?"
