@@ -158,6 +158,7 @@ def main():
     ap.add_argument("--workload", default="eam_strong", choices=sorted(WORKLOADS))
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--print-rate", type=int, default=10, help="steps per timestep() call = CoMD's printRate (default 10, mycommand.c)")
     ap.add_argument("--neighbor-list", type=int, default=int(os.environ.get("COMD_NL", "1")),
                     help="1: neighbour-list force path (skin 0.1*cutoff, mycommand.c:210), 0: link-cell path")
     args = ap.parse_args()
@@ -208,6 +209,8 @@ def main():
         dev.set_eam(potential["cutoff"], potential["phi"], potential["rho"], potential["f"])
     if args.neighbor_list:
         dev.set_neighbor_list(True, skin)
+    for kv in filter(None, os.environ.get("COMD_OPTS", "").split(",")):      # tuning knobs (comd_dev_set_option), A/B runs only
+        k, v = kv.split("="); dev.set_option(k, int(v))
     if world > 1:
         import torch
         uid = torch.zeros(128, dtype=torch.uint8, device="cuda")
@@ -241,7 +244,10 @@ def main():
     force_ms = []
     dev.kernel_stats()                       # reset the force-time ring
     dev.timer_start()                        # CUDA events on the library's stream (the one the kernels run on)
-    dev.timestep(args.steps, dt)             # K steps enqueued back to back, no host sync in between
+    left = args.steps                        # K steps in intervals of printRate, as CoMD.c:122-139 drives timestep():
+    while left > 0:                          # potential energies are due at the end of every interval
+        dev.timestep(min(left, args.print_rate), dt)
+        left -= args.print_rate
     t_local = dev.timer_stop() * 1e-3
     force_ms.append(dev.kernel_stats()["last_force_ms"])
     l1 = dev.kernel_stats()["launches"]

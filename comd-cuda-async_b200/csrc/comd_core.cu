@@ -559,7 +559,7 @@ extern "C" int comd_dev_destroy(ComdDev* d)
    cudaFree(d->e); cudaFree(d->cellStart); cudaFree(d->cellCount); cudaFree(d->cellFill); cudaFree(d->cellType);
    cudaFree(d->cellKey); cudaFree(d->shell); cudaFree(d->tmpSrc); cudaFree(d->tmpGid); cudaFree(d->tmpCell);
    cudaFree(d->scanBlock); cudaFree(d->cnt); cudaFreeHost(d->hCnt); cudaFree(d->redPartial); cudaFree(d->redOut);
-   cudaFreeHost(d->hRed); cudaFree(d->rhobar); cudaFree(d->dfEmbed); cudaFree(d->tabMem); cudaFree(d->tPRmem); cudaFree(d->tW[0]); cudaFree(d->tW[1]); cudaFree(d->tDR); cudaFree(d->runOff);
+   cudaFreeHost(d->hRed); cudaFree(d->rhobar); cudaFree(d->dfEmbed); cudaFree(d->tabMem); cudaFree(d->tPRmem); cudaFree(d->tW[0]); cudaFree(d->tW[1]); cudaFree(d->tDR); cudaFree(d->rvPhi); cudaFree(d->rvRho); cudaFree(d->r3); cudaFree(d->runOff);
    cudaFree(d->nlList); cudaFree(d->nlCount); cudaFree(d->nlCountHit); cudaFree(d->poolToSorted); cudaFree(d->nlStat);
    for (int f = 0; f < 6; ++f) { cudaFree(d->sendIdx[f]); cudaFree(d->recvIdx[f]); }
    for (int k = 0; k < 2; ++k) { cudaFree(d->sendBuf[k]); cudaFree(d->recvBuf[k]); cudaFree(d->fpSend[k]); cudaFree(d->fpRecv[k]); }
@@ -652,7 +652,37 @@ extern "C" int comd_dev_set_eam(ComdDev* d, double cutoff, const ComdTable* phi,
       CUDA_TRY(cudaMalloc(&d->tDR, w.size() * sizeof(double)));
       CUDA_TRY(cudaMemcpy(d->tDR, w.data(), w.size() * sizeof(double), cudaMemcpyHostToDevice));
    }
-   d->potKind = 2; d->cutoff = cutoff;
+   {  // list path: per interval i the four numbers interpolate() (eam.c:573-578) forms from T[i-1..i+2], in the
+      // same IEEE operations, as one 32-byte record: value = a + 0.5 t (g1 + t c2), slope = 0.5 (g1 + t q) invDx
+      const ComdTable* tv[2] = { phi, rho };
+      double4** dst[2] = { &d->rvPhi, &d->rvRho };
+      std::vector<double> w3;
+      const bool sameGrid = phi->n == rho->n && phi->x0 == rho->x0 && phi->invDx == rho->invDx;
+      if (d->r3) { cudaFree(d->r3); d->r3 = nullptr; }
+      if (sameGrid) w3.resize(4 * (size_t)(phi->n + 2));
+      for (int k = 0; k < 2; ++k)
+      {
+         if (*dst[k]) { cudaFree(*dst[k]); *dst[k] = nullptr; }
+         const int n = tv[k]->n;
+         const double* T = tv[k]->values;
+         std::vector<double> w(4 * (size_t)(n + 2));
+         for (int i = 0; i <= n; ++i)
+         {
+            const double tm = T[i - 1], t0 = T[i], t1 = T[i + 1], t2 = T[i + 2 > n + 1 ? n + 1 : i + 2];
+            const double g1 = t1 - tm, g2 = t2 - t0;
+            w[4 * i] = t0; w[4 * i + 1] = g1; w[4 * i + 2] = t1 + tm - 2.0 * t0; w[4 * i + 3] = g2 - g1;
+            if (sameGrid) { w3[4 * i + 2 * k] = g1; w3[4 * i + 2 * k + 1] = g2 - g1; }
+         }
+         CUDA_TRY(cudaMalloc(dst[k], w.size() * sizeof(double)));
+         CUDA_TRY(cudaMemcpy(*dst[k], w.data(), w.size() * sizeof(double), cudaMemcpyHostToDevice));
+      }
+      if (sameGrid)
+      {
+         CUDA_TRY(cudaMalloc(&d->r3, w3.size() * sizeof(double)));
+         CUDA_TRY(cudaMemcpy(d->r3, w3.data(), w3.size() * sizeof(double), cudaMemcpyHostToDevice));
+      }
+   }
+   d->potKind = 2; d->cutoff = cutoff; d->eValid = 0;
    return COMD_OK;
 }
 
@@ -882,6 +912,7 @@ extern "C" int comd_dev_advance_position(ComdDev* d, double dt)
 extern "C" int comd_dev_energy(ComdDev* d, double eLocal[2])
 {
    if (!d || !eLocal) return COMD_E_ARG;
+   if (d->potKind != 0 && !d->eValid) { comdSetError("comd_dev_energy: no force evaluation with energies since the atoms last moved"); return COMD_E_STATE; }
    CUDA_TRY(cudaSetDevice(d->device));
    k_energy_partial<<<RED_BLOCKS, 256, 0, d->stream>>>(0.5 / d->mass, d->A.cell, d->cellType, d->e, d->A.p[0], d->A.p[1], d->A.p[2],
       d->cnt, d->redPartial); LAUNCH_CHECK(d);
@@ -892,20 +923,28 @@ extern "C" int comd_dev_energy(ComdDev* d, double eLocal[2])
    return rc;
 }
 
-extern "C" int comd_dev_compute_force(ComdDev* d)
+// One force evaluation.  wantEnergy = 0 (inner steps of comd_dev_timestep, list path, EAM) skips the
+// per-atom pair energies nobody can observe; the forces are the same bits either way (force_nl.cuh).
+static int computeForce(ComdDev* d, int wantEnergy)
 {
-   if (!d) return COMD_E_ARG;
    if (d->potKind == 0) { comdSetError("comd_dev_compute_force: no potential set"); return COMD_E_STATE; }
    CUDA_TRY(cudaSetDevice(d->device));
    if (d->useNL) { int rc = comdNeighborBuildIfNeeded(d); if (rc != COMD_OK) return rc; }
    if (d->posDirty && !d->useNL && d->optForceVariant == 1) { int rc = comdRefreshShadow(d); if (rc != COMD_OK) return rc; }
    const int slot = d->nForceEv % 128;
    CUDA_TRY(cudaEventRecord(d->evForce[2 * slot], d->stream));
-   int rc = d->potKind == 1 ? comdForceLJ(d) : comdForceEAM(d);
+   d->wantEnergy = wantEnergy;
+   int rc = d->potKind == 1 ? comdForceLJ(d) : comdForceEAM(d);      // both set d->eValid
    if (rc != COMD_OK) return rc;
    CUDA_TRY(cudaEventRecord(d->evForce[2 * slot + 1], d->stream));
    d->nForceEv++;
    return COMD_OK;
+}
+
+extern "C" int comd_dev_compute_force(ComdDev* d)
+{
+   if (!d) return COMD_E_ARG;
+   return computeForce(d, 1);
 }
 
 // FP32 shadow positions after a drift that was not followed by a redistribute
@@ -929,6 +968,11 @@ extern "C" int comd_dev_set_option(ComdDev* d, const char* key, long value)
 {
    if (!d || !key) return COMD_E_ARG;
    if (!strcmp(key, "force_variant")) { if (value < 0 || value > 1) { comdSetError("force_variant: 0 or 1"); return COMD_E_ARG; } d->optForceVariant = (int)value; return COMD_OK; }
+   if (!strcmp(key, "energy_every_step")) { d->optEnergyEveryStep = value != 0; return COMD_OK; }
+   if (!strcmp(key, "nl_threads")) { if (value < 32 || value > 768 || value % 32) { comdSetError("nl_threads: multiple of 32 in 32..768"); return COMD_E_ARG; } d->optNlThreads = (int)value; return COMD_OK; }
+   if (!strcmp(key, "nl_block")) { const int bx = (int)(value / 10000), by = (int)(value / 100 % 100), bz = (int)(value % 100);
+      if (value != 0 && (bx < 1 || by < 1 || bz < 1 || by * bz > 32)) { comdSetError("nl_block: bx*10000 + by*100 + bz with by*bz <= 32, or 0 for auto"); return COMD_E_ARG; }
+      d->optNlBlock[0] = bx; d->optNlBlock[1] = by; d->optNlBlock[2] = bz; return COMD_OK; }
    if (!strcmp(key, "tile_tx")) { if (value < 1 || value > 16) { comdSetError("tile_tx: 1..16"); return COMD_E_ARG; } d->optTileTx = (int)value; return COMD_OK; }
    comdSetError("comd_dev_set_option: unknown key '%s'", key);
    return COMD_E_ARG;
@@ -946,7 +990,7 @@ extern "C" int comd_dev_timestep(ComdDev* d, int nSteps, double dt)
       d->posDirty = 1;
       int rc = comd_dev_redistribute(d);
       if (rc != COMD_OK) return rc;
-      rc = comd_dev_compute_force(d);
+      rc = computeForce(d, it == nSteps - 1 || d->optEnergyEveryStep);
       if (rc != COMD_OK) return rc;
       rc = comd_dev_advance_velocity(d, 0.5 * dt);
       if (rc != COMD_OK) return rc;

@@ -103,6 +103,14 @@ struct ComdDev
    double2 *tW[2];                       // two copies of the interleaved table, the second shifted by one entry: the 64-byte
                                          // window [i-1, i+2] of any lookup is 32-byte aligned in one of them (two 256-bit loads)
    double2 *tDR;                         // pass 3: {g1, g2-g1} of rho per interval (one 128-bit load), entry 0
+   // list path: one 32-byte record per interval, so every table lookup is ONE sector (LDG.E.256)
+   double4 *rvPhi, *rvRho;               // {T[i], g1, T[i+1]+T[i-1]-2T[i], g2-g1}: value and derivative of one table
+   double4 *r3;                          // {g1, g2-g1} of phi and of rho side by side (same grid only, else NULL)
+   int wantEnergy;                       // this force evaluation also produces per-atom potential energies
+   int eValid;                           // d->e holds the energies of the current configuration
+   int optEnergyEveryStep;               // comd_dev_timestep: energies at every step (1) or only at the last one (0, default)
+   int optNlThreads;                     // CTA size of the list force kernels
+   int optNlBlock[3];                    // cells per work block of the list force kernels (0 = auto)
    double *rhobar, *dfEmbed;
    // neighbour list
    int useNL; double skin;

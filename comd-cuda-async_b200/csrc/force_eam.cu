@@ -261,15 +261,26 @@ int comdForceEAM(ComdDev* d)
 {
    const double rc2 = d->cutoff * d->cutoff;
    cudaStream_t s = d->stream;
-   if (d->useNL || d->optForceVariant == 1)
-   {
-      PairParams Q = {};
-      Q.rc2 = rc2; Q.tPhi = d->tPhi; Q.tRho = d->tRho; Q.tF = d->tF; Q.tPR = d->tPR; Q.tW0 = d->tPR ? d->tW[0] : nullptr; Q.tW1 = d->tW[1]; Q.tDR = d->tDR;
-      int rc = d->useNL ? launchForceNL<PK_EAM1>(d, Q, nullptr) : launchForceTile<PK_EAM1>(d, Q, nullptr);
+   PairParams Q = {};
+   Q.rc2 = rc2; Q.tPhi = d->tPhi; Q.tRho = d->tRho; Q.tF = d->tF; Q.tPR = d->tPR; Q.tW0 = d->tPR ? d->tW[0] : nullptr; Q.tW1 = d->tW[1]; Q.tDR = d->tDR;
+   Q.rvPhi = d->rvPhi; Q.rvRho = d->rvRho; Q.r3 = d->r3;
+   if (d->useNL)
+   {  // list path: rhobar, F' halo, then every pair force in pass 3 (force_nl.cuh); pair energies on request
+      d->eValid = d->wantEnergy;
+      int rc = launchForceNL<PK_RHO>(d, Q);
       if (rc != COMD_OK) return rc;
       rc = comdFprimeHalo(d);
       if (rc != COMD_OK) return rc;
-      return d->useNL ? launchForceNL<PK_EAM3>(d, Q, d->dfEmbed) : launchForceTile<PK_EAM3>(d, Q, d->dfEmbed);
+      return d->wantEnergy ? launchForceNL<PK_EAMFE>(d, Q) : launchForceNL<PK_EAMF>(d, Q);
+   }
+   d->eValid = 1;
+   if (d->optForceVariant == 1)
+   {
+      int rc = launchForceTile<PK_EAM1>(d, Q, nullptr);
+      if (rc != COMD_OK) return rc;
+      rc = comdFprimeHalo(d);
+      if (rc != COMD_OK) return rc;
+      return launchForceTile<PK_EAM3>(d, Q, d->dfEmbed);
    }
    const int grid = gridFor(d->approxAtoms, 128, 148 * 64);
    k_eam_pass1<<<grid, 128, 0, s>>>(d->g, d->tPhi, d->tRho, d->tF, rc2, d->A.r[0], d->A.r[1], d->A.r[2], d->A.cell, d->cellType,

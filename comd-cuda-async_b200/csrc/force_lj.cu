@@ -66,11 +66,12 @@ int comdForceLJ(ComdDev* d)
    P.rc2 = d->cutoff * d->cutoff;
    const double rc6 = P.s6 / (P.rc2 * P.rc2 * P.rc2);
    P.eShift = 1.0 * rc6 * (rc6 - 1.0);                 // POT_SHIFT 1.0, ljForce.c:83,173-174
+   d->eValid = 1;
    if (d->useNL || d->optForceVariant == 1)
    {
       PairParams Q = {};
       Q.s6 = P.s6; Q.eps = P.eps; Q.eShift = P.eShift; Q.rc2 = P.rc2;
-      return d->useNL ? launchForceNL<PK_LJ>(d, Q, nullptr) : launchForceTile<PK_LJ>(d, Q, nullptr);
+      return d->useNL ? launchForceNL<PK_LJ>(d, Q) : launchForceTile<PK_LJ>(d, Q, nullptr);
    }
    k_lj_force_rows<<<gridFor(d->approxAtoms, 128, 148 * 64), 128, 0, d->stream>>>(d->g, P, d->A.r[0], d->A.r[1], d->A.r[2],
       d->A.cell, d->cellType, d->cellStart, d->cnt, d->f[0], d->f[1], d->f[2], d->e);

@@ -62,6 +62,8 @@ struct PairParams
    const double2* tPR;                // interleaved {phi,rho} (same grid), entry 0; valid [-1, n+1]
    const double2* tW0; const double2* tW1;   // shifted copies of tPR for 256-bit window loads (comd_dev.cuh), or NULL
    const double2* tDR;                // pass 3: {g1, g2-g1} of rho per interval
+   // list path (force_nl.cuh): 32-byte records, one sector per lookup
+   const double4* rvPhi; const double4* rvRho; const double4* r3;
 };
 
 // ---- PTX helpers: mbarrier + 1-D bulk copy (TMA engine, UBLKCP in SASS) -----------------

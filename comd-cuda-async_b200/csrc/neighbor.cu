@@ -23,6 +23,7 @@
 // in ascending index order -- the force kernels then meet rounds that are all hits followed by
 // rounds that are all misses instead of a 70 % mixture in every round.
 #define NL_FARCAP 64            // skin-shell entries parked per atom
+#define NL_U 4                  // candidate rounds in flight per trip
 __global__ void __launch_bounds__(256)
 k_nl_build(DevGeom g, double rc2, double rl2, const double4* __restrict__ rq,
            const int* __restrict__ cell, const unsigned char* __restrict__ cellType, const int* __restrict__ cellStart,
@@ -45,6 +46,7 @@ k_nl_build(DevGeom g, double rc2, double rl2, const double4* __restrict__ rq,
       if (i < n) { c = cell[i]; act = (cellType[c] & CT_LOCAL) != 0 && i < rows; }
       if (!__any_sync(full, act)) continue;
       double4 pi = make_double4(0.0, 0.0, 0.0, 0.0);
+      const int i0 = act ? i : 0;                      // a lane without a candidate re-reads its own atom
       if (act) pi = rq[i];
       int nNear = 0, nFar = 0;
       int* row = list + (long)(act ? i : 0) * stride;
@@ -58,25 +60,34 @@ k_nl_build(DevGeom g, double rc2, double rl2, const double4* __restrict__ rq,
             jb = cellStart[rc - 1]; je = cellStart[rc + 2];
          }
          const int maxlen = __reduce_max_sync(full, je - jb);
-         for (int base = 0; base < maxlen; base += NL_G)
+         // four rounds of 8 candidates per trip: the four 32-byte position loads are issued before any of
+         // the (ballot-serialised) bookkeeping, so a trip exposes one memory latency instead of four
+         for (int base = 0; base < maxlen; base += NL_U * NL_G)
          {
-            const int j = jb + base + gl;
-            bool near = false, far = false;
-            if (j < je && j != i)
+            double4 pj[NL_U];
+            #pragma unroll
+            for (int u = 0; u < NL_U; ++u)
             {
-               const double4 pj = rq[j];
-               const double dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
-               const double r2 = dx * dx + dy * dy + dz * dz;
-               near = r2 <= rc2;
-               far = !near && r2 <= rl2;
+               const int j = jb + base + u * NL_G + gl;
+               pj[u] = rq[j < je ? j : i0];
             }
-            const unsigned below = (1u << gl) - 1u, grp = (1u << NL_G) - 1u;
-            const unsigned mN = (__ballot_sync(full, near) >> (g4 * NL_G)) & grp;
-            const unsigned mF = (__ballot_sync(full, far) >> (g4 * NL_G)) & grp;
-            if (near) { const int pos = nNear + __popc(mN & below); if (pos < stride) row[pos] = j; }
-            if (far) { const int pos = nFar + __popc(mF & below); if (pos < NL_FARCAP) myFar[pos] = j; }
-            nNear += __popc(mN);
-            nFar += __popc(mF);
+            #pragma unroll
+            for (int u = 0; u < NL_U; ++u)
+            {
+               const int j = jb + base + u * NL_G + gl;
+               const double dx = pi.x - pj[u].x, dy = pi.y - pj[u].y, dz = pi.z - pj[u].z;
+               const double r2 = dx * dx + dy * dy + dz * dz;
+               const bool ok = j < je && j != i;
+               const bool near = ok && r2 <= rc2;
+               const bool far = ok && !near && r2 <= rl2;
+               const unsigned below = (1u << gl) - 1u, grp = (1u << NL_G) - 1u;
+               const unsigned mN = (__ballot_sync(full, near) >> (g4 * NL_G)) & grp;
+               const unsigned mF = (__ballot_sync(full, far) >> (g4 * NL_G)) & grp;
+               if (near) { const int pos = nNear + __popc(mN & below); if (pos < stride) row[pos] = j; }
+               if (far) { const int pos = nFar + __popc(mF & below); if (pos < NL_FARCAP) myFar[pos] = j; }
+               nNear += __popc(mN);
+               nFar += __popc(mF);
+            }
          }
       }
       __syncwarp();

@@ -26,6 +26,8 @@ else:
     dev.set_eam(potential["cutoff"], potential["phi"], potential["rho"], potential["f"])
 if NL:
     dev.set_neighbor_list(True, skin)
+for kv in filter(None, os.environ.get("COMD_OPTS", "").split(",")):
+    k, v = kv.split("="); dev.set_option(k, int(v))
 dev.upload(gid, r, p)
 dev.compute_force()
 dev.timestep(3, 1.0)          # thermalise a little: realistic hit patterns
@@ -37,8 +39,9 @@ ms = dev.kernel_stats()["last_force_ms"]
 e = dev.energy()
 print("%s n=%d atoms=%d force %.4f ms  (%.1f ps/atom)  E/atom %.9f" % (pot, n, len(gid), ms, ms * 1e9 / len(gid), (e[0] + e[1]) / len(gid)))
 if steps:
+    dev.kernel_stats()
     dev.timer_start(); dev.timestep(steps, 1.0); t = dev.timer_stop()
-    print("step %.4f ms" % (t / steps))
+    print("step %.4f ms  force inside timestep %.4f ms  opts=%s" % (t / steps, dev.kernel_stats()["last_force_ms"], os.environ.get("COMD_OPTS", "")))
 if NL:
     print("neighbour list:", dev.neighbor_stats())
 dev.close()
