@@ -42,7 +42,8 @@ FLOP_PER_ATOM_STEP = {"lj": 78 * 27 + 22, "setfl": 54 * (56 + 37) + 20 + 22, "fu
 HBM_B_PER_ATOM_STEP = {"lj": 96, "setfl": 192, "funcfl": 192}
 # the force kernels' share of that work (what roofline.achieved counts per force launch set)
 # DRAM bytes per atom per force evaluation measured by ncu (sum over the force kernels): (potential, list path?) -> B/atom
-NCU_DRAM_B_PER_ATOM_FORCE = {("setfl", 1): (412.36 + 59.84 + 422.44 + 20.15) * 1e6 / 864000.0}
+NCU_DRAM_B_PER_ATOM_FORCE = {("setfl", 1): (367.97 + 14.16 + 256.72 + 4.95) * 1e6 / 864000.0,    # profiles/r1_v4_nl_ncu_full_eam60.txt
+                             ("lj", 1): (424.85 + 5.43) * 1e6 / 864000.0}                         # profiles/r1_v6_nl_ncu_full_lj60.txt
 FORCE_FLOP_PER_ATOM = {"lj": 78 * 27, "setfl": 54 * (56 + 37) + 20, "funcfl": 42 * 93 + 20}
 
 
@@ -101,23 +102,38 @@ class ClockSampler:
                     reasons=sorted(reasons), samples=len(sm))
 
 
-def cpu_reference_rate(pot, seconds_hint=15.0):
+def host_cores():
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
+def cpu_reference_rate(pot, procs=None):
     """The reference's own CPU path (oracle/_ref/CoMD-ref, -m cpu_nl) on a bounded sample of the same
-    workload, timed by its own timestep timer; falls back to the restated oracle (kind 'port')."""
+    workload, timed by its own timestep timer; falls back to the restated oracle (kind 'port').
+    The reference compiled here is single-rank (its MPI layer is shimmed out, oracle/ref_build), so the host
+    cores are filled the way its rank-per-core decomposition would fill them minus the halo traffic: one
+    independent copy of the sample per core, all running at once, rates added."""
     exe = os.path.join(ROOT, "oracle", "_ref", "CoMD-ref")
     potdir = os.path.join(ROOT, "oracle", "_ref", "pots")
-    n, steps = (32, 10) if pot != "lj" else (40, 10)       # EAM 131k atoms / LJ 256k atoms x 10 steps ~ 5-10 s on one core
+    procs = procs or min(host_cores(), 256)
+    n, steps = (32, 10) if pot != "lj" else (40, 10)       # EAM 131k atoms / LJ 256k atoms x 10 steps ~ 5-10 s per core
     flags = {"lj": [], "funcfl": ["-e"], "setfl": ["-e", "-t", "setfl"]}[pot]
-    sample = "%s %dx%dx%d unit cells (%d atoms) x %d steps, -m cpu_nl, 1 rank" % (
-        {"lj": "LJ 2.5sigma", "funcfl": "EAM Cu_u6", "setfl": "EAM Cu01"}[pot], n, n, n, 4 * n ** 3, steps)
+    sample = "%d concurrent single-rank copies of: %s %dx%dx%d unit cells (%d atoms) x %d steps, -m cpu_nl" % (
+        procs, {"lj": "LJ 2.5sigma", "funcfl": "EAM Cu_u6", "setfl": "EAM Cu01"}[pot], n, n, n, 4 * n ** 3, steps)
     if os.path.exists(exe):
         t0 = time.time()
-        out = subprocess.run([exe, "-m", "cpu_nl", "-d", potdir, "-x", str(n), "-y", str(n), "-z", str(n), "-N", str(steps),
-                              "-n", str(steps)] + flags, cwd=os.path.join(ROOT, "oracle", "_ref"), capture_output=True).stdout.decode("utf-8", "replace")
-        m = re.search(r"Average atom rate:\s+([0-9.eE+-]+) atoms/us", out)
-        if m:
-            return dict(value=float(m.group(1)) * 1e6, unit="atom-steps/s", cores=1, kind="reference", sample=sample,
-                        wall_s=round(time.time() - t0, 2))
+        cmd = [exe, "-m", "cpu_nl", "-d", potdir, "-x", str(n), "-y", str(n), "-z", str(n), "-N", str(steps), "-n", str(steps)] + flags
+        ps = [subprocess.Popen(cmd, cwd=os.path.join(ROOT, "oracle", "_ref"), stdout=subprocess.PIPE, stderr=subprocess.DEVNULL) for _ in range(procs)]
+        rates = []
+        for q in ps:
+            m = re.search(r"Average atom rate:\s+([0-9.eE+-]+) atoms/us", q.communicate()[0].decode("utf-8", "replace"))
+            if m:
+                rates.append(float(m.group(1)) * 1e6)
+        if len(rates) == procs:
+            return dict(value=float(sum(rates)), unit="atom-steps/s", cores=procs, kind="reference", sample=sample,
+                        per_core=float(np.mean(rates)), wall_s=round(time.time() - t0, 2))
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import pyoracle as po
     kind = {"lj": po.POT_LJ, "funcfl": po.POT_FUNCFL, "setfl": po.POT_SETFL}[pot]
@@ -299,9 +315,10 @@ def main():
         "config": {"workload": label, "atoms": n_global, "atoms_per_gpu": n_local, "proc_grid": "%dx%dx%d" % grid,
                    "cells_per_gpu": "%dx%dx%d" % tuple(geom.gridSize[:]), "parallelism": "3-D spatial domain decomposition, 1 rank/GPU",
                    "force_path": "neighbour list (skin 0.1*cutoff, rebuilt when an atom moved > skin/2)" if args.neighbor_list else "link cells (re-binned every step)",
+                   "energies": "potential + kinetic energy every %d steps (CoMD printRate)" % args.print_rate,
                    "l2": "working set %.0f MB per GPU > 126 MB L2 (no flush needed)" % (n_local * 200e-6) if n_local * 200 > 126e6
                          else "working set fits L2: small-config line, not the headline"},
-        "roofline": {"bound": "fp64", "kernel": "force (%s)" % (("k_force_nl<LJ>" if pot == "lj" else "k_force_nl<EAM1> + F' halo + k_force_nl<EAM3>") if args.neighbor_list
+        "roofline": {"bound": "fp64", "kernel": "force (%s)" % (("k_force_nl<LJ>" if pot == "lj" else "k_force_nl<RHO> + F' halo + k_force_nl<EAMF|EAMFE>") if args.neighbor_list
                                                                  else ("k_force_tile<LJ>" if pot == "lj" else "k_force_tile<EAM1> + F' halo + k_force_tile<EAM3>")),
                      "achieved": achieved_tf, "peak": fp64_peak, "unit": "TFLOP/s",
                      "frac": (achieved_tf / fp64_peak) if achieved_tf else None,
@@ -311,7 +328,7 @@ def main():
                      "hbm": {"achieved": hbm_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": hbm_gbs / peaks["hbm_gbs"],
                              "peak_source": peaks["source"], "algorithmic_bytes_per_atom_step": HBM_B_PER_ATOM_STEP[pot]},
                      "traffic": (NCU_DRAM_B_PER_ATOM_FORCE.get((pot, int(bool(args.neighbor_list)))) or 0) * n_local or None,
-                     "traffic_source": "dram__bytes_read+write per force evaluation from ncu --set full at 864k atoms (profiles/r1_v3_nl_ncu_full_eam60.txt), scaled per atom"
+                     "traffic_source": "dram__bytes_read+write per force evaluation from ncu --set full at 864k atoms (profiles/r1_v4_nl_ncu_full_eam60.txt, r1_v6_nl_ncu_full_lj60.txt), scaled per atom"
                                        if NCU_DRAM_B_PER_ATOM_FORCE.get((pot, int(bool(args.neighbor_list)))) else None},
         "e2e": {"value": n_global * args.e2e_steps / t_e2e, "unit": "atom-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "steps": args.e2e_steps},

@@ -24,6 +24,9 @@
 // rounds that are all misses instead of a 70 % mixture in every round.
 #define NL_FARCAP 64            // skin-shell entries parked per atom
 #define NL_U 4                  // candidate rounds in flight per trip
+// Row layout: chunks of 32 entries, each stored transposed -- entry e = 8u + l of a chunk (round u, lane l of
+// the force kernels) sits at 4l + u, so a lane reads the indices of four rounds with one 128-bit load.
+__device__ __forceinline__ int nlSlot(int pos) { return (pos & ~31) | ((pos & 7) << 2) | ((pos >> 3) & 3); }
 __global__ void __launch_bounds__(256)
 k_nl_build(DevGeom g, double rc2, double rl2, const double4* __restrict__ rq,
            const int* __restrict__ cell, const unsigned char* __restrict__ cellType, const int* __restrict__ cellStart,
@@ -83,7 +86,7 @@ k_nl_build(DevGeom g, double rc2, double rl2, const double4* __restrict__ rq,
                const unsigned below = (1u << gl) - 1u, grp = (1u << NL_G) - 1u;
                const unsigned mN = (__ballot_sync(full, near) >> (g4 * NL_G)) & grp;
                const unsigned mF = (__ballot_sync(full, far) >> (g4 * NL_G)) & grp;
-               if (near) { const int pos = nNear + __popc(mN & below); if (pos < stride) row[pos] = j; }
+               if (near) { const int pos = nNear + __popc(mN & below); if (pos < stride) row[nlSlot(pos)] = j; }
                if (far) { const int pos = nFar + __popc(mF & below); if (pos < NL_FARCAP) myFar[pos] = j; }
                nNear += __popc(mN);
                nFar += __popc(mF);
@@ -93,7 +96,7 @@ k_nl_build(DevGeom g, double rc2, double rl2, const double4* __restrict__ rq,
       __syncwarp();
       const int nn = nNear + nFar;
       const bool over = nn > stride || nFar > NL_FARCAP;
-      if (act && !over) for (int k = gl; k < nFar; k += NL_G) row[nNear + k] = myFar[k];
+      if (act && !over) for (int k = gl; k < nFar; k += NL_G) row[nlSlot(nNear + k)] = myFar[k];
       __syncwarp();
       if (act && gl == 0)
       {
@@ -186,7 +189,7 @@ static int nlAllocate(ComdDev* d)
    const double rl = d->cutoff + d->skin;
    const double expect = 4.0 / 3.0 * 3.14159265358979323846 * rl * rl * rl * (double)nLocal / vol;
    int stride = (int)(expect * 1.35) + 16;
-   stride = (stride + NL_G - 1) / NL_G * NL_G;
+   stride = (stride + 31) / 32 * 32;                      // whole chunks (nlSlot)
    const long rows = d->cap;
    if (d->nlList && d->nlStride >= stride && d->nlRows >= rows) return COMD_OK;
    if (d->nlList) { cudaFree(d->nlList); cudaFree(d->nlCount); cudaFree(d->nlCountHit); for (int k = 0; k < 3; ++k) cudaFree(d->nlLastR[k]); }

@@ -361,3 +361,54 @@ def test_neighbor_list_energy_after_100_steps_vs_reference():
     assert abs(ep - g[-1][0]) <= ENERGY100_TOL * abs(g[-1][0])
     assert dev.num_local() == len(a["gid"])
     dev.close()
+
+
+@pytest.mark.parametrize("kind", ["funcfl", "setfl"])
+def test_neighbor_list_energy_on_demand_does_not_change_the_trajectory(kind):
+    """The list path evaluates the EAM pair energies only where the caller can read them (after
+    comd_dev_compute_force and after the last step of comd_dev_timestep).  Forces come from the same
+    instructions either way, so 25 steps in one call, 25 steps with energies at every step and 25 single
+    steps must end in the same bits, energies included."""
+    n = 8
+    orc = oracle_sim(KINDS[kind], n, delta=0.05, temperature=900.0)
+    a = orc.atoms()
+    out = []
+    for mode in ("last", "every", "single"):
+        dev, _ = device_for(orc, (n, n, n), nl_skin=0.1)
+        if mode == "every":
+            dev.set_option("energy_every_step", 1)
+        dev.upload(a["gid"], a["r"], a["p"])
+        dev.compute_force()
+        if mode == "single":
+            for _ in range(25):
+                dev.timestep(1, 1.0)
+        else:
+            dev.timestep(25, 1.0)
+        out.append((by_gid(dev.download()), dev.energy()))
+        dev.close()
+    for d, e in out[1:]:
+        for k in ("r", "p", "f", "U"):
+            assert np.array_equal(d[k], out[0][0][k]), k
+        assert e == out[0][1]
+
+
+@pytest.mark.parametrize("kind", list(KINDS))
+@pytest.mark.parametrize("block", [10101, 20302, 80804, 40116])
+def test_neighbor_list_work_block_shape_is_invisible(kind, block):
+    """The list kernels walk blocks of bx*by*bz cells per CTA; the shape (also ragged against the grid, also
+    a single block for the whole domain) is a scheduling choice and must not change one bit of the result."""
+    n = 10
+    orc = oracle_sim(KINDS[kind], n, delta=0.08, temperature=600.0)
+    a = orc.atoms()
+    res = []
+    for b in (0, block):
+        dev, _ = device_for(orc, (n, n, n), nl_skin=0.1)
+        dev.set_option("nl_block", b)
+        dev.upload(a["gid"], a["r"], a["p"])
+        dev.compute_force()
+        dev.timestep(3, 1.0)
+        res.append(by_gid(dev.download()))
+        dev.close()
+    o = by_gid(a)
+    for k in ("r", "p", "f", "U"):
+        assert np.array_equal(res[0][k], res[1][k]), k
