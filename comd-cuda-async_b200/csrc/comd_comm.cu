@@ -123,7 +123,7 @@ static int exchangePhase(ComdDev* d, int ax, double* sendBuf[2], double* recvBuf
                          int* cache = nullptr, bool useCache = false)
 {
    const int fM = 2 * ax, fP = fM + 1;
-   cudaStream_t s = d->stream;
+   cudaStream_t s = d->xs;
    if (d->nbrRank[fM] == d->rank)
    {
       k_self_counts<<<1, 1, 0, s>>>(d->cnt, sendBase, recvBase, fM); LAUNCH_CHECK(d);

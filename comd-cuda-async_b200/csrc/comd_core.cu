@@ -14,6 +14,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <vector>
+#include <algorithm>
 
 // ------------------------------------------------------------------ errors
 static thread_local char g_err[512] = "";
@@ -468,6 +469,14 @@ extern "C" int comd_dev_create(ComdDev** out, int deviceId, const ComdGeometry* 
    CUDA_TRY(cudaStreamCreateWithFlags(&d->stream, cudaStreamNonBlocking));
    for (int k = 0; k < 256; ++k) CUDA_TRY(cudaEventCreate(&d->evForce[k]));
    CUDA_TRY(cudaEventCreate(&d->evT0)); CUDA_TRY(cudaEventCreate(&d->evT1));
+   {
+      int lo = 0, hi = 0;
+      CUDA_TRY(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+      CUDA_TRY(cudaStreamCreateWithPriority(&d->commStream, cudaStreamNonBlocking, hi));
+      CUDA_TRY(cudaEventCreateWithFlags(&d->evRefresh, cudaEventDisableTiming)); CUDA_TRY(cudaEventCreateWithFlags(&d->evPass1, cudaEventDisableTiming));
+      CUDA_TRY(cudaEventCreateWithFlags(&d->evFp, cudaEventDisableTiming)); CUDA_TRY(cudaEventCreateWithFlags(&d->evStepBegin, cudaEventDisableTiming));
+      d->xs = d->stream; d->optOverlap = 1; d->phStep = -1;
+   }
    const long cap = d->cap;
    int rc;
    if ((rc = allocAtoms(d->A, cap)) != COMD_OK) return rc;
@@ -567,6 +576,28 @@ extern "C" int comd_dev_destroy(ComdDev* d)
    cudaFree(d->rowTab); cudaFree(d->e2eScratch);
    for (int k = 0; k < 256; ++k) cudaEventDestroy(d->evForce[k]);
    cudaEventDestroy(d->evT0); cudaEventDestroy(d->evT1);
+   if (d->optPhaseTiming && d->phaseSteps > 0 && d->rank == 0)
+   {
+      static const char* nm[6] = { "kick+drift+check+flag", "ghost refresh / rebuild", "pass 1 (or LJ force)", "F' halo", "pass 3", "kick" };
+      fprintf(stderr, "[comd phase timing, rank 0, %ld steps] ", d->phaseSteps);
+      const int n = (int)(d->phaseSteps < 1024 ? d->phaseSteps : 1024);
+      for (int k = 0; k < 6; ++k)
+      {  // median: the first NCCL calls and the rebuild steps are outliers by two orders of magnitude
+         std::vector<float> v(d->phaseSample[k], d->phaseSample[k] + n);
+         std::sort(v.begin(), v.end());
+         fprintf(stderr, "%s median %.3f max %.3f ms | ", nm[k], v[n / 2], v[n - 1]);
+      }
+      fprintf(stderr, "\n[comd phase timing] last steps, phases in the order above:");
+      for (long st = d->phaseSteps > 26 ? d->phaseSteps - 26 : 0; st < d->phaseSteps; ++st)
+      {
+         fprintf(stderr, "\n   step %3ld:", st);
+         for (int k = 0; k < 6; ++k) fprintf(stderr, " %7.3f", d->phaseSample[k][st % 1024]);
+      }
+      fprintf(stderr, "\n");
+   }
+   for (int a = 0; a < 32; ++a) for (int b = 0; b < 8; ++b) if (d->evPh[a][b]) cudaEventDestroy(d->evPh[a][b]);
+   cudaEventDestroy(d->evRefresh); cudaEventDestroy(d->evPass1); cudaEventDestroy(d->evFp); cudaEventDestroy(d->evStepBegin);
+   cudaStreamDestroy(d->commStream);
    cudaStreamDestroy(d->stream);
    delete d;
    return COMD_OK;
@@ -721,6 +752,7 @@ extern "C" int comd_dev_redistribute(ComdDev* d)
    CUDA_TRY(cudaSetDevice(d->device));
    const DevGeom& g = d->g;
    cudaStream_t s = d->stream;
+   if (!(d->useNL && d->nlValid)) PH_MARK(d, 1);
    if (d->useNL && d->nlValid)
    {  // redistributeAtomsGpuNL (timestep.c:278-354): re-bin only when the list must be rebuilt,
       // otherwise refresh the ghost positions in place
@@ -936,6 +968,7 @@ static int computeForce(ComdDev* d, int wantEnergy)
    d->wantEnergy = wantEnergy;
    int rc = d->potKind == 1 ? comdForceLJ(d) : comdForceEAM(d);      // both set d->eValid
    if (rc != COMD_OK) return rc;
+   if (d->potKind == 1 || !d->useNL) { PH_MARK(d, 3); PH_MARK(d, 4); }
    CUDA_TRY(cudaEventRecord(d->evForce[2 * slot + 1], d->stream));
    d->nForceEv++;
    return COMD_OK;
@@ -968,6 +1001,14 @@ extern "C" int comd_dev_set_option(ComdDev* d, const char* key, long value)
 {
    if (!d || !key) return COMD_E_ARG;
    if (!strcmp(key, "force_variant")) { if (value < 0 || value > 1) { comdSetError("force_variant: 0 or 1"); return COMD_E_ARG; } d->optForceVariant = (int)value; return COMD_OK; }
+   if (!strcmp(key, "overlap")) { d->optOverlap = value != 0; return COMD_OK; }
+   if (!strcmp(key, "overlap_sms")) { if (value < 0 || value > 148) { comdSetError("overlap_sms: 0..148"); return COMD_E_ARG; } d->optOverlapSms = (int)value; return COMD_OK; }
+   if (!strcmp(key, "phase_timing"))
+   {
+      d->optPhaseTiming = value != 0;
+      if (value) for (int a = 0; a < 32; ++a) for (int b = 0; b < 8; ++b) if (!d->evPh[a][b]) CUDA_TRY(cudaEventCreate(&d->evPh[a][b]));
+      return COMD_OK;
+   }
    if (!strcmp(key, "energy_every_step")) { d->optEnergyEveryStep = value != 0; return COMD_OK; }
    if (!strcmp(key, "nl_threads")) { if (value < 32 || value > 768 || value % 32) { comdSetError("nl_threads: multiple of 32 in 32..768"); return COMD_E_ARG; } d->optNlThreads = (int)value; return COMD_OK; }
    if (!strcmp(key, "nl_block")) { const int bx = (int)(value / 10000), by = (int)(value / 100 % 100), bz = (int)(value % 100);
@@ -985,15 +1026,36 @@ extern "C" int comd_dev_timestep(ComdDev* d, int nSteps, double dt)
    CUDA_TRY(cudaSetDevice(d->device));
    for (int it = 0; it < nSteps; ++it)
    {
+      d->phStep = it; d->inTimestep = 1;
+      PH_MARK(d, 0);
       k_kick_drift<<<gridFor(d->approxAtoms, 256), 256, 0, d->stream>>>(0.5 * dt, dt, 1.0 / d->mass, d->A.cell, d->cellType,
          d->A.r[0], d->A.r[1], d->A.r[2], d->A.p[0], d->A.p[1], d->A.p[2], d->f[0], d->f[1], d->f[2], d->cnt, d->A.rq); LAUNCH_CHECK(d);
       d->posDirty = 1;
-      int rc = comd_dev_redistribute(d);
-      if (rc != COMD_OK) return rc;
-      rc = computeForce(d, it == nSteps - 1 || d->optEnergyEveryStep);
-      if (rc != COMD_OK) return rc;
+      int rc = comd_dev_redistribute(d);           // marks 1 (decision known) and 2 (ghosts in place / enqueued)
+      if (rc != COMD_OK) { d->inTimestep = 0; return rc; }
+      PH_MARK(d, 2);
+      rc = computeForce(d, it == nSteps - 1 || d->optEnergyEveryStep);     // marks 3, 4
+      if (rc != COMD_OK) { d->inTimestep = 0; return rc; }
+      PH_MARK(d, 5);
       rc = comd_dev_advance_velocity(d, 0.5 * dt);
       if (rc != COMD_OK) return rc;
+      PH_MARK(d, 6);
+   }
+   d->phStep = -1; d->inTimestep = 0;
+   if (d->optPhaseTiming)
+   {
+      CUDA_TRY(cudaStreamSynchronize(d->stream));
+      for (int it = 0; it < nSteps && it < 32; ++it)
+      {
+         for (int k = 0; k < 6; ++k)
+         {
+            float ms = 0.f;
+            if (cudaEventElapsedTime(&ms, d->evPh[it][k], d->evPh[it][k + 1]) != cudaSuccess) ms = 0.f;
+            d->phaseSample[k][d->phaseSteps % 1024] = ms;
+         }
+         d->phaseSteps++;
+      }
+      cudaGetLastError();
    }
    return COMD_OK;
 }

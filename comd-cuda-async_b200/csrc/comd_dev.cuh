@@ -137,7 +137,19 @@ struct ComdDev
    int hAtomCnt[12], hFpCnt[12], fpCntValid;   // host copies of the last message sizes (send 6 | recv 6); F' cache validity per axis
    // nccl
    void* nccl; void* ncclComm;
+   // halo / compute overlap (list path, more than one rank): the exchange phases run on `commStream`
+   // while the force kernels work on the blocks of cells that see no ghost (force_nl.cuh)
+   cudaStream_t commStream;      // high priority
+   cudaStream_t xs;              // stream the exchange code enqueues on: `stream`, or `commStream` inside an overlapped section
+   cudaEvent_t evRefresh, evPass1, evFp, evStepBegin;
+   int optOverlap;               // 1 (default): overlap where it applies
+   int optOverlapSms;            // SMs an overlapped interior launch may fill (0 = default)
+   int inTimestep;               // inside comd_dev_timestep: redistribute is always followed by the force call
+   int refreshInFlight;          // ghost refresh of this step enqueued on commStream, evRefresh recorded behind it
+   // per-phase timing of comd_dev_timestep (option "phase_timing"): marks 0..6 per step, first 32 steps of a call
+   int optPhaseTiming; cudaEvent_t evPh[32][8]; float phaseSample[6][1024]; long phaseSteps; int phStep;
 };
+#define PH_MARK(d, id) do { if ((d)->optPhaseTiming && (d)->phStep >= 0 && (d)->phStep < 32) cudaEventRecord((d)->evPh[(d)->phStep][id], (d)->stream); } while (0)
 
 // ---- geometry helpers -----------------------------------------------------------
 __host__ __device__ inline int cellIndex(const DevGeom& g, int ix, int iy, int iz)   // unpadded coords in [-1, n]

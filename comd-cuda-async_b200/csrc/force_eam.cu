@@ -240,14 +240,14 @@ k_fp_unpack(DevGeom g, int axis, const int* __restrict__ runTab, int runStride, 
 int comdFprimeHalo(ComdDev* d)
 {
    const DevGeom& g = d->g;
-   cudaStream_t s = d->stream;
+   cudaStream_t s = d->xs;
    int maxRuns = g.n[1] * g.n[2];
    if (g.n[2] > maxRuns) maxRuns = g.n[2];
    const int runStride = maxRuns + 2;
    k_fp_layout<<<12, 1024, 0, s>>>(g, d->cellStart, d->runOff, runStride, d->cnt); LAUNCH_CHECK(d);
    for (int ax = 0; ax < 3; ++ax)
    {
-      dim3 grid(148, 2);
+      dim3 grid(32, 2);                // small messages; few CTAs so they fit beside an overlapped force launch
       k_fp_pack<<<grid, 256, 0, s>>>(g, ax, d->runOff, runStride, d->dfEmbed, d->fpSend[0], d->fpSend[1], d->msgCap, d->cnt); LAUNCH_CHECK(d);
       int rc = comdExchangeFprimePhase(d, ax);
       if (rc != COMD_OK) return rc;
@@ -267,11 +267,29 @@ int comdForceEAM(ComdDev* d)
    if (d->useNL)
    {  // list path: rhobar, F' halo, then every pair force in pass 3 (force_nl.cuh); pair energies on request
       d->eValid = d->wantEnergy;
-      int rc = launchForceNL<PK_RHO>(d, Q);
+      const bool overlap = d->nRanks > 1 && d->optOverlap;
+      int rc;
+      if (d->refreshInFlight) { rc = launchForceNLSplit<PK_RHO>(d, Q, d->evRefresh); d->refreshInFlight = 0; }
+      else rc = launchForceNL<PK_RHO>(d, Q);
       if (rc != COMD_OK) return rc;
+      PH_MARK(d, 3);
+      if (!overlap)
+      {
+         rc = comdFprimeHalo(d);
+         if (rc != COMD_OK) return rc;
+         PH_MARK(d, 4);
+         return d->wantEnergy ? launchForceNL<PK_EAMFE>(d, Q) : launchForceNL<PK_EAMF>(d, Q);
+      }
+      // F'(rhobar) of the ghosts travels on the exchange stream while pass 3 works on the interior blocks
+      CUDA_TRY(cudaEventRecord(d->evPass1, d->stream));
+      CUDA_TRY(cudaStreamWaitEvent(d->commStream, d->evPass1, 0));
+      d->xs = d->commStream;
       rc = comdFprimeHalo(d);
+      d->xs = d->stream;
       if (rc != COMD_OK) return rc;
-      return d->wantEnergy ? launchForceNL<PK_EAMFE>(d, Q) : launchForceNL<PK_EAMF>(d, Q);
+      CUDA_TRY(cudaEventRecord(d->evFp, d->commStream));
+      PH_MARK(d, 4);
+      return d->wantEnergy ? launchForceNLSplit<PK_EAMFE>(d, Q, d->evFp) : launchForceNLSplit<PK_EAMF>(d, Q, d->evFp);
    }
    d->eValid = 1;
    if (d->optForceVariant == 1)

@@ -71,6 +71,7 @@ int comdForceLJ(ComdDev* d)
    {
       PairParams Q = {};
       Q.s6 = P.s6; Q.eps = P.eps; Q.eShift = P.eShift; Q.rc2 = P.rc2;
+      if (d->useNL && d->refreshInFlight) { d->refreshInFlight = 0; return launchForceNLSplit<PK_LJ>(d, Q, d->evRefresh); }
       return d->useNL ? launchForceNL<PK_LJ>(d, Q) : launchForceTile<PK_LJ>(d, Q, nullptr);
    }
    k_lj_force_rows<<<gridFor(d->approxAtoms, 128, 148 * 64), 128, 0, d->stream>>>(d->g, P, d->A.r[0], d->A.r[1], d->A.r[2],

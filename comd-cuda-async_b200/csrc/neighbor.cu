@@ -191,7 +191,10 @@ static int nlAllocate(ComdDev* d)
    int stride = (int)(expect * 1.35) + 16;
    stride = (stride + 31) / 32 * 32;                      // whole chunks (nlSlot)
    const long rows = d->cap;
-   if (d->nlList && d->nlStride >= stride && d->nlRows >= rows) return COMD_OK;
+   // Keep the first allocation: the row stride is sized once from the mean density (a row overflow is reported,
+   // ERRB_NLFULL).  Re-deriving it at every rebuild made the stride depend on which counters happened to be
+   // on the host (mid-redistribute they are not) and cost a 1.5 GB cudaFree + cudaMalloc inside a time step.
+   if (d->nlList && d->nlRows >= rows) return COMD_OK;
    if (d->nlList) { cudaFree(d->nlList); cudaFree(d->nlCount); cudaFree(d->nlCountHit); for (int k = 0; k < 3; ++k) cudaFree(d->nlLastR[k]); }
    d->nlList = nullptr;
    CUDA_TRY(cudaMalloc(&d->nlList, (size_t)rows * stride * sizeof(int)));
@@ -249,18 +252,35 @@ int comdNeighborRefreshOrRebuild(ComdDev* d, int* didRefresh)
    if (rc != COMD_OK) return rc;
    CUDA_TRY(cudaMemcpyAsync(d->hCnt + C_NLREBUILD, d->cnt + C_NLREBUILD, sizeof(int), cudaMemcpyDeviceToHost, s));
    CUDA_TRY(cudaStreamSynchronize(s));
+   PH_MARK(d, 1);
    if (d->hCnt[C_NLREBUILD]) return COMD_OK;       // caller runs the full re-bin + exchange
+   // More than one rank: the three exchange phases go to the high-priority exchange stream and the force
+   // kernels start on the interior blocks meanwhile (force_nl.cuh); evRefresh marks "ghosts in place".
+   const bool overlap = d->nRanks > 1 && d->optOverlap && d->inTimestep;   // only where the force call is known to follow
+   if (overlap)
+   {
+      CUDA_TRY(cudaEventRecord(d->evStepBegin, s));
+      CUDA_TRY(cudaStreamWaitEvent(d->commStream, d->evStepBegin, 0));
+      d->xs = d->commStream;
+   }
+   cudaStream_t x = d->xs;
    for (int ax = 0; ax < 3; ++ax)
    {
       const int fM = 2 * ax, fP = fM + 1;
-      dim3 grid(148, 2);
-      k_nl_refresh_pack<<<grid, 256, 0, s>>>(ax, d->A.r[0], d->A.r[1], d->A.r[2], d->sendIdx[fM], d->sendIdx[fP], d->cnt,
+      dim3 grid(32, 2);                // few CTAs: they must fit beside an overlapped force launch
+      k_nl_refresh_pack<<<grid, 256, 0, x>>>(ax, d->A.r[0], d->A.r[1], d->A.r[2], d->sendIdx[fM], d->sendIdx[fP], d->cnt,
          d->sendBuf[0], d->sendBuf[1], d->shift[fM][0], d->shift[fM][1], d->shift[fM][2],
          d->shift[fP][0], d->shift[fP][1], d->shift[fP][2]); LAUNCH_CHECK(d);
       rc = comdExchangeRefreshPhase(d, ax);
-      if (rc != COMD_OK) return rc;
-      k_nl_refresh_unpack<<<grid, 256, 0, s>>>(ax, d->A.r[0], d->A.r[1], d->A.r[2], d->recvIdx[fM], d->recvIdx[fP], d->cnt,
+      if (rc != COMD_OK) { d->xs = d->stream; return rc; }
+      k_nl_refresh_unpack<<<grid, 256, 0, x>>>(ax, d->A.r[0], d->A.r[1], d->A.r[2], d->recvIdx[fM], d->recvIdx[fP], d->cnt,
          d->recvBuf[0], d->recvBuf[1], d->A.rq); LAUNCH_CHECK(d);
+   }
+   if (overlap)
+   {
+      CUDA_TRY(cudaEventRecord(d->evRefresh, d->commStream));
+      d->xs = d->stream;
+      d->refreshInFlight = 1;
    }
    d->nlRefreshes++;
    *didRefresh = 1;

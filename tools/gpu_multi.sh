@@ -6,7 +6,7 @@ mkdir -p gpurun_out
 for wl in ${WLS:-eam_60 eam_strong lj_weak}; do
   for nl in ${NLS:-0 1}; do
     COMD_NL=$nl timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 \
-       bench.py --gpus $N --steps 10 --warmup 3 --workload $wl --no-cpu-baseline > gpurun_out/${TAG}_n${N}_${wl}_nl${nl}.log 2>&1
+       bench.py --gpus $N --steps ${STEPS:-20} --warmup 3 --workload $wl --no-cpu-baseline > gpurun_out/${TAG}_n${N}_${wl}_nl${nl}.log 2>&1
     echo "$wl nl=$nl N=$N rc=$?"
     grep "^{" gpurun_out/${TAG}_n${N}_${wl}_nl${nl}.log | python -c "
 import sys,json
