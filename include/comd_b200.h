@@ -122,7 +122,10 @@ int  comd_dev_advance_position(ComdDev* dev, double dt);
 /* computeEnergy (gpu_kernels.cu:1046): eLocal[0] = potential, eLocal[1] = kinetic (rank-local sums) */
 int  comd_dev_energy(ComdDev* dev, double eLocal[2]);
 /* nSteps of timestep() (timestep.c:48-100) without returning to the host in between:
- * kick, drift, redistribute, force, kick.  Leaves r, p, f at t + nSteps*dt. */
+ * kick, drift, redistribute, force, kick.  Leaves r, p, f and the per-atom energies U at
+ * t + nSteps*dt.  On the neighbour-list path the EAM pair energies, which only the caller can
+ * observe, are evaluated at the last of the nSteps force calls (the forces of every step come
+ * from the same instructions either way); option "energy_every_step" restores eam.c's schedule. */
 int  comd_dev_timestep(ComdDev* dev, int nSteps, double dt);
 
 /* ---- neighbour list (optional path): buildNeighborListGpu (gpu_kernels.cu:1981),
@@ -142,9 +145,15 @@ int  comd_comm_allreduce_sum_int(ComdDev* dev, long* inout, int n); /* addIntPar
 int  comd_comm_barrier(ComdDev* dev);                               /* barrierParallel, parallel.c:93  */
 
 /* ---- tuning knobs (no reference counterpart; defaults are the measured-best settings):
- *   "force_variant"  1 = tiled TMA-staged filter/process kernels (default), 0 = thread-per-atom
- *                    stencil loop (the shape of LJ_Force_thread_atom, gpu_lj_thread_atom.h:31-143)
- *   "tile_tx"        target cells per force tile along x (1..16) */
+ *   "force_variant"      link-cell path: 1 = tiled TMA-staged filter/process kernels (default), 0 = thread-per-atom
+ *                        stencil loop (the shape of LJ_Force_thread_atom, gpu_lj_thread_atom.h:31-143)
+ *   "tile_tx"            link-cell path: target cells per force tile along x (1..16)
+ *   "energy_every_step"  list path: per-atom EAM pair energies at every step of comd_dev_timestep (default 0)
+ *   "nl_block"           list path: cells per work block as bx*10000 + by*100 + bz (by*bz <= 32), 0 = auto
+ *   "nl_threads"         list path: cap on the CTA size of the force kernels (multiple of 32)
+ *   "overlap"            list path, N > 1: halo exchange overlapped with the interior blocks (default 1)
+ *   "overlap_sms"        SMs an overlapped interior launch may fill (default 140 of 148)
+ *   "phase_timing"       per-phase CUDA-event timing of comd_dev_timestep, reported on stderr by comd_dev_destroy */
 int  comd_dev_set_option(ComdDev* dev, const char* key, long value);
 
 /* ---- measurement hooks (bench.py / tests) ---------------------------------------- */
