@@ -796,6 +796,7 @@ extern "C" int comd_dev_redistribute(ComdDev* d)
                                                        d->A, d->B, d->cnt, d->useNL ? d->poolToSorted : nullptr); LAUNCH_CHECK(d);
    AtomArrays t = d->A; d->A = d->B; d->B = t;
    d->nlValid = 0;
+   d->e2eOrderValid = 0;
    d->posDirty = 0;
    if (d->useNL) return comdNeighborAfterSort(d);
    return COMD_OK;
@@ -1164,6 +1165,46 @@ k_compact_local(CompactArrays A, const int* __restrict__ rowBeg, const int* __re
    }
 }
 
+// ---- e2e resume path: the caller hands back the atoms of the previous comd_dev_step_host call --------
+// Local atom k of the compact (host) order lives at sorted index rowBeg[row] + (k - rowOff[row]).
+// check: same gids in the same order, and no input position further than skin/2 from the snapshot the
+// neighbour list was built on -> the sort and the list are still valid for these inputs.
+__global__ void __launch_bounds__(256)
+k_e2e_check(const int* __restrict__ rowBeg, const int* __restrict__ rowOff, int nRows, int n, double half2,
+            const int* __restrict__ gidIn, const double* __restrict__ xin, const double* __restrict__ yin, const double* __restrict__ zin,
+            const int* __restrict__ gid, const double* __restrict__ lx, const double* __restrict__ ly, const double* __restrict__ lz,
+            int* __restrict__ flag)
+{
+   bool bad = false;
+   if (blockIdx.x == 0 && threadIdx.x == 0 && rowOff[nRows] != n) bad = true;
+   for (int row = blockIdx.x; row < nRows; row += gridDim.x)
+   {
+      const int b = rowBeg[row], o = rowOff[row], len = rowOff[row + 1] - o;
+      for (int t = threadIdx.x; t < len; t += blockDim.x)
+      {
+         if (o + t >= n) { bad = true; break; }
+         const double dx = xin[o + t] - lx[b + t], dy = yin[o + t] - ly[b + t], dz = zin[o + t] - lz[b + t];
+         bad |= gidIn[o + t] != gid[b + t] || !(dx * dx + dy * dy + dz * dz <= half2);
+      }
+   }
+   if (bad) *flag = 1;
+}
+struct ScatterArrays { const double* in[9]; double* out[9]; };
+__global__ void __launch_bounds__(256)
+k_e2e_scatter(ScatterArrays A, const int* __restrict__ rowBeg, const int* __restrict__ rowOff, int nRows, double4* __restrict__ rq)
+{
+   for (int row = blockIdx.x; row < nRows; row += gridDim.x)
+   {
+      const int b = rowBeg[row], o = rowOff[row], len = rowOff[row + 1] - o;
+      for (int t = threadIdx.x; t < len; t += blockDim.x)
+      {
+         #pragma unroll
+         for (int k = 0; k < 9; ++k) A.out[k][b + t] = A.in[k][o + t];
+         rq[b + t] = make_double4(A.in[0][o + t], A.in[1][o + t], A.in[2][o + t], 0.0);
+      }
+   }
+}
+
 static bool isPinned(const void* p)
 {
    cudaPointerAttributes at;
@@ -1216,37 +1257,73 @@ extern "C" int comd_dev_step_host(ComdDev* d, int n, double dt,
       if (d->hStageDoubles < need)
       {
          if (d->hStage) cudaFreeHost(d->hStage);
-   cudaFree(d->rowTab); cudaFree(d->e2eScratch);
          d->hStage = nullptr; d->hStageDoubles = 0;
          CUDA_TRY(cudaMallocHost(&d->hStage, need * sizeof(double)));
          d->hStageDoubles = need;
       }
    }
    double* st = d->hStage;
-   // ---- inputs
-   for (int k = 0; k < 9; ++k)
-   {
-      const double* src = in[k];
-      if (!pinnedIn) { memcpy(st + k * cap, in[k], n * sizeof(double)); src = st + k * cap; }
-      CUDA_TRY(cudaMemcpyAsync(devIn[k], src, n * sizeof(double), cudaMemcpyHostToDevice, s));
-   }
-   {
-      const int* src = gidIn;
-      if (!pinnedIn) { memcpy(st + 9 * cap, gidIn, n * sizeof(int)); src = reinterpret_cast<const int*>(st + 9 * cap); }
-      CUDA_TRY(cudaMemcpyAsync(A.gid, src, n * sizeof(int), cudaMemcpyHostToDevice, s));
-   }
-   CUDA_TRY(cudaMemsetAsync(A.spec, 0, n * sizeof(int), s));
-   k_set_int<<<gridFor(n, 256), 256, 0, s>>>(A.cell, cellIndex(d->g, 0, 0, 0), n); LAUNCH_CHECK(d);
-   k_set_int<<<1, 1, 0, s>>>(d->cnt + C_NATOMS, n, 1); LAUNCH_CHECK(d);
-   d->approxAtoms = n; d->approxHasGhosts = 0;
-   d->nlValid = 0;                                 // new atoms: the list path must re-bin and rebuild
-   int rc = comd_dev_timestep(d, 1, dt);
-   if (rc != COMD_OK) return rc;
-   // ---- results: compact the local atoms on the device (B is free scratch after the sort)
    const int nRows = d->g.n[1] * d->g.n[2];
    if (!d->rowTab) CUDA_TRY(cudaMalloc(&d->rowTab, (2 * (size_t)nRows + 2) * sizeof(int)));
    if (!d->e2eScratch) CUDA_TRY(cudaMalloc(&d->e2eScratch, (size_t)cap * 4 * sizeof(double)));
    int* rowBeg = d->rowTab; int* rowOff = d->rowTab + nRows;
+   // ---- inputs land in scratch (B is free between sorts): gid and r first, they decide the path
+   AtomArrays& S = d->B;
+   double* scr[9] = { S.r[0], S.r[1], S.r[2], S.p[0], S.p[1], S.p[2], d->e2eScratch, d->e2eScratch + cap, d->e2eScratch + 2 * cap };
+   {
+      const int* src = gidIn;
+      if (!pinnedIn) { memcpy(st + 9 * cap, gidIn, n * sizeof(int)); src = reinterpret_cast<const int*>(st + 9 * cap); }
+      CUDA_TRY(cudaMemcpyAsync(S.gid, src, n * sizeof(int), cudaMemcpyHostToDevice, s));
+   }
+   // Resume path: the previous call left the atoms sorted, the list built and the local-row table of its
+   // compaction in place.  If the caller hands the same atoms back in that order and none is further than
+   // skin/2 from the list's snapshot, neither the sort nor the list has to be redone: the inputs are
+   // scattered to their rows and the step starts from there.  All ranks must agree (the two paths issue
+   // different collectives), hence the flag is summed over the ranks.
+   const bool tryResume = d->useNL && d->nlValid && d->e2eOrderValid;
+   for (int k = 0; k < 9; ++k)
+   {
+      const double* src = in[k];
+      if (!pinnedIn) { memcpy(st + k * cap, in[k], n * sizeof(double)); src = st + k * cap; }
+      CUDA_TRY(cudaMemcpyAsync(scr[k], src, n * sizeof(double), cudaMemcpyHostToDevice, s));
+      if (k == 2 && tryResume)
+      {
+         CUDA_TRY(cudaMemsetAsync(d->cnt + C_NLREBUILD, 0, sizeof(int), s));
+         const double h = 0.5 * d->skin;
+         k_e2e_check<<<gridFor(nRows, 1, 148 * 8), 256, 0, s>>>(rowBeg, rowOff, nRows, n, h * h, S.gid, scr[0], scr[1], scr[2],
+            A.gid, d->nlLastR[0], d->nlLastR[1], d->nlLastR[2], d->cnt + C_NLREBUILD); LAUNCH_CHECK(d);
+         int rcf = comdAllreduceFlagDevice(d, d->cnt + C_NLREBUILD);
+         if (rcf != COMD_OK) return rcf;
+         CUDA_TRY(cudaMemcpyAsync(d->hCnt + C_NLREBUILD, d->cnt + C_NLREBUILD, sizeof(int), cudaMemcpyDeviceToHost, s));
+      }
+   }
+   bool resume = false;
+   if (tryResume)
+   {
+      CUDA_TRY(cudaStreamSynchronize(s));
+      resume = d->hCnt[C_NLREBUILD] == 0;
+   }
+   d->e2eOrderValid = 0;
+   if (resume)
+   {
+      ScatterArrays Q;
+      for (int k = 0; k < 9; ++k) { Q.in[k] = scr[k]; Q.out[k] = devIn[k]; }
+      k_e2e_scatter<<<gridFor(nRows, 1, 148 * 8), 256, 0, s>>>(Q, rowBeg, rowOff, nRows, A.rq); LAUNCH_CHECK(d);
+      d->e2eResumes++;
+   }
+   else
+   {
+      for (int k = 0; k < 9; ++k) CUDA_TRY(cudaMemcpyAsync(devIn[k], scr[k], n * sizeof(double), cudaMemcpyDeviceToDevice, s));
+      CUDA_TRY(cudaMemcpyAsync(A.gid, S.gid, n * sizeof(int), cudaMemcpyDeviceToDevice, s));
+      CUDA_TRY(cudaMemsetAsync(A.spec, 0, n * sizeof(int), s));
+      k_set_int<<<gridFor(n, 256), 256, 0, s>>>(A.cell, cellIndex(d->g, 0, 0, 0), n); LAUNCH_CHECK(d);
+      k_set_int<<<1, 1, 0, s>>>(d->cnt + C_NATOMS, n, 1); LAUNCH_CHECK(d);
+      d->approxAtoms = n; d->approxHasGhosts = 0;
+      d->nlValid = 0;                              // new atoms: the list path must re-bin and rebuild
+   }
+   int rc = comd_dev_timestep(d, 1, dt);
+   if (rc != COMD_OK) return rc;
+   // ---- results: compact the local atoms on the device (B is free scratch after the sort)
    k_local_rows<<<1, 1024, 0, s>>>(d->g, d->cellStart, rowBeg, rowOff); LAUNCH_CHECK(d);
    CompactArrays C;
    AtomArrays& B = d->B;
@@ -1272,11 +1349,19 @@ extern "C" int comd_dev_step_host(ComdDev* d, int n, double dt,
       CUDA_TRY(cudaMemcpyAsync(dst, B.gid, m * sizeof(int), cudaMemcpyDeviceToHost, s));
    }
    CUDA_TRY(cudaStreamSynchronize(s));
+   d->e2eOrderValid = 1;                           // rowTab describes the order the caller now holds
    if (!pinnedOut)
    {
       for (int k = 0; k < 10; ++k) if (outPtr[k]) memcpy(outPtr[k], st + k * cap, m * sizeof(double));
       if (gidOut) memcpy(gidOut, st + 10 * cap, m * sizeof(int));
    }
+   return COMD_OK;
+}
+
+extern "C" int comd_dev_step_host_stats(ComdDev* d, long* nResumed)
+{
+   if (!d || !nResumed) return COMD_E_ARG;
+   *nResumed = d->e2eResumes;
    return COMD_OK;
 }
 

@@ -129,6 +129,8 @@ struct ComdDev
    // e2e staging
    double* hStage; long hStageDoubles;
    int* rowTab; double* e2eScratch;      // local-row table and f/U scratch of the device-side compaction
+   int e2eOrderValid;                    // rowTab describes the current sort and the caller holds the atoms in that order
+   long e2eResumes;                      // comd_dev_step_host calls served without re-sorting / rebuilding
    // tuning knobs (comd_dev_set_option)
    int optForceVariant;         // 0 = thread-per-atom stencil loop (v1), 1 = tiled TMA/filter/process engine
    int optTileTx;               // target cells per tile along x

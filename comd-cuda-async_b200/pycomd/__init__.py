@@ -47,7 +47,7 @@ ABI_SYMBOLS = [
     "comd_dev_set_neighbor_list", "comd_dev_neighbor_stats", "comd_comm_unique_id", "comd_comm_init",
     "comd_comm_allreduce_sum", "comd_comm_allreduce_sum_int", "comd_comm_barrier", "comd_dev_sync",
     "comd_dev_kernel_stats", "comd_dev_step_host", "comd_dev_fp64_peak", "comd_dev_timer_start", "comd_dev_timer_stop",
-    "comd_dev_set_option", "comd_host_alloc", "comd_host_free",
+    "comd_dev_set_option", "comd_host_alloc", "comd_host_free", "comd_dev_step_host_stats",
 ]
 
 _lib = None
@@ -316,6 +316,13 @@ class Device:
         _chk(lib().comd_dev_step_host(self.h, n, dt, _i(gid), rin, pin, fin, C.byref(m), _i(o["gid"]), rout, pout, fout,
                                       _d(o["U"]), _d(e)))
         return m.value, o, (float(e[0]), float(e[1]))
+
+    def step_host_resumed(self):
+        """step_host calls served from the previous call's sort and neighbour list."""
+        n = C.c_long()
+        lib().comd_dev_step_host_stats.argtypes = [C.c_void_p, C.POINTER(C.c_long)]
+        _chk(lib().comd_dev_step_host_stats(self.h, C.byref(n)))
+        return n.value
 
     # --- multi-GPU
     @staticmethod

@@ -178,6 +178,10 @@ int  comd_dev_step_host(ComdDev* dev, int nLocal, double dt,
                         const int* gidIn, const double* rIn[3], const double* pIn[3], const double* fIn[3],
                         int* nOut, int* gidOut, double* rOut[3], double* pOut[3], double* fOut[3], double* UOut,
                         double eLocal[2]);
+/* A caller that hands the atoms of one comd_dev_step_host call to the next (same gids, same order, no
+ * position further than skin/2 from the neighbour list's snapshot) is served without re-sorting and
+ * without rebuilding the list; anything else takes the full upload path.  *nResumed counts the former. */
+int  comd_dev_step_host_stats(ComdDev* dev, long* nResumed);
 
 #ifdef __cplusplus
 }
