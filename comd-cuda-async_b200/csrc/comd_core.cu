@@ -598,6 +598,7 @@ extern "C" int comd_dev_destroy(ComdDev* d)
    for (int a = 0; a < 32; ++a) for (int b = 0; b < 8; ++b) if (d->evPh[a][b]) cudaEventDestroy(d->evPh[a][b]);
    cudaEventDestroy(d->evRefresh); cudaEventDestroy(d->evPass1); cudaEventDestroy(d->evFp); cudaEventDestroy(d->evStepBegin);
    cudaStreamDestroy(d->commStream);
+   if (d->copyStream) { cudaStreamDestroy(d->copyStream); cudaEventDestroy(d->evCopy); }
    cudaStreamDestroy(d->stream);
    delete d;
    return COMD_OK;
@@ -1020,6 +1021,15 @@ extern "C" int comd_dev_set_option(ComdDev* d, const char* key, long value)
    return COMD_E_ARG;
 }
 
+// first half of a step: p += dt/2 f ; r += dt p/m (timestep.c:62-68), gather copy refreshed
+static int launchKickDrift(ComdDev* d, double dt)
+{
+   k_kick_drift<<<gridFor(d->approxAtoms, 256), 256, 0, d->stream>>>(0.5 * dt, dt, 1.0 / d->mass, d->A.cell, d->cellType,
+      d->A.r[0], d->A.r[1], d->A.r[2], d->A.p[0], d->A.p[1], d->A.p[2], d->f[0], d->f[1], d->f[2], d->cnt, d->A.rq); LAUNCH_CHECK(d);
+   d->posDirty = 1;
+   return COMD_OK;
+}
+
 extern "C" int comd_dev_timestep(ComdDev* d, int nSteps, double dt)
 {
    if (!d || nSteps < 0) return COMD_E_ARG;
@@ -1029,10 +1039,9 @@ extern "C" int comd_dev_timestep(ComdDev* d, int nSteps, double dt)
    {
       d->phStep = it; d->inTimestep = 1;
       PH_MARK(d, 0);
-      k_kick_drift<<<gridFor(d->approxAtoms, 256), 256, 0, d->stream>>>(0.5 * dt, dt, 1.0 / d->mass, d->A.cell, d->cellType,
-         d->A.r[0], d->A.r[1], d->A.r[2], d->A.p[0], d->A.p[1], d->A.p[2], d->f[0], d->f[1], d->f[2], d->cnt, d->A.rq); LAUNCH_CHECK(d);
-      d->posDirty = 1;
-      int rc = comd_dev_redistribute(d);           // marks 1 (decision known) and 2 (ghosts in place / enqueued)
+      int rc = launchKickDrift(d, dt);
+      if (rc != COMD_OK) { d->inTimestep = 0; return rc; }
+      rc = comd_dev_redistribute(d);               // marks 1 (decision known) and 2 (ghosts in place / enqueued)
       if (rc != COMD_OK) { d->inTimestep = 0; return rc; }
       PH_MARK(d, 2);
       rc = computeForce(d, it == nSteps - 1 || d->optEnergyEveryStep);     // marks 3, 4
@@ -1150,6 +1159,8 @@ k_local_rows(DevGeom g, const int* __restrict__ cellStart, int* __restrict__ row
 }
 
 struct CompactArrays { const double* in[10]; double* out[10]; const int* gidIn; int* gidOut; };
+// arrays K0..K1-1 (0-2 r, 3-5 p, 6-8 f, 9 U) of the local atoms, row by row, into dense output arrays
+template <int K0, int K1, bool GID>
 __global__ void __launch_bounds__(256)
 k_compact_local(CompactArrays A, const int* __restrict__ rowBeg, const int* __restrict__ rowOff, int nRows)
 {
@@ -1159,8 +1170,8 @@ k_compact_local(CompactArrays A, const int* __restrict__ rowBeg, const int* __re
       for (int t = threadIdx.x; t < len; t += blockDim.x)
       {
          #pragma unroll
-         for (int k = 0; k < 10; ++k) A.out[k][o + t] = A.in[k][b + t];
-         A.gidOut[o + t] = A.gidIn[b + t];
+         for (int k = K0; k < K1; ++k) A.out[k][o + t] = A.in[k][b + t];
+         if (GID) A.gidOut[o + t] = A.gidIn[b + t];
       }
    }
 }
@@ -1321,34 +1332,76 @@ extern "C" int comd_dev_step_host(ComdDev* d, int n, double dt,
       d->approxAtoms = n; d->approxHasGhosts = 0;
       d->nlValid = 0;                              // new atoms: the list path must re-bin and rebuild
    }
-   int rc = comd_dev_timestep(d, 1, dt);
-   if (rc != COMD_OK) return rc;
-   // ---- results: compact the local atoms on the device (B is free scratch after the sort)
-   k_local_rows<<<1, 1024, 0, s>>>(d->g, d->cellStart, rowBeg, rowOff); LAUNCH_CHECK(d);
-   CompactArrays C;
-   AtomArrays& B = d->B;
+   // ---- the step, in the pieces of comd_dev_timestep, so that results leave as soon as they are final:
+   // positions and gids are final after the drift + redistribute and cross PCIe (copy stream) while the
+   // force kernels run; momenta, forces and energies follow after the second kick.
+   if (!d->copyStream)
+   {
+      CUDA_TRY(cudaStreamCreateWithFlags(&d->copyStream, cudaStreamNonBlocking));
+      CUDA_TRY(cudaEventCreateWithFlags(&d->evCopy, cudaEventDisableTiming));
+   }
+   d->inTimestep = 1;
+   int rc = launchKickDrift(d, dt);
+   if (rc == COMD_OK) rc = comd_dev_redistribute(d);
+   if (rc != COMD_OK) { d->inTimestep = 0; return rc; }
+   AtomArrays& B = d->B;                           // free scratch after the sort / the input scatter
    const double* cin[10] = { d->A.r[0], d->A.r[1], d->A.r[2], d->A.p[0], d->A.p[1], d->A.p[2], d->f[0], d->f[1], d->f[2], d->e };
    double* cout[10] = { B.r[0], B.r[1], B.r[2], B.p[0], B.p[1], B.p[2], d->e2eScratch, d->e2eScratch + cap, d->e2eScratch + 2 * cap,
                         d->e2eScratch + 3 * cap };
-   for (int k = 0; k < 10; ++k) { C.in[k] = cin[k]; C.out[k] = cout[k]; }
-   C.gidIn = d->A.gid; C.gidOut = B.gid;
-   k_compact_local<<<gridFor(nRows, 1, 148 * 8), 256, 0, s>>>(C, rowBeg, rowOff, nRows); LAUNCH_CHECK(d);
+   k_local_rows<<<1, 1024, 0, s>>>(d->g, d->cellStart, rowBeg, rowOff); LAUNCH_CHECK(d);
+   {
+      CompactArrays C;
+      for (int k = 0; k < 10; ++k) { C.in[k] = cin[k]; C.out[k] = cout[k]; }
+      C.gidIn = d->A.gid; C.gidOut = B.gid;
+      k_compact_local<0, 3, true><<<gridFor(nRows, 1, 148 * 8), 256, 0, s>>>(C, rowBeg, rowOff, nRows); LAUNCH_CHECK(d);
+      CUDA_TRY(cudaEventRecord(d->evCopy, s));
+      CUDA_TRY(cudaStreamWaitEvent(d->copyStream, d->evCopy, 0));
+   }
+   // The early copy needs the local count on the host before the step has finished: it is the input count on
+   // one rank (nobody can leave) and on any rank whose atoms were resumed and not re-binned in this step.
+   const bool earlyCopy = d->nRanks == 1 || (resume && d->nlValid);
+   if (earlyCopy)
+   {
+      for (int k = 0; k < 3; ++k)
+      {
+         if (!outPtr[k]) continue;
+         double* dst = pinnedOut ? outPtr[k] : st + k * cap;
+         CUDA_TRY(cudaMemcpyAsync(dst, cout[k], n * sizeof(double), cudaMemcpyDeviceToHost, d->copyStream));
+      }
+      if (gidOut)
+      {
+         int* dst = pinnedOut ? gidOut : reinterpret_cast<int*>(st + 10 * cap);
+         CUDA_TRY(cudaMemcpyAsync(dst, B.gid, n * sizeof(int), cudaMemcpyDeviceToHost, d->copyStream));
+      }
+   }
+   rc = computeForce(d, 1);
+   if (rc == COMD_OK) rc = comd_dev_advance_velocity(d, 0.5 * dt);
+   d->inTimestep = 0;
+   if (rc != COMD_OK) return rc;
+   {
+      CompactArrays C;
+      for (int k = 0; k < 10; ++k) { C.in[k] = cin[k]; C.out[k] = cout[k]; }
+      C.gidIn = d->A.gid; C.gidOut = B.gid;
+      k_compact_local<3, 10, false><<<gridFor(nRows, 1, 148 * 8), 256, 0, s>>>(C, rowBeg, rowOff, nRows); LAUNCH_CHECK(d);
+   }
    rc = comd_dev_energy(d, eLocal);                // syncs, refreshes hCnt
    if (rc != COMD_OK) return rc;
    const int m = d->hCnt[C_NLOCAL];
    if (nOut) *nOut = m;
-   for (int k = 0; k < 10; ++k)
+   if (earlyCopy && m != n) { comdSetError("comd_dev_step_host: %d local atoms after the step, %d on input", m, n); return COMD_E_STATE; }
+   for (int k = earlyCopy ? 3 : 0; k < 10; ++k)
    {
       if (!outPtr[k]) continue;
       double* dst = pinnedOut ? outPtr[k] : st + k * cap;
       CUDA_TRY(cudaMemcpyAsync(dst, cout[k], m * sizeof(double), cudaMemcpyDeviceToHost, s));
    }
-   if (gidOut)
+   if (gidOut && !earlyCopy)
    {
       int* dst = pinnedOut ? gidOut : reinterpret_cast<int*>(st + 10 * cap);
       CUDA_TRY(cudaMemcpyAsync(dst, B.gid, m * sizeof(int), cudaMemcpyDeviceToHost, s));
    }
    CUDA_TRY(cudaStreamSynchronize(s));
+   CUDA_TRY(cudaStreamSynchronize(d->copyStream));
    d->e2eOrderValid = 1;                           // rowTab describes the order the caller now holds
    if (!pinnedOut)
    {

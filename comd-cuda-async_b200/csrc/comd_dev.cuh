@@ -129,6 +129,7 @@ struct ComdDev
    // e2e staging
    double* hStage; long hStageDoubles;
    int* rowTab; double* e2eScratch;      // local-row table and f/U scratch of the device-side compaction
+   cudaStream_t copyStream; cudaEvent_t evCopy;   // results that are final early leave on their own stream (comd_dev_step_host)
    int e2eOrderValid;                    // rowTab describes the current sort and the caller holds the atoms in that order
    long e2eResumes;                      // comd_dev_step_host calls served without re-sorting / rebuilding
    // tuning knobs (comd_dev_set_option)
