@@ -330,27 +330,41 @@ k_advance_position(double dt, double invMass, const int* __restrict__ cell, cons
    }
 }
 // first half of a step in one pass: p += dt/2 f ; r += dt p / m
+// First half of a step (timestep.c:62-68).  TWO: the second half-kick of the previous step is applied first --
+// same f, two separately rounded additions, i.e. the bits advanceVelocity + advanceVelocity would give.
+// CHECK: the neighbour list's rebuild criterion (any local atom further than skin/2 from the snapshot the
+// list was built on, neighborList.c:212-234) is evaluated on the new position while it is in registers.
+template <bool TWO, bool CHECK>
 __global__ void __launch_bounds__(256)
 k_kick_drift(double dtHalf, double dt, double invMass, const int* __restrict__ cell, const unsigned char* __restrict__ cellType,
              double* __restrict__ rx, double* __restrict__ ry, double* __restrict__ rz,
              double* __restrict__ px, double* __restrict__ py, double* __restrict__ pz,
              const double* __restrict__ fx, const double* __restrict__ fy, const double* __restrict__ fz,
-             const int* __restrict__ cnt, double4* __restrict__ rq)
+             int* __restrict__ cnt, double4* __restrict__ rq,
+             const double* __restrict__ lx, const double* __restrict__ ly, const double* __restrict__ lz, double half2)
 {
    const int n = cnt[C_NATOMS];
+   bool hit = false;
    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
    {
       if (!(cellType[cell[i]] & CT_LOCAL)) continue;
-      const double a = __dadd_rn(px[i], __dmul_rn(dtHalf, fx[i]));
-      const double b = __dadd_rn(py[i], __dmul_rn(dtHalf, fy[i]));
-      const double c = __dadd_rn(pz[i], __dmul_rn(dtHalf, fz[i]));
+      const double hx = __dmul_rn(dtHalf, fx[i]), hy = __dmul_rn(dtHalf, fy[i]), hz = __dmul_rn(dtHalf, fz[i]);
+      double a = px[i], b = py[i], c = pz[i];
+      if (TWO) { a = __dadd_rn(a, hx); b = __dadd_rn(b, hy); c = __dadd_rn(c, hz); }
+      a = __dadd_rn(a, hx); b = __dadd_rn(b, hy); c = __dadd_rn(c, hz);
       px[i] = a; py[i] = b; pz[i] = c;
       const double x = __dadd_rn(rx[i], __dmul_rn(__dmul_rn(dt, a), invMass));
       const double y = __dadd_rn(ry[i], __dmul_rn(__dmul_rn(dt, b), invMass));
       const double z = __dadd_rn(rz[i], __dmul_rn(__dmul_rn(dt, c), invMass));
       rx[i] = x; ry[i] = y; rz[i] = z;
       rq[i] = make_double4(x, y, z, 0.0);
+      if (CHECK)
+      {
+         const double dx = lx[i] - x, dy = ly[i] - y, dz = lz[i] - z;
+         hit |= dx * dx + dy * dy + dz * dz > half2;
+      }
    }
+   if (CHECK && __any_sync(0xffffffffu, hit) && (threadIdx.x & 31) == 0) cnt[C_NLREBUILD] = 1;   // every writer stores the same value
 }
 
 // ---- energy: deterministic two-level reduction (fixed grid, fixed tree); replaces
@@ -937,6 +951,7 @@ extern "C" int comd_dev_advance_position(ComdDev* d, double dt)
 {
    if (!d) return COMD_E_ARG;
    CUDA_TRY(cudaSetDevice(d->device));
+   d->checkFused = 0;
    k_advance_position<<<gridFor(d->approxAtoms, 256), 256, 0, d->stream>>>(dt, 1.0 / d->mass, d->A.cell, d->cellType,
       d->A.r[0], d->A.r[1], d->A.r[2], d->A.p[0], d->A.p[1], d->A.p[2], d->cnt, d->A.rq); LAUNCH_CHECK(d);
    d->posDirty = 1;
@@ -1022,11 +1037,22 @@ extern "C" int comd_dev_set_option(ComdDev* d, const char* key, long value)
 }
 
 // first half of a step: p += dt/2 f ; r += dt p/m (timestep.c:62-68), gather copy refreshed
-static int launchKickDrift(ComdDev* d, double dt)
+static int launchKickDrift(ComdDev* d, double dt, bool two = false)
 {
-   k_kick_drift<<<gridFor(d->approxAtoms, 256), 256, 0, d->stream>>>(0.5 * dt, dt, 1.0 / d->mass, d->A.cell, d->cellType,
-      d->A.r[0], d->A.r[1], d->A.r[2], d->A.p[0], d->A.p[1], d->A.p[2], d->f[0], d->f[1], d->f[2], d->cnt, d->A.rq); LAUNCH_CHECK(d);
+   const bool check = d->useNL && d->nlValid;
+   const double h = 0.5 * d->skin;
+   const int grid = gridFor(d->approxAtoms, 256);
+#define KD_ARGS 0.5 * dt, dt, 1.0 / d->mass, d->A.cell, d->cellType, d->A.r[0], d->A.r[1], d->A.r[2], d->A.p[0], d->A.p[1], d->A.p[2], \
+   d->f[0], d->f[1], d->f[2], d->cnt, d->A.rq, d->nlLastR[0], d->nlLastR[1], d->nlLastR[2], h * h
+   if (check) CUDA_TRY(cudaMemsetAsync(d->cnt + C_NLREBUILD, 0, sizeof(int), d->stream));
+   if (two && check) k_kick_drift<true, true><<<grid, 256, 0, d->stream>>>(KD_ARGS);
+   else if (two) k_kick_drift<true, false><<<grid, 256, 0, d->stream>>>(KD_ARGS);
+   else if (check) k_kick_drift<false, true><<<grid, 256, 0, d->stream>>>(KD_ARGS);
+   else k_kick_drift<false, false><<<grid, 256, 0, d->stream>>>(KD_ARGS);
+#undef KD_ARGS
+   LAUNCH_CHECK(d);
    d->posDirty = 1;
+   d->checkFused = check;                          // comdNeighborRefreshOrRebuild finds the flag already evaluated
    return COMD_OK;
 }
 
@@ -1039,7 +1065,7 @@ extern "C" int comd_dev_timestep(ComdDev* d, int nSteps, double dt)
    {
       d->phStep = it; d->inTimestep = 1;
       PH_MARK(d, 0);
-      int rc = launchKickDrift(d, dt);
+      int rc = launchKickDrift(d, dt, it > 0);    // it > 0: the previous step left its second half-kick to this kernel
       if (rc != COMD_OK) { d->inTimestep = 0; return rc; }
       rc = comd_dev_redistribute(d);               // marks 1 (decision known) and 2 (ghosts in place / enqueued)
       if (rc != COMD_OK) { d->inTimestep = 0; return rc; }
@@ -1047,8 +1073,11 @@ extern "C" int comd_dev_timestep(ComdDev* d, int nSteps, double dt)
       rc = computeForce(d, it == nSteps - 1 || d->optEnergyEveryStep);     // marks 3, 4
       if (rc != COMD_OK) { d->inTimestep = 0; return rc; }
       PH_MARK(d, 5);
-      rc = comd_dev_advance_velocity(d, 0.5 * dt);
-      if (rc != COMD_OK) return rc;
+      if (it == nSteps - 1)
+      {
+         rc = comd_dev_advance_velocity(d, 0.5 * dt);
+         if (rc != COMD_OK) { d->inTimestep = 0; return rc; }
+      }
       PH_MARK(d, 6);
    }
    d->phStep = -1; d->inTimestep = 0;

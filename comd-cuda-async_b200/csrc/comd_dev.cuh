@@ -147,6 +147,7 @@ struct ComdDev
    cudaEvent_t evRefresh, evPass1, evFp, evStepBegin;
    int optOverlap;               // 1 (default): overlap where it applies
    int optOverlapSms;            // SMs an overlapped interior launch may fill (0 = default)
+   int checkFused;               // the drift kernel already evaluated the list's rebuild criterion for the current positions
    int inTimestep;               // inside comd_dev_timestep: redistribute is always followed by the force call
    int refreshInFlight;          // ghost refresh of this step enqueued on commStream, evRefresh recorded behind it
    // per-phase timing of comd_dev_timestep (option "phase_timing"): marks 0..6 per step, first 32 steps of a call

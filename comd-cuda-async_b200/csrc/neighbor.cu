@@ -244,10 +244,14 @@ int comdNeighborRefreshOrRebuild(ComdDev* d, int* didRefresh)
 {
    cudaStream_t s = d->stream;
    *didRefresh = 0;
-   CUDA_TRY(cudaMemsetAsync(d->cnt + C_NLREBUILD, 0, sizeof(int), s));
-   const double h = 0.5 * d->skin;
-   k_nl_check<<<gridFor(d->approxAtoms, 256, 148 * 8), 256, 0, s>>>(h * h, d->A.r[0], d->A.r[1], d->A.r[2],
-      d->nlLastR[0], d->nlLastR[1], d->nlLastR[2], d->A.cell, d->cellType, d->cnt); LAUNCH_CHECK(d);
+   if (d->checkFused) d->checkFused = 0;           // the drift kernel of this step evaluated the criterion (comd_core.cu, k_kick_drift)
+   else
+   {
+      CUDA_TRY(cudaMemsetAsync(d->cnt + C_NLREBUILD, 0, sizeof(int), s));
+      const double h = 0.5 * d->skin;
+      k_nl_check<<<gridFor(d->approxAtoms, 256, 148 * 8), 256, 0, s>>>(h * h, d->A.r[0], d->A.r[1], d->A.r[2],
+         d->nlLastR[0], d->nlLastR[1], d->nlLastR[2], d->A.cell, d->cellType, d->cnt); LAUNCH_CHECK(d);
+   }
    int rc = comdAllreduceFlagDevice(d, d->cnt + C_NLREBUILD);     // "if one rebuilds, all rebuild"
    if (rc != COMD_OK) return rc;
    CUDA_TRY(cudaMemcpyAsync(d->hCnt + C_NLREBUILD, d->cnt + C_NLREBUILD, sizeof(int), cudaMemcpyDeviceToHost, s));
