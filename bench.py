@@ -276,6 +276,22 @@ def main():
         t_max = t_local
     clocks = sampler.stop() if rank == 0 else None
     e1 = dev.energy()
+    # the same K steps on eam.c's own schedule (pair energies evaluated at every step, not only where they are
+    # read): reported beside `value` so that nobody has to take the on-demand energies on trust
+    dev.set_option("energy_every_step", 1)
+    barrier()
+    dev.timer_start()
+    left = args.steps
+    while left > 0:
+        dev.timestep(min(left, args.print_rate), dt)
+        left -= args.print_rate
+    t_every = dev.timer_stop() * 1e-3
+    dev.set_option("energy_every_step", 0)
+    if dist is not None:
+        import torch
+        t = torch.tensor([t_every], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        t_every = float(t.item())
     n_after = dev.num_local()
 
     # ---- e2e: the same step through HOST buffers (H2D of gid,r,p,f + D2H of gid,r,p,f,U inside the timed region)
@@ -337,6 +353,7 @@ def main():
                 "steps": args.e2e_steps, "chained": True, "resumed_steps": e2e_resumed,
                 "note": "each call's host results are the next call's host inputs; a resumed step reuses the device-side sort and neighbour list "
                         "(valid by the skin/2 criterion), the others re-sort and rebuild"},
+        "value_energies_every_step": n_global * args.steps / t_every,
         "gpu_launches": int(l1 - l0),
         "clocks": clocks,
         "check": {"e_total_per_atom_before": (e0[0] + e0[1]) / n_local, "e_total_per_atom_after": (e1[0] + e1[1]) / n_local,
