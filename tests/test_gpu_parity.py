@@ -459,3 +459,23 @@ def test_step_host_chained_calls_resume_without_resort(kind):
     assert np.array_equal(np.sort(o2["gid"][:m2]), np.sort(g))
     assert abs(sum(e2) - sum(e1)) <= 1e-5 * abs(sum(e1))            # one more step of an energy-conserving integrator
     dev2.close()
+
+
+@pytest.mark.parametrize("kind", ["lj", "setfl"])
+def test_neighbor_list_non_cubic_box(kind):
+    """6 x 9 x 13 unit cells: different cell counts per axis, work blocks ragged against every face."""
+    nxyz = (6, 9, 13)
+    orc = oracle_sim(KINDS[kind], 0, delta=0.07, temperature=600.0, nxyz=nxyz)
+    a = orc.atoms()
+    dev, _ = device_for(orc, nxyz, nl_skin=0.1)
+    dev.upload(a["gid"], a["r"], a["p"])
+    dev.compute_force()
+    d = by_gid(dev.download()); o = by_gid(a)
+    assert rel_err(d["f"], o["f"]) <= FORCE_TOL
+    assert rel_err(d["U"], o["U"] * u_scale(kind)) <= FORCE_TOL
+    dev.timestep(10, 1.0)
+    orc.timestep(10)
+    ep, ek = dev.energy(); eo = orc.energies()
+    assert abs((ep + ek) - sum(eo)) <= 1e-9 * abs(sum(eo))
+    assert dev.num_local() == len(a["gid"])
+    dev.close()
