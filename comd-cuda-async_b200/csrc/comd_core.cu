@@ -583,7 +583,7 @@ extern "C" int comd_dev_destroy(ComdDev* d)
    cudaFree(d->cellKey); cudaFree(d->shell); cudaFree(d->tmpSrc); cudaFree(d->tmpGid); cudaFree(d->tmpCell);
    cudaFree(d->scanBlock); cudaFree(d->cnt); cudaFreeHost(d->hCnt); cudaFree(d->redPartial); cudaFree(d->redOut);
    cudaFreeHost(d->hRed); cudaFree(d->rhobar); cudaFree(d->dfEmbed); cudaFree(d->tabMem); cudaFree(d->tPRmem); cudaFree(d->tW[0]); cudaFree(d->tW[1]); cudaFree(d->tDR); cudaFree(d->rvPhi); cudaFree(d->rvRho); cudaFree(d->r3); cudaFree(d->runOff);
-   cudaFree(d->nlList); cudaFree(d->nlCount); cudaFree(d->nlCountHit); cudaFree(d->poolToSorted); cudaFree(d->nlStat);
+   cudaFree(d->nlWork); cudaFree(d->nlList); cudaFree(d->nlCount); cudaFree(d->nlCountHit); cudaFree(d->poolToSorted); cudaFree(d->nlStat);
    for (int f = 0; f < 6; ++f) { cudaFree(d->sendIdx[f]); cudaFree(d->recvIdx[f]); }
    for (int k = 0; k < 2; ++k) { cudaFree(d->sendBuf[k]); cudaFree(d->recvBuf[k]); cudaFree(d->fpSend[k]); cudaFree(d->fpRecv[k]); }
    if (d->hStage) cudaFreeHost(d->hStage);
