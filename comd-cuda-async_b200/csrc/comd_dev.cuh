@@ -116,6 +116,7 @@ struct ComdDev
    int useNL; double skin;
    int *nlList; int *nlCount; int nlStride; int nlMax; double* nlLastR[3]; int nlBuilds; int nlValid;
    long nlRows;                 // rows allocated in nlList
+   int optNlChunksPerCta;                // target work chunks per CTA of the list force kernels (0 = default 32)
    int *nlWork; unsigned nlWorkSeq;      // work counters of the list force kernels (one per launch, ring of 64)
    int *nlCountHit;             // per atom: list prefix that held every in-cutoff entry in the last pass 1
    int nlRefreshes;             // steps served by a ghost refresh instead of a rebuild
