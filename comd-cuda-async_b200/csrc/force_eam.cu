@@ -247,7 +247,7 @@ int comdFprimeHalo(ComdDev* d)
    k_fp_layout<<<12, 1024, 0, s>>>(g, d->cellStart, d->runOff, runStride, d->cnt); LAUNCH_CHECK(d);
    for (int ax = 0; ax < 3; ++ax)
    {
-      dim3 grid(32, 2);                // small messages; few CTAs so they fit beside an overlapped force launch
+      dim3 grid(d->nRanks > 1 ? 32 : 148, 2);   // ranks > 1: few CTAs, they must fit beside an overlapped force launch
       k_fp_pack<<<grid, 256, 0, s>>>(g, ax, d->runOff, runStride, d->dfEmbed, d->fpSend[0], d->fpSend[1], d->msgCap, d->cnt); LAUNCH_CHECK(d);
       int rc = comdExchangeFprimePhase(d, ax);
       if (rc != COMD_OK) return rc;

@@ -271,7 +271,7 @@ int comdNeighborRefreshOrRebuild(ComdDev* d, int* didRefresh)
    for (int ax = 0; ax < 3; ++ax)
    {
       const int fM = 2 * ax, fP = fM + 1;
-      dim3 grid(32, 2);                // few CTAs: they must fit beside an overlapped force launch
+      dim3 grid(d->nRanks > 1 ? 32 : 148, 2);   // ranks > 1: few CTAs, they must fit beside an overlapped force launch
       k_nl_refresh_pack<<<grid, 256, 0, x>>>(ax, d->A.r[0], d->A.r[1], d->A.r[2], d->sendIdx[fM], d->sendIdx[fP], d->cnt,
          d->sendBuf[0], d->sendBuf[1], d->shift[fM][0], d->shift[fM][1], d->shift[fM][2],
          d->shift[fP][0], d->shift[fP][1], d->shift[fP][2]); LAUNCH_CHECK(d);
