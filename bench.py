@@ -124,16 +124,23 @@ def cpu_reference_rate(pot, procs=None):
         procs, {"lj": "LJ 2.5sigma", "funcfl": "EAM Cu_u6", "setfl": "EAM Cu01"}[pot], n, n, n, 4 * n ** 3, steps)
     if os.path.exists(exe):
         t0 = time.time()
-        cmd = [exe, "-m", "cpu_nl", "-d", potdir, "-x", str(n), "-y", str(n), "-z", str(n), "-N", str(steps), "-n", str(steps)] + flags
-        ps = [subprocess.Popen(cmd, cwd=os.path.join(ROOT, "oracle", "_ref"), stdout=subprocess.PIPE, stderr=subprocess.DEVNULL) for _ in range(procs)]
-        rates = []
-        for q in ps:
-            m = re.search(r"Average atom rate:\s+([0-9.eE+-]+) atoms/us", q.communicate()[0].decode("utf-8", "replace"))
-            if m:
-                rates.append(float(m.group(1)) * 1e6)
-        if len(rates) == procs:
-            return dict(value=float(sum(rates)), unit="atom-steps/s", cores=procs, kind="reference", sample=sample,
-                        per_core=float(np.mean(rates)), wall_s=round(time.time() - t0, 2))
+        builds = {}
+        for name, binary in (("-O2", exe), ("-O3 -march=x86-64-v3", exe + "-O3")):      # oracle/ref_build/Makefile; the reference's own Makefile sets no -O at all
+            if not os.path.exists(binary):
+                continue
+            cmd = [binary, "-m", "cpu_nl", "-d", potdir, "-x", str(n), "-y", str(n), "-z", str(n), "-N", str(steps), "-n", str(steps)] + flags
+            ps = [subprocess.Popen(cmd, cwd=os.path.join(ROOT, "oracle", "_ref"), stdout=subprocess.PIPE, stderr=subprocess.DEVNULL) for _ in range(procs)]
+            rates = []
+            for q in ps:
+                m = re.search(r"Average atom rate:\s+([0-9.eE+-]+) atoms/us", q.communicate()[0].decode("utf-8", "replace"))
+                if m:
+                    rates.append(float(m.group(1)) * 1e6)
+            if len(rates) == procs:
+                builds[name] = float(sum(rates))
+        if builds:
+            best = max(builds, key=builds.get)
+            return dict(value=builds[best], unit="atom-steps/s", cores=procs, kind="reference", sample=sample, build=best,
+                        by_build=builds, per_core=builds[best] / procs, wall_s=round(time.time() - t0, 2))
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import pyoracle as po
     kind = {"lj": po.POT_LJ, "funcfl": po.POT_FUNCFL, "setfl": po.POT_SETFL}[pot]
