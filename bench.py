@@ -125,11 +125,14 @@ def cpu_reference_rate(pot, procs=None):
     if os.path.exists(exe):
         t0 = time.time()
         builds = {}
+        import shutil
+        import tempfile
+        scratch = tempfile.mkdtemp(prefix="comd_ref_")      # the reference writes a YAML report per run into its cwd
         for name, binary in (("-O2", exe), ("-O3 -march=x86-64-v3", exe + "-O3")):      # oracle/ref_build/Makefile; the reference's own Makefile sets no -O at all
             if not os.path.exists(binary):
                 continue
             cmd = [binary, "-m", "cpu_nl", "-d", potdir, "-x", str(n), "-y", str(n), "-z", str(n), "-N", str(steps), "-n", str(steps)] + flags
-            ps = [subprocess.Popen(cmd, cwd=os.path.join(ROOT, "oracle", "_ref"), stdout=subprocess.PIPE, stderr=subprocess.DEVNULL) for _ in range(procs)]
+            ps = [subprocess.Popen(cmd, cwd=scratch, stdout=subprocess.PIPE, stderr=subprocess.DEVNULL) for _ in range(procs)]
             rates = []
             for q in ps:
                 m = re.search(r"Average atom rate:\s+([0-9.eE+-]+) atoms/us", q.communicate()[0].decode("utf-8", "replace"))
@@ -137,6 +140,7 @@ def cpu_reference_rate(pot, procs=None):
                     rates.append(float(m.group(1)) * 1e6)
             if len(rates) == procs:
                 builds[name] = float(sum(rates))
+        shutil.rmtree(scratch, ignore_errors=True)
         if builds:
             best = max(builds, key=builds.get)
             return dict(value=builds[best], unit="atom-steps/s", cores=procs, kind="reference", sample=sample, build=best,
