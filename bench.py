@@ -185,6 +185,7 @@ def main():
     ap.add_argument("--workload", default="eam_strong", choices=sorted(WORKLOADS))
     ap.add_argument("--e2e-steps", type=int, default=4)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--skin", type=float, default=0.1, help="neighbour-list skin relative to the cutoff (CoMD -S, default 0.1)")
     ap.add_argument("--print-rate", type=int, default=10, help="steps per timestep() call = CoMD's printRate (default 10, mycommand.c)")
     ap.add_argument("--neighbor-list", type=int, default=int(os.environ.get("COMD_NL", "1")),
                     help="1: neighbour-list force path (skin 0.1*cutoff, mycommand.c:210), 0: link-cell path")
@@ -217,7 +218,7 @@ def main():
     lat = potential["lat"]
     gext = [n_cells[a] * lat for a in range(3)]
     coord = (rank % grid[0], (rank // grid[0]) % grid[1], rank // (grid[0] * grid[1]))
-    skin = 0.1 * potential["cutoff"] if args.neighbor_list else 0.0
+    skin = args.skin * potential["cutoff"] if args.neighbor_list else 0.0
     geom = pycomd.make_geometry(gext, potential["cutoff"] + skin, grid, coord)
     lmin = [geom.localMin[a] for a in range(3)]; lmax = [geom.localMax[a] for a in range(3)]
     gid, r = P.fcc_block(n_cells, lat, lmin, lmax)
@@ -344,7 +345,7 @@ def main():
         "dtype": "f64", "data": "synthetic FCC Cu lattice (a=3.615 A), numpy-seeded Maxwell-Boltzmann momenta at 600 K, dt=1 fs",
         "config": {"workload": label, "atoms": n_global, "atoms_per_gpu": n_local, "proc_grid": "%dx%dx%d" % grid,
                    "cells_per_gpu": "%dx%dx%d" % tuple(geom.gridSize[:]), "parallelism": "3-D spatial domain decomposition, 1 rank/GPU",
-                   "force_path": "neighbour list (skin 0.1*cutoff, rebuilt when an atom moved > skin/2)" if args.neighbor_list else "link cells (re-binned every step)",
+                   "force_path": ("neighbour list (skin %g*cutoff, rebuilt when an atom moved > skin/2)" % args.skin) if args.neighbor_list else "link cells (re-binned every step)",
                    "energies": "potential + kinetic energy every %d steps (CoMD printRate)" % args.print_rate,
                    "l2": "working set %.0f MB per GPU > 126 MB L2 (no flush needed)" % (n_local * 200e-6) if n_local * 200 > 126e6
                          else "working set fits L2: small-config line, not the headline"},
