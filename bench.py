@@ -168,10 +168,13 @@ def run_reference(args, pot, label, scaling):
         rates.append(base["value"])
     v = float(np.mean(rates))
     base["value"] = v
+    ncell = WORKLOADS[args.workload][1]
+    n_atoms = 4 * ncell ** 3 * (args.gpus if scaling == "weak" else 1)
     print(json.dumps({
         "impl": "reference", "metric": "atom-steps/s", "value": v, "unit": "atom-steps/s", "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": None, "higher_is_better": True, "scaling": scaling, "vs_baseline": None,
-        "dtype": "f64", "data": "synthetic", "config": {"workload": label, "note": "reference CPU path (-m cpu_nl), bounded sample, rate is size-independent (O(N))"},
+        "warmup": args.warmup, "ms_per_step": 1e3 * n_atoms / v, "higher_is_better": True, "scaling": scaling, "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic", "config": {"workload": label, "note": "reference CPU path (-m cpu_nl), bounded sample, rate is size-independent (O(N)); "
+                                                                                     "ms_per_step = atoms of the workload / sampled rate"},
         "cpu_baseline": base, "e2e": {"value": v, "unit": "atom-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
 
