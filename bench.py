@@ -326,11 +326,22 @@ def main():
         m, o, _ = dev.step_host(dt, o["gid"][:m], [a[:m] for a in o["r"]], [a[:m] for a in o["p"]], [a[:m] for a in o["f"]])
     t_e2e = time.perf_counter() - t0
     e2e_resumed = dev.step_host_resumed() - r0
+    # the same chain with the library waiting for each upload before it starts the step (what every call did before
+    # the speculative start existed, and what calls on more than one rank still do)
+    dev.set_option("e2e_speculate", 0)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.e2e_steps):
+        m, o, _ = dev.step_host(dt, o["gid"][:m], [a[:m] for a in o["r"]], [a[:m] for a in o["p"]], [a[:m] for a in o["f"]])
+    t_e2e_wait = time.perf_counter() - t0
     if dist is not None:
         import torch
         t = torch.tensor([t_e2e], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         t_e2e = float(t.item())
+        t = torch.tensor([t_e2e_wait], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        t_e2e_wait = float(t.item())
     h2d = n_local * (4 + 9 * 8)
     d2h = n_local * (4 + 10 * 8) + 16              # local atoms only (compacted on the device): gid + r,p,f,U, and the two energies
 
@@ -366,8 +377,12 @@ def main():
                                        if NCU_DRAM_B_PER_ATOM_FORCE.get((pot, int(bool(args.neighbor_list)))) else None},
         "e2e": {"value": n_global * args.e2e_steps / t_e2e, "unit": "atom-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "steps": args.e2e_steps, "chained": True, "resumed_steps": e2e_resumed,
-                "note": "each call's host results are the next call's host inputs; a resumed step reuses the device-side sort and neighbour list "
-                        "(valid by the skin/2 criterion), the others re-sort and rebuild"},
+                "value_upload_first": n_global * args.e2e_steps / t_e2e_wait,
+                "note": "each call's host results (pinned, updated in place) are the next call's host inputs; a resumed step reuses the "
+                        "device-side sort and neighbour list (valid by the skin/2 criterion), the others re-sort and rebuild.  On one rank the "
+                        "step starts from the atoms the device still holds while the inputs cross PCIe and is kept only if the uploaded "
+                        "inputs equal them bit for bit (otherwise redone from the upload); value_upload_first = the same chain with that "
+                        "switched off (every step waits for its upload)"},
         "value_energies_every_step": n_global * args.steps / t_every,
         "gpu_launches": int(l1 - l0),
         "clocks": clocks,

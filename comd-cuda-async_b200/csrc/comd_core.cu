@@ -490,6 +490,7 @@ extern "C" int comd_dev_create(ComdDev** out, int deviceId, const ComdGeometry* 
       CUDA_TRY(cudaEventCreateWithFlags(&d->evRefresh, cudaEventDisableTiming)); CUDA_TRY(cudaEventCreateWithFlags(&d->evPass1, cudaEventDisableTiming));
       CUDA_TRY(cudaEventCreateWithFlags(&d->evFp, cudaEventDisableTiming)); CUDA_TRY(cudaEventCreateWithFlags(&d->evStepBegin, cudaEventDisableTiming));
       d->xs = d->stream; d->optOverlap = 1; d->phStep = -1;
+      d->e2eSpecArmed = 1;
    }
    const long cap = d->cap;
    int rc;
@@ -587,7 +588,9 @@ extern "C" int comd_dev_destroy(ComdDev* d)
    for (int f = 0; f < 6; ++f) { cudaFree(d->sendIdx[f]); cudaFree(d->recvIdx[f]); }
    for (int k = 0; k < 2; ++k) { cudaFree(d->sendBuf[k]); cudaFree(d->recvBuf[k]); cudaFree(d->fpSend[k]); cudaFree(d->fpRecv[k]); }
    if (d->hStage) cudaFreeHost(d->hStage);
-   cudaFree(d->rowTab); cudaFree(d->e2eScratch);
+   cudaFree(d->rowTab); cudaFree(d->e2eU); cudaFree(d->e2eUgid); cudaFree(d->e2eFlag);
+   for (int k = 0; k < 2; ++k) { cudaFree(d->e2eOut[k]); cudaFree(d->e2eOutGid[k]); }
+   if (d->hE2eFlag) cudaFreeHost(d->hE2eFlag);
    for (int k = 0; k < 256; ++k) cudaEventDestroy(d->evForce[k]);
    cudaEventDestroy(d->evT0); cudaEventDestroy(d->evT1);
    if (d->optPhaseTiming && d->phaseSteps > 0 && d->rank == 0)
@@ -612,7 +615,11 @@ extern "C" int comd_dev_destroy(ComdDev* d)
    for (int a = 0; a < 32; ++a) for (int b = 0; b < 8; ++b) if (d->evPh[a][b]) cudaEventDestroy(d->evPh[a][b]);
    cudaEventDestroy(d->evRefresh); cudaEventDestroy(d->evPass1); cudaEventDestroy(d->evFp); cudaEventDestroy(d->evStepBegin);
    cudaStreamDestroy(d->commStream);
-   if (d->copyStream) { cudaStreamDestroy(d->copyStream); cudaEventDestroy(d->evCopy); }
+   if (d->copyStream)
+   {
+      cudaStreamDestroy(d->copyStream); cudaStreamDestroy(d->upStream);
+      cudaEventDestroy(d->evCopy); cudaEventDestroy(d->evUpR); cudaEventDestroy(d->evUpP); cudaEventDestroy(d->evUp);
+   }
    cudaStreamDestroy(d->stream);
    delete d;
    return COMD_OK;
@@ -621,6 +628,7 @@ extern "C" int comd_dev_destroy(ComdDev* d)
 extern "C" int comd_dev_set_mass(ComdDev* d, double m)
 {
    if (!d || !(m > 0.0)) { comdSetError("comd_dev_set_mass: bad argument"); return COMD_E_ARG; }
+   d->e2ePristine = 0;
    d->mass = m;
    return COMD_OK;
 }
@@ -764,6 +772,7 @@ extern "C" int comd_dev_sync(ComdDev* d)
 extern "C" int comd_dev_redistribute(ComdDev* d)
 {
    if (!d) return COMD_E_ARG;
+   d->e2ePristine = 0;
    CUDA_TRY(cudaSetDevice(d->device));
    const DevGeom& g = d->g;
    cudaStream_t s = d->stream;
@@ -823,6 +832,7 @@ extern "C" int comd_dev_upload_atoms(ComdDev* d, int n, const int* gid, const in
 {
    if (!d || n < 0 || !gid || !rx || !ry || !rz) { comdSetError("comd_dev_upload_atoms: bad argument"); return COMD_E_ARG; }
    if (n > d->cap) { comdSetError("comd_dev_upload_atoms: %d atoms > capacity %ld", n, d->cap); return COMD_E_CAPACITY; }
+   d->e2ePristine = 0;
    CUDA_TRY(cudaSetDevice(d->device));
    cudaStream_t s = d->stream;
    AtomArrays& A = d->A;
@@ -941,6 +951,7 @@ extern "C" int comd_dev_cell_counts(ComdDev* d, int* nAtomsPerRefBox, int nTotal
 extern "C" int comd_dev_advance_velocity(ComdDev* d, double dt)
 {
    if (!d) return COMD_E_ARG;
+   d->e2ePristine = 0;
    CUDA_TRY(cudaSetDevice(d->device));
    k_advance_velocity<<<gridFor(d->approxAtoms, 256), 256, 0, d->stream>>>(dt, d->A.cell, d->cellType, d->A.p[0], d->A.p[1], d->A.p[2],
       d->f[0], d->f[1], d->f[2], d->cnt); LAUNCH_CHECK(d);
@@ -950,6 +961,7 @@ extern "C" int comd_dev_advance_velocity(ComdDev* d, double dt)
 extern "C" int comd_dev_advance_position(ComdDev* d, double dt)
 {
    if (!d) return COMD_E_ARG;
+   d->e2ePristine = 0;
    CUDA_TRY(cudaSetDevice(d->device));
    d->checkFused = 0;
    k_advance_position<<<gridFor(d->approxAtoms, 256), 256, 0, d->stream>>>(dt, 1.0 / d->mass, d->A.cell, d->cellType,
@@ -994,6 +1006,7 @@ static int computeForce(ComdDev* d, int wantEnergy)
 extern "C" int comd_dev_compute_force(ComdDev* d)
 {
    if (!d) return COMD_E_ARG;
+   d->e2ePristine = 0;
    return computeForce(d, 1);
 }
 
@@ -1020,6 +1033,7 @@ extern "C" int comd_dev_set_option(ComdDev* d, const char* key, long value)
    if (!strcmp(key, "force_variant")) { if (value < 0 || value > 1) { comdSetError("force_variant: 0 or 1"); return COMD_E_ARG; } d->optForceVariant = (int)value; return COMD_OK; }
    if (!strcmp(key, "nl_chunks_per_cta")) { if (value < 0 || value > 64) { comdSetError("nl_chunks_per_cta: 0..64"); return COMD_E_ARG; } d->optNlChunksPerCta = (int)value; return COMD_OK; }
    if (!strcmp(key, "overlap")) { d->optOverlap = value != 0; return COMD_OK; }
+   if (!strcmp(key, "e2e_speculate")) { d->e2eSpecArmed = value != 0; return COMD_OK; }
    if (!strcmp(key, "overlap_sms")) { if (value < 0 || value > 148) { comdSetError("overlap_sms: 0..148"); return COMD_E_ARG; } d->optOverlapSms = (int)value; return COMD_OK; }
    if (!strcmp(key, "phase_timing"))
    {
@@ -1061,6 +1075,7 @@ extern "C" int comd_dev_timestep(ComdDev* d, int nSteps, double dt)
 {
    if (!d || nSteps < 0) return COMD_E_ARG;
    if (d->potKind == 0) { comdSetError("comd_dev_timestep: no potential set"); return COMD_E_STATE; }
+   d->e2ePristine = 0;
    CUDA_TRY(cudaSetDevice(d->device));
    for (int it = 0; it < nSteps; ++it)
    {
@@ -1266,30 +1281,54 @@ extern "C" int comd_host_free(void* p)
    return COMD_OK;
 }
 
+// the inputs of a speculative call against what the previous call handed out, bit for bit
+struct EqualArrays { const double* a[9]; const double* b[9]; };
+__global__ void __launch_bounds__(256)
+k_e2e_equal(EqualArrays Q, const int* __restrict__ ga, const int* __restrict__ gb, int n, int* __restrict__ flag)
+{
+   bool bad = false;
+   for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x)
+   {
+      bad |= ga[t] != gb[t];
+      #pragma unroll
+      for (int k = 0; k < 9; ++k) bad |= __double_as_longlong(Q.a[k][t]) != __double_as_longlong(Q.b[k][t]);
+   }
+   if (bad) *flag = 1;
+}
+
+static bool rangesOverlap(const void* a, const void* b, size_t bytes)
+{
+   const char* x = static_cast<const char*>(a); const char* y = static_cast<const char*>(b);
+   return x && y && x < y + bytes && y < x + bytes;
+}
+
 // End-to-end step through HOST buffers: one full timestep() whose inputs (gid, r, p, f at
 // time t) start in host memory and whose results (gid, r, p, f, U at t+dt, device order, local
 // atoms only) end there.  bench.py times this as `e2e`.  Buffers obtained from comd_host_alloc
 // (pinned) are copied directly; pageable ones go through a pinned staging area.  The ghost-free
 // result is compacted on the device, so only local atoms cross PCIe.
-extern "C" int comd_dev_step_host(ComdDev* d, int n, double dt,
-                                  const int* gidIn, const double* rIn[3], const double* pIn[3], const double* fIn[3],
-                                  int* nOut, int* gidOut, double* rOut[3], double* pOut[3], double* fOut[3], double* UOut,
-                                  double eLocal[2])
+//
+// Three ways through it, cheapest first:
+//  * speculative (one rank, pinned buffers, the call follows another comd_dev_step_host call with nothing
+//    in between): the device already holds what it handed out last time, so the step starts at once while
+//    the inputs are still crossing PCIe on their own stream; a kernel then compares them bit for bit with
+//    the previous results.  Equal -> the step that ran is the step that was asked for.  Different -> the
+//    step is redone from the uploaded inputs (full path) and speculation is switched off for this handle.
+//    An output buffer may be the input buffer of the same quantity (in-place update): each result is
+//    copied out only after the upload of the array it may overwrite has finished.
+//  * resume: same atoms in the same order and none further than skin/2 from the list's snapshot -> the
+//    inputs are scattered to their rows, sort and list are kept.
+//  * full: new atoms; re-bin, sort, rebuild.
+static int stepHostImpl(ComdDev* d, int n, double dt, bool inputsOnDevice,
+                        const int* gidIn, const double* const in[9],
+                        int* nOut, int* gidOut, double* const outPtr[10], double eLocal[2])
 {
-   if (!d || n <= 0 || !gidIn || !rIn || !pIn || !fIn) { comdSetError("comd_dev_step_host: bad argument"); return COMD_E_ARG; }
-   if (n > d->cap) { comdSetError("comd_dev_step_host: %d atoms > capacity %ld", n, d->cap); return COMD_E_CAPACITY; }
-   if (d->potKind == 0) { comdSetError("comd_dev_step_host: no potential set"); return COMD_E_STATE; }
-   CUDA_TRY(cudaSetDevice(d->device));
    cudaStream_t s = d->stream;
    const long cap = d->cap;
    AtomArrays& A = d->A;
-   const double* in[9] = { rIn[0], rIn[1], rIn[2], pIn[0], pIn[1], pIn[2], fIn[0], fIn[1], fIn[2] };
    double* devIn[9] = { A.r[0], A.r[1], A.r[2], A.p[0], A.p[1], A.p[2], d->f[0], d->f[1], d->f[2] };
-   bool pinnedIn = isPinned(gidIn);
-   for (int k = 0; k < 9; ++k) pinnedIn = pinnedIn && isPinned(in[k]);
-   double* outPtr[10] = { rOut ? rOut[0] : nullptr, rOut ? rOut[1] : nullptr, rOut ? rOut[2] : nullptr,
-                          pOut ? pOut[0] : nullptr, pOut ? pOut[1] : nullptr, pOut ? pOut[2] : nullptr,
-                          fOut ? fOut[0] : nullptr, fOut ? fOut[1] : nullptr, fOut ? fOut[2] : nullptr, UOut };
+   bool pinnedIn = inputsOnDevice || isPinned(gidIn);
+   for (int k = 0; k < 9 && !inputsOnDevice; ++k) pinnedIn = pinnedIn && isPinned(in[k]);
    bool pinnedOut = !gidOut || isPinned(gidOut);
    for (int k = 0; k < 10; ++k) pinnedOut = pinnedOut && (!outPtr[k] || isPinned(outPtr[k]));
    if (!pinnedIn || !pinnedOut)
@@ -1306,56 +1345,98 @@ extern "C" int comd_dev_step_host(ComdDev* d, int n, double dt,
    double* st = d->hStage;
    const int nRows = d->g.n[1] * d->g.n[2];
    if (!d->rowTab) CUDA_TRY(cudaMalloc(&d->rowTab, (2 * (size_t)nRows + 2) * sizeof(int)));
-   if (!d->e2eScratch) CUDA_TRY(cudaMalloc(&d->e2eScratch, (size_t)cap * 4 * sizeof(double)));
-   int* rowBeg = d->rowTab; int* rowOff = d->rowTab + nRows;
-   // ---- inputs land in scratch (B is free between sorts): gid and r first, they decide the path
-   AtomArrays& S = d->B;
-   double* scr[9] = { S.r[0], S.r[1], S.r[2], S.p[0], S.p[1], S.p[2], d->e2eScratch, d->e2eScratch + cap, d->e2eScratch + 2 * cap };
+   if (!d->e2eU)
    {
-      const int* src = gidIn;
-      if (!pinnedIn) { memcpy(st + 9 * cap, gidIn, n * sizeof(int)); src = reinterpret_cast<const int*>(st + 9 * cap); }
-      CUDA_TRY(cudaMemcpyAsync(S.gid, src, n * sizeof(int), cudaMemcpyHostToDevice, s));
+      CUDA_TRY(cudaMalloc(&d->e2eU, (size_t)cap * 9 * sizeof(double)));
+      CUDA_TRY(cudaMalloc(&d->e2eUgid, (size_t)cap * sizeof(int)));
+      for (int k = 0; k < 2; ++k)
+      {
+         CUDA_TRY(cudaMalloc(&d->e2eOut[k], (size_t)cap * 10 * sizeof(double)));
+         CUDA_TRY(cudaMalloc(&d->e2eOutGid[k], (size_t)cap * sizeof(int)));
+      }
+      CUDA_TRY(cudaMalloc(&d->e2eFlag, sizeof(int)));
+      CUDA_TRY(cudaMallocHost(&d->hE2eFlag, sizeof(int)));
+      CUDA_TRY(cudaStreamCreateWithFlags(&d->copyStream, cudaStreamNonBlocking));
+      CUDA_TRY(cudaStreamCreateWithFlags(&d->upStream, cudaStreamNonBlocking));
+      CUDA_TRY(cudaEventCreateWithFlags(&d->evCopy, cudaEventDisableTiming));
+      CUDA_TRY(cudaEventCreateWithFlags(&d->evUpR, cudaEventDisableTiming));
+      CUDA_TRY(cudaEventCreateWithFlags(&d->evUpP, cudaEventDisableTiming));
+      CUDA_TRY(cudaEventCreateWithFlags(&d->evUp, cudaEventDisableTiming));
    }
+   int* rowBeg = d->rowTab; int* rowOff = d->rowTab + nRows;
+   const int prev = d->e2eCur, nxt = prev ^ 1;
+   double* scr[9]; double* cout[10]; EqualArrays Q;
+   for (int k = 0; k < 9; ++k) { scr[k] = d->e2eU + k * cap; Q.a[k] = scr[k]; Q.b[k] = d->e2eOut[prev] + k * cap; }
+   for (int k = 0; k < 10; ++k) cout[k] = d->e2eOut[nxt] + k * cap;
+   int* ugid = d->e2eUgid; int* coutGid = d->e2eOutGid[nxt];
+
    // Resume path: the previous call left the atoms sorted, the list built and the local-row table of its
    // compaction in place.  If the caller hands the same atoms back in that order and none is further than
    // skin/2 from the list's snapshot, neither the sort nor the list has to be redone: the inputs are
    // scattered to their rows and the step starts from there.  All ranks must agree (the two paths issue
    // different collectives), hence the flag is summed over the ranks.
-   const bool tryResume = d->useNL && d->nlValid && d->e2eOrderValid;
-   for (int k = 0; k < 9; ++k)
-   {
-      const double* src = in[k];
-      if (!pinnedIn) { memcpy(st + k * cap, in[k], n * sizeof(double)); src = st + k * cap; }
-      CUDA_TRY(cudaMemcpyAsync(scr[k], src, n * sizeof(double), cudaMemcpyHostToDevice, s));
-      if (k == 2 && tryResume)
+   const bool tryResume = !inputsOnDevice && d->useNL && d->nlValid && d->e2eOrderValid;
+   bool cross = false;                             // an output buffer over the input buffer of another quantity
+   if (!inputsOnDevice)
+      for (int k = 0; k < 10; ++k)
       {
-         CUDA_TRY(cudaMemsetAsync(d->cnt + C_NLREBUILD, 0, sizeof(int), s));
-         const double h = 0.5 * d->skin;
-         k_e2e_check<<<gridFor(nRows, 1, 148 * 8), 256, 0, s>>>(rowBeg, rowOff, nRows, n, h * h, S.gid, scr[0], scr[1], scr[2],
-            A.gid, d->nlLastR[0], d->nlLastR[1], d->nlLastR[2], d->cnt + C_NLREBUILD); LAUNCH_CHECK(d);
-         int rcf = comdAllreduceFlagDevice(d, d->cnt + C_NLREBUILD);
-         if (rcf != COMD_OK) return rcf;
-         CUDA_TRY(cudaMemcpyAsync(d->hCnt + C_NLREBUILD, d->cnt + C_NLREBUILD, sizeof(int), cudaMemcpyDeviceToHost, s));
+         for (int j = 0; j < 9; ++j) cross = cross || (j != k && rangesOverlap(outPtr[k], in[j], n * sizeof(double)));
+         cross = cross || rangesOverlap(outPtr[k], gidIn, n * sizeof(int));
+         if (k < 9) cross = cross || rangesOverlap(gidOut, in[k], n * sizeof(double));
+      }
+   const bool spec = tryResume && d->e2ePristine && d->e2eSpecArmed && d->nRanks == 1 && pinnedIn && pinnedOut && !cross && n == d->e2eLastM;
+   cudaStream_t u = spec ? d->upStream : s;
+   if (!inputsOnDevice)
+   {
+      if (spec) CUDA_TRY(cudaMemsetAsync(d->e2eFlag, 0, sizeof(int), u));
+      {
+         const int* src = gidIn;
+         if (!pinnedIn) { memcpy(st + 9 * cap, gidIn, n * sizeof(int)); src = reinterpret_cast<const int*>(st + 9 * cap); }
+         CUDA_TRY(cudaMemcpyAsync(ugid, src, n * sizeof(int), cudaMemcpyHostToDevice, u));
+      }
+      for (int k = 0; k < 9; ++k)
+      {
+         const double* src = in[k];
+         if (!pinnedIn) { memcpy(st + k * cap, in[k], n * sizeof(double)); src = st + k * cap; }
+         CUDA_TRY(cudaMemcpyAsync(scr[k], src, n * sizeof(double), cudaMemcpyHostToDevice, u));
+         if (spec && k == 2) CUDA_TRY(cudaEventRecord(d->evUpR, u));
+         if (spec && k == 5) CUDA_TRY(cudaEventRecord(d->evUpP, u));
+         if (!spec && k == 2 && tryResume)
+         {
+            CUDA_TRY(cudaMemsetAsync(d->cnt + C_NLREBUILD, 0, sizeof(int), s));
+            const double h = 0.5 * d->skin;
+            k_e2e_check<<<gridFor(nRows, 1, 148 * 8), 256, 0, s>>>(rowBeg, rowOff, nRows, n, h * h, ugid, scr[0], scr[1], scr[2],
+               A.gid, d->nlLastR[0], d->nlLastR[1], d->nlLastR[2], d->cnt + C_NLREBUILD); LAUNCH_CHECK(d);
+            int rcf = comdAllreduceFlagDevice(d, d->cnt + C_NLREBUILD);
+            if (rcf != COMD_OK) return rcf;
+            CUDA_TRY(cudaMemcpyAsync(d->hCnt + C_NLREBUILD, d->cnt + C_NLREBUILD, sizeof(int), cudaMemcpyDeviceToHost, s));
+         }
+      }
+      if (spec)
+      {
+         k_e2e_equal<<<148 * 8, 256, 0, u>>>(Q, ugid, d->e2eOutGid[prev], n, d->e2eFlag); LAUNCH_CHECK(d);
+         CUDA_TRY(cudaMemcpyAsync(d->hE2eFlag, d->e2eFlag, sizeof(int), cudaMemcpyDeviceToHost, u));
+         CUDA_TRY(cudaEventRecord(d->evUp, u));
       }
    }
    bool resume = false;
-   if (tryResume)
+   if (tryResume && !spec)
    {
       CUDA_TRY(cudaStreamSynchronize(s));
       resume = d->hCnt[C_NLREBUILD] == 0;
    }
    d->e2eOrderValid = 0;
-   if (resume)
+   if (spec) { }                                   // the device holds these atoms already (checked by k_e2e_equal)
+   else if (resume)
    {
-      ScatterArrays Q;
-      for (int k = 0; k < 9; ++k) { Q.in[k] = scr[k]; Q.out[k] = devIn[k]; }
-      k_e2e_scatter<<<gridFor(nRows, 1, 148 * 8), 256, 0, s>>>(Q, rowBeg, rowOff, nRows, A.rq); LAUNCH_CHECK(d);
-      d->e2eResumes++;
+      ScatterArrays W;
+      for (int k = 0; k < 9; ++k) { W.in[k] = scr[k]; W.out[k] = devIn[k]; }
+      k_e2e_scatter<<<gridFor(nRows, 1, 148 * 8), 256, 0, s>>>(W, rowBeg, rowOff, nRows, A.rq); LAUNCH_CHECK(d);
    }
    else
    {
       for (int k = 0; k < 9; ++k) CUDA_TRY(cudaMemcpyAsync(devIn[k], scr[k], n * sizeof(double), cudaMemcpyDeviceToDevice, s));
-      CUDA_TRY(cudaMemcpyAsync(A.gid, S.gid, n * sizeof(int), cudaMemcpyDeviceToDevice, s));
+      CUDA_TRY(cudaMemcpyAsync(A.gid, ugid, n * sizeof(int), cudaMemcpyDeviceToDevice, s));
       CUDA_TRY(cudaMemsetAsync(A.spec, 0, n * sizeof(int), s));
       k_set_int<<<gridFor(n, 256), 256, 0, s>>>(A.cell, cellIndex(d->g, 0, 0, 0), n); LAUNCH_CHECK(d);
       k_set_int<<<1, 1, 0, s>>>(d->cnt + C_NATOMS, n, 1); LAUNCH_CHECK(d);
@@ -1365,27 +1446,24 @@ extern "C" int comd_dev_step_host(ComdDev* d, int n, double dt,
    // ---- the step, in the pieces of comd_dev_timestep, so that results leave as soon as they are final:
    // positions and gids are final after the drift + redistribute and cross PCIe (copy stream) while the
    // force kernels run; momenta, forces and energies follow after the second kick.
-   if (!d->copyStream)
-   {
-      CUDA_TRY(cudaStreamCreateWithFlags(&d->copyStream, cudaStreamNonBlocking));
-      CUDA_TRY(cudaEventCreateWithFlags(&d->evCopy, cudaEventDisableTiming));
-   }
    d->inTimestep = 1;
    int rc = launchKickDrift(d, dt);
    if (rc == COMD_OK) rc = comd_dev_redistribute(d);
    if (rc != COMD_OK) { d->inTimestep = 0; return rc; }
-   AtomArrays& B = d->B;                           // free scratch after the sort / the input scatter
    const double* cin[10] = { d->A.r[0], d->A.r[1], d->A.r[2], d->A.p[0], d->A.p[1], d->A.p[2], d->f[0], d->f[1], d->f[2], d->e };
-   double* cout[10] = { B.r[0], B.r[1], B.r[2], B.p[0], B.p[1], B.p[2], d->e2eScratch, d->e2eScratch + cap, d->e2eScratch + 2 * cap,
-                        d->e2eScratch + 3 * cap };
    k_local_rows<<<1, 1024, 0, s>>>(d->g, d->cellStart, rowBeg, rowOff); LAUNCH_CHECK(d);
    {
       CompactArrays C;
       for (int k = 0; k < 10; ++k) { C.in[k] = cin[k]; C.out[k] = cout[k]; }
-      C.gidIn = d->A.gid; C.gidOut = B.gid;
+      C.gidIn = d->A.gid; C.gidOut = coutGid;
       k_compact_local<0, 3, true><<<gridFor(nRows, 1, 148 * 8), 256, 0, s>>>(C, rowBeg, rowOff, nRows); LAUNCH_CHECK(d);
       CUDA_TRY(cudaEventRecord(d->evCopy, s));
       CUDA_TRY(cudaStreamWaitEvent(d->copyStream, d->evCopy, 0));
+      // A result leaves only after the upload of the same quantity has finished.  In-place callers need that order
+      // (the result lands on the input); for everybody else it keeps the two PCIe directions from running flat out
+      // at the same time, which this platform does not reward: measured on C5 with separate result buffers and no
+      // waits 53.5 ms per call, with the waits 42.3 (59.4 when the step waits for the whole upload first).
+      if (spec) CUDA_TRY(cudaStreamWaitEvent(d->copyStream, d->evUpR, 0));
    }
    // The early copy needs the local count on the host before the step has finished: it is the input count on
    // one rank (nobody can leave) and on any rank whose atoms were resumed and not re-binned in this step.
@@ -1401,7 +1479,7 @@ extern "C" int comd_dev_step_host(ComdDev* d, int n, double dt,
       if (gidOut)
       {
          int* dst = pinnedOut ? gidOut : reinterpret_cast<int*>(st + 10 * cap);
-         CUDA_TRY(cudaMemcpyAsync(dst, B.gid, n * sizeof(int), cudaMemcpyDeviceToHost, d->copyStream));
+         CUDA_TRY(cudaMemcpyAsync(dst, coutGid, n * sizeof(int), cudaMemcpyDeviceToHost, d->copyStream));
       }
    }
    rc = computeForce(d, 1);
@@ -1411,7 +1489,7 @@ extern "C" int comd_dev_step_host(ComdDev* d, int n, double dt,
    {
       CompactArrays C;
       for (int k = 0; k < 10; ++k) { C.in[k] = cin[k]; C.out[k] = cout[k]; }
-      C.gidIn = d->A.gid; C.gidOut = B.gid;
+      C.gidIn = d->A.gid; C.gidOut = coutGid;
       k_compact_local<3, 10, false><<<gridFor(nRows, 1, 148 * 8), 256, 0, s>>>(C, rowBeg, rowOff, nRows); LAUNCH_CHECK(d);
    }
    rc = comd_dev_energy(d, eLocal);                // syncs, refreshes hCnt
@@ -1421,6 +1499,8 @@ extern "C" int comd_dev_step_host(ComdDev* d, int n, double dt,
    if (earlyCopy && m != n) { comdSetError("comd_dev_step_host: %d local atoms after the step, %d on input", m, n); return COMD_E_STATE; }
    for (int k = earlyCopy ? 3 : 0; k < 10; ++k)
    {
+      if (spec && k == 3) CUDA_TRY(cudaStreamWaitEvent(s, d->evUpP, 0));     // p leaves after p has arrived,
+      if (spec && k == 6) CUDA_TRY(cudaStreamWaitEvent(s, d->evUp, 0));      // f and U after everything has
       if (!outPtr[k]) continue;
       double* dst = pinnedOut ? outPtr[k] : st + k * cap;
       CUDA_TRY(cudaMemcpyAsync(dst, cout[k], m * sizeof(double), cudaMemcpyDeviceToHost, s));
@@ -1428,17 +1508,46 @@ extern "C" int comd_dev_step_host(ComdDev* d, int n, double dt,
    if (gidOut && !earlyCopy)
    {
       int* dst = pinnedOut ? gidOut : reinterpret_cast<int*>(st + 10 * cap);
-      CUDA_TRY(cudaMemcpyAsync(dst, B.gid, m * sizeof(int), cudaMemcpyDeviceToHost, s));
+      CUDA_TRY(cudaMemcpyAsync(dst, coutGid, m * sizeof(int), cudaMemcpyDeviceToHost, s));
    }
    CUDA_TRY(cudaStreamSynchronize(s));
    CUDA_TRY(cudaStreamSynchronize(d->copyStream));
+   if (spec)
+   {
+      CUDA_TRY(cudaStreamSynchronize(d->upStream));
+      if (*d->hE2eFlag != 0)
+      {  // not the atoms the device held: the step that ran was the wrong one.  The inputs are complete in the
+         // landing area (and possibly overwritten on the host by now): redo from there, never speculate again.
+         d->e2eSpecArmed = 0;
+         return stepHostImpl(d, n, dt, true, gidIn, in, nOut, gidOut, outPtr, eLocal);
+      }
+   }
+   if (spec || resume) d->e2eResumes++;
+   d->e2eCur = nxt; d->e2eLastM = m;
    d->e2eOrderValid = 1;                           // rowTab describes the order the caller now holds
+   d->e2ePristine = 1;
    if (!pinnedOut)
    {
       for (int k = 0; k < 10; ++k) if (outPtr[k]) memcpy(outPtr[k], st + k * cap, m * sizeof(double));
       if (gidOut) memcpy(gidOut, st + 10 * cap, m * sizeof(int));
    }
    return COMD_OK;
+}
+
+extern "C" int comd_dev_step_host(ComdDev* d, int n, double dt,
+                                  const int* gidIn, const double* rIn[3], const double* pIn[3], const double* fIn[3],
+                                  int* nOut, int* gidOut, double* rOut[3], double* pOut[3], double* fOut[3], double* UOut,
+                                  double eLocal[2])
+{
+   if (!d || n <= 0 || !gidIn || !rIn || !pIn || !fIn) { comdSetError("comd_dev_step_host: bad argument"); return COMD_E_ARG; }
+   if (n > d->cap) { comdSetError("comd_dev_step_host: %d atoms > capacity %ld", n, d->cap); return COMD_E_CAPACITY; }
+   if (d->potKind == 0) { comdSetError("comd_dev_step_host: no potential set"); return COMD_E_STATE; }
+   CUDA_TRY(cudaSetDevice(d->device));
+   const double* in[9] = { rIn[0], rIn[1], rIn[2], pIn[0], pIn[1], pIn[2], fIn[0], fIn[1], fIn[2] };
+   double* outPtr[10] = { rOut ? rOut[0] : nullptr, rOut ? rOut[1] : nullptr, rOut ? rOut[2] : nullptr,
+                          pOut ? pOut[0] : nullptr, pOut ? pOut[1] : nullptr, pOut ? pOut[2] : nullptr,
+                          fOut ? fOut[0] : nullptr, fOut ? fOut[1] : nullptr, fOut ? fOut[2] : nullptr, UOut };
+   return stepHostImpl(d, n, dt, false, gidIn, in, nOut, gidOut, outPtr, eLocal);
 }
 
 extern "C" int comd_dev_step_host_stats(ComdDev* d, long* nResumed)

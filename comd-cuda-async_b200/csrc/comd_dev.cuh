@@ -130,9 +130,17 @@ struct ComdDev
    cudaEvent_t evForce[2 * 128]; int nForceEv; cudaEvent_t evT0, evT1; double lastForceMs; long nLaunches;   // force-time ring (128 calls) + user timer
    // e2e staging
    double* hStage; long hStageDoubles;
-   int* rowTab; double* e2eScratch;      // local-row table and f/U scratch of the device-side compaction
+   int* rowTab;                          // local-row table of the device-side compaction
+   double* e2eU; int* e2eUgid;           // landing area of the uploaded inputs (9 slabs of cap doubles + gids)
+   double* e2eOut[2]; int* e2eOutGid[2]; // compacted results (10 slabs each) of this call and of the previous one
+   int e2eCur;                           // which of the two holds what the caller was handed last
+   int e2eLastM;                         // ... and how many atoms that was
    cudaStream_t copyStream; cudaEvent_t evCopy;   // results that are final early leave on their own stream (comd_dev_step_host)
+   cudaStream_t upStream; cudaEvent_t evUpR, evUpP, evUp;   // uploads of a speculative call (see comd_dev_step_host)
+   int* e2eFlag; int* hE2eFlag;          // "inputs differ from what the device holds" (device, pinned host)
    int e2eOrderValid;                    // rowTab describes the current sort and the caller holds the atoms in that order
+   int e2ePristine;                      // nothing but comd_dev_step_host has touched the atoms since its last return
+   int e2eSpecArmed;                     // speculation allowed (cleared for good by the first mismatch)
    long e2eResumes;                      // comd_dev_step_host calls served without re-sorting / rebuilding
    // tuning knobs (comd_dev_set_option)
    int optForceVariant;         // 0 = thread-per-atom stencil loop (v1), 1 = tiled TMA/filter/process engine

@@ -153,7 +153,9 @@ int  comd_comm_barrier(ComdDev* dev);                               /* barrierPa
  *   "nl_threads"         list path: cap on the CTA size of the force kernels (multiple of 32)
  *   "overlap"            list path, N > 1: halo exchange overlapped with the interior blocks (default 1)
  *   "overlap_sms"        SMs an overlapped interior launch may fill (default 140 of 148)
- *   "phase_timing"       per-phase CUDA-event timing of comd_dev_timestep, reported on stderr by comd_dev_destroy */
+ *   "phase_timing"       per-phase CUDA-event timing of comd_dev_timestep, reported on stderr by comd_dev_destroy
+ *   "e2e_speculate"      1 (default): a comd_dev_step_host call that follows another one may start from the atoms the
+ *                        device still holds while its inputs are uploaded (see there); 0: always wait for the upload */
 int  comd_dev_set_option(ComdDev* dev, const char* key, long value);
 
 /* ---- measurement hooks (bench.py / tests) ---------------------------------------- */
@@ -180,7 +182,12 @@ int  comd_dev_step_host(ComdDev* dev, int nLocal, double dt,
                         double eLocal[2]);
 /* A caller that hands the atoms of one comd_dev_step_host call to the next (same gids, same order, no
  * position further than skin/2 from the neighbour list's snapshot) is served without re-sorting and
- * without rebuilding the list; anything else takes the full upload path.  *nResumed counts the former. */
+ * without rebuilding the list; anything else takes the full upload path.  *nResumed counts the former.
+ * On one rank, with pinned buffers and no other call on the handle in between, such a call does not wait
+ * for its upload either: the step starts from the atoms the device handed out last time, the uploaded inputs
+ * are compared with them bit for bit, and only if they differ is the step redone from the upload (after
+ * which the handle stops speculating).  A result buffer may be the input buffer of the same quantity
+ * (in-place update); a result buffer over the input of ANOTHER quantity switches the early start off. */
 int  comd_dev_step_host_stats(ComdDev* dev, long* nResumed);
 
 #ifdef __cplusplus

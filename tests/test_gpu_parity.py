@@ -462,6 +462,57 @@ def test_step_host_chained_calls_resume_without_resort(kind):
 
 
 @pytest.mark.parametrize("kind", ["lj", "setfl"])
+def test_step_host_in_place_hand_back_runs_ahead_of_the_upload(kind):
+    """The caller updates its pinned buffers in place (results of call k are the inputs of call k+1, same
+    memory).  On one rank the library starts the step from the atoms it still holds while the upload is in
+    flight and verifies the upload against them afterwards: same bits as the path that waits for the upload
+    (option e2e_speculate 0).  An input that was touched in between must be noticed: the step is redone from
+    the uploaded atoms and matches a library that never speculated."""
+    n = 8
+    orc = oracle_sim(KINDS[kind], n, delta=0.05, temperature=600.0)
+    a = orc.atoms()
+    dev0, _ = device_for(orc, (n, n, n), nl_skin=0.1)
+    dev0.upload(a["gid"], a["r"], a["p"])
+    dev0.compute_force()
+    d0 = dev0.download()
+    dev0.close()
+    cols = lambda x: [np.ascontiguousarray(x[:, k]) for k in range(3)]
+    snap = lambda o, m: dict(gid=o["gid"][:m].copy(), r=[x[:m].copy() for x in o["r"]], p=[x[:m].copy() for x in o["p"]],
+                             f=[x[:m].copy() for x in o["f"]], U=o["U"][:m].copy())
+    runs = []
+    for speculate in (1, 0):
+        dev, _ = device_for(orc, (n, n, n), nl_skin=0.1)
+        dev.set_option("e2e_speculate", speculate)
+        m, o, e = dev.step_host(1.0, d0["gid"], cols(d0["r"]), cols(d0["p"]), cols(d0["f"]))
+        for _ in range(6):                         # views of the pinned result buffers: in place
+            m, o, e = dev.step_host(1.0, o["gid"][:m], [x[:m] for x in o["r"]], [x[:m] for x in o["p"]], [x[:m] for x in o["f"]])
+        assert dev.step_host_resumed() == 6
+        before = snap(o, m)
+        o["p"][0][:m] *= 1.0 + 1e-3                 # a thermostat touches the momenta between two calls
+        touched = snap(o, m)
+        m2, o2, e2 = dev.step_host(1.0, o["gid"][:m], [x[:m] for x in o["r"]], [x[:m] for x in o["p"]], [x[:m] for x in o["f"]])
+        after = snap(o2, m2)
+        runs.append((before, e, touched, after, e2, dev.step_host_resumed()))
+        dev.close()
+    (b1, e1, t1, a1, f1, r1), (b0, e0, t0, a0, f0, r0) = runs
+    for k in ("gid", "U"):
+        assert np.array_equal(b1[k], b0[k]), k
+    for k in ("r", "p", "f"):
+        for c in range(3):
+            assert np.array_equal(b1[k][c], b0[k][c]), (k, c)
+    assert e1 == e0
+    assert r1 == 6 and r0 == 7                      # speculation lost once and redid the step; the waiting path resumed
+    # after the touch: full path (new sort, new list) against resume -> same atoms, round-off apart
+    o1 = np.argsort(a1["gid"]); o0 = np.argsort(a0["gid"])
+    assert np.array_equal(a1["gid"][o1], a0["gid"][o0])
+    for k, tol in (("r", 1e-14), ("p", 1e-12), ("f", 1e-11)):
+        for c in range(3):
+            assert rel_err(a1[k][c][o1], a0[k][c][o0]) <= tol, (k, c)
+    assert rel_err(a1["U"][o1], a0["U"][o0]) <= 1e-12
+    assert abs(sum(f1) - sum(f0)) <= 1e-12 * abs(sum(f0))
+
+
+@pytest.mark.parametrize("kind", ["lj", "setfl"])
 def test_neighbor_list_non_cubic_box(kind):
     """6 x 9 x 13 unit cells: different cell counts per axis, work blocks ragged against every face."""
     nxyz = (6, 9, 13)
