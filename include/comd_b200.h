@@ -151,6 +151,7 @@ int  comd_comm_barrier(ComdDev* dev);                               /* barrierPa
  *   "energy_every_step"  list path: per-atom EAM pair energies at every step of comd_dev_timestep (default 0)
  *   "nl_block"           list path: cells per work block as bx*10000 + by*100 + bz (by*bz <= 32), 0 = auto
  *   "nl_threads"         list path: cap on the CTA size of the force kernels (multiple of 32)
+ *   "nl_chunks_per_cta"  list path: work chunks per persistent CTA handed out through the global counter (default 32)
  *   "overlap"            list path, N > 1: halo exchange overlapped with the interior blocks (default 1)
  *   "overlap_sms"        SMs an overlapped interior launch may fill (default 140 of 148)
  *   "phase_timing"       per-phase CUDA-event timing of comd_dev_timestep, reported on stderr by comd_dev_destroy

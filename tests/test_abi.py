@@ -44,3 +44,13 @@ def test_geometry_matches_reference_arithmetic():
         g = pycomd.make_geometry([n * lat] * 3, cutoff)
         assert list(g.gridSize) == [grid] * 3
         assert g.boxSize[0] >= cutoff
+
+
+def test_every_option_key_is_documented_in_the_header():
+    """comd_dev_set_option keys are part of the boundary: each key the library accepts is listed in the header."""
+    core = open(os.path.join(ROOT, "comd-cuda-async_b200", "csrc", "comd_core.cu")).read()
+    keys = set(re.findall(r'strcmp\(key, "([a-z_0-9]+)"\)', core))
+    assert len(keys) >= 8
+    header = open(os.path.join(ROOT, "include", "comd_b200.h")).read()
+    missing = sorted(k for k in keys if '"%s"' % k not in header)
+    assert not missing, missing
