@@ -57,3 +57,29 @@ def test_driver_async_flag_gives_the_same_trace(tmp_path):
     a = trace(run(os.path.join(PKG, "CoMD-b200"), args, tmp_path))
     b = trace(run(os.path.join(PKG, "CoMD-b200"), args + ["-a", "1"], tmp_path))
     assert a == b and len(a) == 4
+
+
+@pytest.mark.parametrize("method", ["thread_atom", "thread_atom_nl"])
+def test_driver_reproduces_the_trace_the_reference_published(tmp_path, method):
+    """The one full-size energy trace the reference ships (its own GPU kernels on 16 K20 ranks, EAM Cu_u6 80^3,
+    100 steps; tests/golden/ref_log_eam_cu_u6_80x80x80.txt) against the same command line on one B200.
+    Step 0 agrees in all 12 printed decimals.  Later steps agree to 4e-6 (total), 5.4e-6 (potential) and
+    2.5e-4 (kinetic) relative: the published run is the reference's GPU path, whose trajectory drifts away from
+    the reference's CPU path -- the oracle of this repository -- by that much (the CPU path's total energy reads
+    -3.460522629, -3.460524223, -3.460527823 ... at steps 10, 20, 30, which is what this build prints to 1e-8;
+    the GPU log reads -3.460520822, -3.460517911, -3.460516645).  So the bounds below are what two implementations
+    of the same model owe each other over 100 steps, not the 1e-6 of the CPU-path parity tests above."""
+    subprocess.check_call(["make", "-s", "-C", PKG, "host"])
+    gold = trace(open(os.path.join(ROOT, "tests", "golden", "ref_log_eam_cu_u6_80x80x80.txt")).read())
+    ours = trace(run(os.path.join(PKG, "CoMD-b200"), ["-e", "-x", "80", "-y", "80", "-z", "80", "-d", POTS, "-m", method], tmp_path))
+    assert len(gold) == len(ours) == 11
+    for (s0, et0, eu0, ek0, n0), (s1, et1, eu1, ek1, n1) in zip(ours, gold):
+        assert s0 == s1 and n0 == n1 == 2048000
+        if s0 == 0:
+            assert abs(et0 - et1) <= 1.5e-12 and abs(eu0 - eu1) <= 1.5e-12 and abs(ek0 - ek1) <= 1.5e-12, (et0, et1, eu0, eu1, ek0, ek1)
+            continue
+        assert abs(et0 - et1) <= 1e-5 * abs(et1), (s0, et0, et1)
+        assert abs(eu0 - eu1) <= 1e-5 * abs(eu1), (s0, eu0, eu1)
+        assert abs(ek0 - ek1) <= 5e-4 * abs(ek1), (s0, ek0, ek1)
+    # energy conservation as the reference states it (CoMD.c:914-945): initial vs final total energy
+    assert abs(ours[-1][1] - ours[0][1]) <= 5e-6 * abs(ours[0][1])
