@@ -259,9 +259,6 @@ def main():
         if dist is not None:
             dist.barrier()
 
-    import ctypes
-    cudart = ctypes.CDLL("libcudart.so")
-
     # ---- warm-up, then EXACTLY K timed steps, CUDA events via the library's stream (comd_dev_sync on both sides)
     dev.timestep(args.warmup, dt)
     barrier()
