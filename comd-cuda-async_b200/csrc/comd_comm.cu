@@ -187,12 +187,15 @@ int comdExchangeFprimePhase(ComdDev* d, int ax)
    return rc;
 }
 
-// ghost refresh between neighbour-list rebuilds: same atoms, same order as the last full atom
-// exchange, positions only (the in-place update of unloadAtomsBuffer's hash-table branch,
-// haloExchange.c:1673-1683)
+// ghost refresh between neighbour-list rebuilds: positions of the atoms of the F' halo's cell runs (neighbor.cu),
+// so the message sizes are the F' halo's and share its count cache (the in-place update of unloadAtomsBuffer's
+// hash-table branch, haloExchange.c:1673-1683)
 int comdExchangeRefreshPhase(ComdDev* d, int ax)
 {
-   return exchangePhase(d, ax, d->sendBuf, d->recvBuf, C_SEND0, C_RECV0, 3, d->hAtomCnt, true);
+   const bool cached = (d->fpCntValid & (1 << ax)) != 0;
+   int rc = exchangePhase(d, ax, d->sendBuf, d->recvBuf, C_FPSEND0, C_FPGOT0, 3, d->hFpCnt, cached);
+   if (rc == COMD_OK) d->fpCntValid |= 1 << ax;
+   return rc;
 }
 
 // "if one process has to rebuild its neighbour list, all have to" (neighborList.c:236-244)

@@ -89,7 +89,6 @@ k_pack_atoms(int axis, const double* __restrict__ rx, const double* __restrict__
              const int* __restrict__ cellKey, const unsigned char* __restrict__ cellType,
              const int* __restrict__ shell, int* __restrict__ cnt,
              double* __restrict__ bufM, double* __restrict__ bufP, long msgCap,
-             int* __restrict__ idxM, int* __restrict__ idxP,
              double shMx, double shMy, double shMz, double shPx, double shPy, double shPz)
 {
    const int n = cnt[C_NSHELL];
@@ -116,8 +115,6 @@ k_pack_atoms(int axis, const double* __restrict__ rx, const double* __restrict__
             const long k = b + __popc(m & ((1u << lane) - 1));
             if (k >= msgCap) { atomicOr(&cnt[C_ERR], ERRB_CAPACITY); continue; }
             double* o = (d ? bufP : bufM) + k * COMD_MSG_DOUBLES;
-            int* rec = d ? idxP : idxM;
-            if (rec) rec[k] = i;
             int2 id = make_int2(gid[i], spec[i]);
             o[0] = *reinterpret_cast<double*>(&id);
             o[1] = rx[i] + (d ? shPx : shMx);
@@ -138,7 +135,7 @@ k_unpack_atoms(DevGeom g, const double* __restrict__ buf, const int* __restrict_
                double* __restrict__ px, double* __restrict__ py, double* __restrict__ pz,
                int* __restrict__ gid, int* __restrict__ spec,
                int* __restrict__ cellKey, int* __restrict__ cellCount, int* __restrict__ shell,
-               int* __restrict__ cnt, long cap, int* __restrict__ recIdx)
+               int* __restrict__ cnt, long cap)
 {
    const int n = *nRecvPtr;
    const int lane = threadIdx.x & 31;
@@ -155,7 +152,6 @@ k_unpack_atoms(DevGeom g, const double* __restrict__ buf, const int* __restrict_
       if (!have) continue;
       const long j = b + lane;            // lanes with `have` are a prefix of the warp
       if (j >= cap) { atomicOr(&cnt[C_ERR], ERRB_CAPACITY); continue; }
-      if (recIdx) recIdx[k] = (int)j;
       const double* in = buf + (long)k * COMD_MSG_DOUBLES;
       double w = in[0];
       int2 id = *reinterpret_cast<int2*>(&w);
@@ -264,7 +260,7 @@ k_scatter(const int* __restrict__ cellKey, const int* __restrict__ gid, const in
 __global__ void __launch_bounds__(256)
 k_rank_gather(DevGeom geo, const int* __restrict__ tmpSrc, const int* __restrict__ tmpGid, const int* __restrict__ tmpCell,
               const int* __restrict__ cellStart, const unsigned char* __restrict__ cellType,
-              AtomArrays src, AtomArrays dst, int* __restrict__ cnt, int* __restrict__ poolToSorted)
+              AtomArrays src, AtomArrays dst, int* __restrict__ cnt)
 {
    const int n = cnt[C_NATOMS];
    const int lane = threadIdx.x & 31;
@@ -280,7 +276,6 @@ k_rank_gather(DevGeom geo, const int* __restrict__ tmpSrc, const int* __restrict
          int rank = 0;
          for (int u = b; u < e; ++u) { const int gu = tmpGid[u]; rank += (gu < g) || (gu == g && u < t); }
          const int d = b + rank, s = tmpSrc[t];
-         if (poolToSorted) poolToSorted[s] = d;
          const double x = src.r[0][s], y = src.r[1][s], z = src.r[2][s];
          dst.r[0][d] = x; dst.r[1][d] = y; dst.r[2][d] = z;
          dst.rf[d] = make_float4((float)(x - geo.lMin[0]), (float)(y - geo.lMin[1]), (float)(z - geo.lMin[2]), 0.f);
@@ -538,12 +533,6 @@ extern "C" int comd_dev_create(ComdDev** out, int deviceId, const ComdGeometry* 
       CUDA_TRY(cudaMalloc(&d->fpRecv[k], d->msgCap * sizeof(double)));
    }
    CUDA_TRY(cudaMalloc(&d->runOff, (plane + 2) * 24 * sizeof(int)));
-   for (int f = 0; f < 6; ++f)
-   {
-      CUDA_TRY(cudaMalloc(&d->sendIdx[f], d->msgCap * sizeof(int)));
-      CUDA_TRY(cudaMalloc(&d->recvIdx[f], d->msgCap * sizeof(int)));
-   }
-   CUDA_TRY(cudaMalloc(&d->poolToSorted, cap * sizeof(int)));
    CUDA_TRY(cudaMalloc(&d->nlStat, 2 * sizeof(unsigned long long)));
    CUDA_TRY(cudaMemset(d->nlStat, 0, 2 * sizeof(unsigned long long)));
 
@@ -584,8 +573,7 @@ extern "C" int comd_dev_destroy(ComdDev* d)
    cudaFree(d->cellKey); cudaFree(d->shell); cudaFree(d->tmpSrc); cudaFree(d->tmpGid); cudaFree(d->tmpCell);
    cudaFree(d->scanBlock); cudaFree(d->cnt); cudaFreeHost(d->hCnt); cudaFree(d->redPartial); cudaFree(d->redOut);
    cudaFreeHost(d->hRed); cudaFree(d->rhobar); cudaFree(d->dfEmbed); cudaFree(d->tabMem); cudaFree(d->tPRmem); cudaFree(d->tW[0]); cudaFree(d->tW[1]); cudaFree(d->tDR); cudaFree(d->rvPhi); cudaFree(d->rvRho); cudaFree(d->r3); cudaFree(d->runOff);
-   cudaFree(d->nlWork); cudaFree(d->nlList); cudaFree(d->nlCount); cudaFree(d->nlCountHit); cudaFree(d->poolToSorted); cudaFree(d->nlStat);
-   for (int f = 0; f < 6; ++f) { cudaFree(d->sendIdx[f]); cudaFree(d->recvIdx[f]); }
+   cudaFree(d->nlWork); cudaFree(d->nlList); cudaFree(d->nlCount); cudaFree(d->nlCountHit); cudaFree(d->nlStat);
    for (int k = 0; k < 2; ++k) { cudaFree(d->sendBuf[k]); cudaFree(d->recvBuf[k]); cudaFree(d->fpSend[k]); cudaFree(d->fpRecv[k]); }
    if (d->hStage) cudaFreeHost(d->hStage);
    cudaFree(d->rowTab); cudaFree(d->e2eU); cudaFree(d->e2eUgid); cudaFree(d->e2eFlag);
@@ -640,6 +628,7 @@ extern "C" int comd_dev_set_lj(ComdDev* d, double sigma, double epsilon, double 
       if (d->hostGeom.boxSize[a] < cutoff)
       { comdSetError("comd_dev_set_lj: cell size %g < cutoff %g on axis %d", d->hostGeom.boxSize[a], cutoff, a); return COMD_E_ARG; }
    d->potKind = 1; d->ljSigma = sigma; d->ljEps = epsilon; d->cutoff = cutoff;
+   d->nlValid = 0; d->eValid = 0;                   // a list built for another cutoff is not this potential's list
    return COMD_OK;
 }
 
@@ -737,6 +726,7 @@ extern "C" int comd_dev_set_eam(ComdDev* d, double cutoff, const ComdTable* phi,
       }
    }
    d->potKind = 2; d->cutoff = cutoff; d->eValid = 0;
+   d->nlValid = 0;
    return COMD_OK;
 }
 
@@ -797,7 +787,6 @@ extern "C" int comd_dev_redistribute(ComdDev* d)
       const int fM = 2 * ax, fP = fM + 1;
       k_pack_atoms<<<gridFor(nShellGuess, 256, 148 * 4), 256, 0, s>>>(ax, A.r[0], A.r[1], A.r[2], A.p[0], A.p[1], A.p[2],
          A.gid, A.spec, d->cellKey, d->cellType, d->shell, d->cnt, d->sendBuf[0], d->sendBuf[1], d->msgCap,
-         d->useNL ? d->sendIdx[fM] : nullptr, d->useNL ? d->sendIdx[fP] : nullptr,
          d->shift[fM][0], d->shift[fM][1], d->shift[fM][2], d->shift[fP][0], d->shift[fP][1], d->shift[fP][2]); LAUNCH_CHECK(d);
       int rc = comdExchangeAtomsPhase(d, ax);
       if (rc != COMD_OK) return rc;
@@ -805,8 +794,7 @@ extern "C" int comd_dev_redistribute(ComdDev* d)
       for (int k = 0; k < 2; ++k)
       {
          k_unpack_atoms<<<gridFor(nShellGuess / 8 + 1, 256, 148 * 2), 256, 0, s>>>(g, d->recvBuf[k], d->cnt + C_RECV0 + fM + k,
-            A.r[0], A.r[1], A.r[2], A.p[0], A.p[1], A.p[2], A.gid, A.spec, d->cellKey, d->cellCount, d->shell, d->cnt, d->cap,
-            d->useNL ? d->recvIdx[fM + k] : nullptr);
+            A.r[0], A.r[1], A.r[2], A.p[0], A.p[1], A.p[2], A.gid, A.spec, d->cellKey, d->cellCount, d->shell, d->cnt, d->cap);
          LAUNCH_CHECK(d);
       }
    }
@@ -817,9 +805,10 @@ extern "C" int comd_dev_redistribute(ComdDev* d)
    k_scatter<<<gridFor(nGuess, 256), 256, 0, s>>>(d->cellKey, A.gid, d->cellStart, d->cellFill, d->tmpSrc, d->tmpGid,
                                                    d->tmpCell, d->cnt, d->cap); LAUNCH_CHECK(d);
    k_rank_gather<<<gridFor(nGuess, 256), 256, 0, s>>>(g, d->tmpSrc, d->tmpGid, d->tmpCell, d->cellStart, d->cellType,
-                                                       d->A, d->B, d->cnt, d->useNL ? d->poolToSorted : nullptr); LAUNCH_CHECK(d);
+                                                       d->A, d->B, d->cnt); LAUNCH_CHECK(d);
    AtomArrays t = d->A; d->A = d->B; d->B = t;
    d->nlValid = 0;
+   d->runLayoutValid = 0;
    d->e2eOrderValid = 0;
    d->posDirty = 0;
    if (d->useNL) return comdNeighborAfterSort(d);
@@ -854,6 +843,7 @@ extern "C" int comd_dev_upload_atoms(ComdDev* d, int n, const int* gid, const in
    k_set_int<<<1, 1, 0, s>>>(d->cnt + C_NATOMS, n, 1); LAUNCH_CHECK(d);
    k_set_int<<<1, 1, 0, s>>>(d->cnt + C_ERR, 0, 1); LAUNCH_CHECK(d);
    d->approxAtoms = n; d->approxHasGhosts = 0;
+   d->nlValid = 0; d->e2eOrderValid = 0;            // new atoms: never judge them against the old list's snapshot
    int rc = comd_dev_redistribute(d);
    if (rc != COMD_OK) return rc;
    return syncCounters(d, "comd_dev_upload_atoms");

@@ -121,9 +121,7 @@ struct ComdDev
    int *nlCountHit;             // per atom: list prefix that held every in-cutoff entry in the last pass 1
    int nlRefreshes;             // steps served by a ghost refresh instead of a rebuild
    unsigned long long* nlStat;  // device: [0] stored pairs, [1] max per atom
-   // ghost refresh between rebuilds: per face, sorted-array index of every atom sent / received by the
-   // last full atom exchange (recorded as pool indices, mapped through poolToSorted after the sort)
-   int *sendIdx[6], *recvIdx[6], *poolToSorted;
+   int runLayoutValid;          // d->runOff describes the cell runs of the current sort (halo_runs.cuh; list mode keeps it between rebuilds)
    // reductions
    double *redPartial; double *redOut; double *hRed;
    // stats
@@ -230,12 +228,13 @@ int comdForceLJ(ComdDev* d);
 int comdRefreshShadow(ComdDev* d);
 int comdForceEAM(ComdDev* d);
 int comdFprimeHalo(ComdDev* d);
+int comdHaloRunLayout(ComdDev* d, cudaStream_t s);      // force_eam.cu: run starts/offsets/sizes of the six one-plane halo messages
 int comdNeighborBuildIfNeeded(ComdDev* d);
 int comdCheckErrors(ComdDev* d, const char* where);
 int comdExchangeAtomsPhase(ComdDev* d, int axis);       // comm.cu: moves send buffers to recv buffers (self or NCCL)
 int comdExchangeFprimePhase(ComdDev* d, int axis);
-int comdExchangeRefreshPhase(ComdDev* d, int axis);     // 3 doubles per atom, counts of the last full exchange
+int comdExchangeRefreshPhase(ComdDev* d, int axis);     // 3 doubles per atom of the F' halo's cell runs
 int comdNeighborRefreshOrRebuild(ComdDev* d, int* didRefresh);   // neighbor.cu: the redistributeAtomsGpuNL decision
-int comdNeighborAfterSort(ComdDev* d);                  // neighbor.cu: map recorded pool indices to sorted indices
+int comdNeighborAfterSort(ComdDev* d);                  // neighbor.cu: cell-run layout of the new sort (ghost refresh, F' halo)
 int comdAllreduceMaxFlag(ComdDev* d, int* flag);
 int comdAllreduceFlagDevice(ComdDev* d, int* devFlag); // comm.cu: in-place sum of a device-resident 0/1 flag over the ranks        // comm.cu: OR of a host flag over the ranks

@@ -10,6 +10,7 @@
 //   halo    F' of ghost atoms  : three axis phases, plane by plane (haloExchange.c:1712-1860)
 //   pass 3  per pair r2 <  rc2 : f_i -= (F'_i + F'_j) rho' dr/r
 #include "force_nl.cuh"
+#include "halo_runs.cuh"
 
 // interpolate(), eam.c:557-579, incl. its one-sided clamps
 __device__ __forceinline__ void tableLookup(const DevTable& t, double r, double& f, double& df)
@@ -121,30 +122,7 @@ k_eam_pass3(DevGeom g, DevTable tRho, double rc2,
    }
 }
 
-// ------------------------------------------------------------------ F' halo
-// A face's message is the concatenation of "runs" of consecutive cells, in a canonical
-// order both sides derive from the grid alone; inside a run atoms are in memory order
-// (cell, then gid), which is identical on sender and receiver.
-//   x faces: ny*nz runs of one cell      (send ix = 0 | nx-1, recv ix = -1 | nx,  iy,iz local)
-//   y faces: nz runs of a whole x-row    (send iy = 0 | ny-1, recv iy = -1 | ny,  ix incl. halo, iz local)
-//   z faces: one run = a whole xy-plane  (send iz = 0 | nz-1, recv iz = -1 | nz,  ix,iy incl. halo)
-// (mkForceSendCellList / mkForceRecvCellList, haloExchange.c:1712-1801.)
-struct FpFace { int firstCell, strideA, countA, strideB, countB, cellsPerRun, nRuns; };
-
-__host__ __device__ inline FpFace fpFace(const DevGeom& g, int face, int isRecv)
-{
-   const int ax = face / 2, plus = face % 2;
-   const int PX = g.P[0], PY = g.P[1];
-   int coord;                          // unpadded coordinate of the plane along ax
-   if (!isRecv) coord = plus ? g.n[ax] - 1 : 0; else coord = plus ? g.n[ax] : -1;
-   FpFace f;
-   if (ax == 0) { f.firstCell = cellIndex(g, coord, 0, 0); f.strideA = PX; f.countA = g.n[1]; f.strideB = PX * PY; f.countB = g.n[2]; f.cellsPerRun = 1; }
-   else if (ax == 1) { f.firstCell = cellIndex(g, -1, coord, 0); f.strideA = 0; f.countA = 1; f.strideB = PX * PY; f.countB = g.n[2]; f.cellsPerRun = PX; }
-   else { f.firstCell = cellIndex(g, -1, -1, coord); f.strideA = 0; f.countA = 1; f.strideB = 0; f.countB = 1; f.cellsPerRun = PX * PY; }
-   f.nRuns = f.countA * f.countB;
-   return f;
-}
-
+// ------------------------------------------------------------------ F' halo (message layout: halo_runs.cuh)
 // one block per (face, send|recv): run starts + exclusive offsets + total
 __global__ void __launch_bounds__(1024)
 k_fp_layout(DevGeom g, const int* __restrict__ cellStart, int* __restrict__ runTab, int runStride, int* __restrict__ cnt)
@@ -189,14 +167,6 @@ k_fp_layout(DevGeom g, const int* __restrict__ cellStart, int* __restrict__ runT
    if (t == 0) { runOff[F.nRuns] = carry; cnt[(isRecv ? C_FPRECV0 : C_FPSEND0) + face] = carry; }
 }
 
-// message element m -> run by binary search in runOff, then a straight copy
-__device__ __forceinline__ int fpLocate(const int* __restrict__ runOff, int nRuns, int m)
-{
-   int lo = 0, hi = nRuns;            // runOff[lo] <= m < runOff[hi]
-   while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (runOff[mid] <= m) lo = mid; else hi = mid; }
-   return lo;
-}
-
 __global__ void __launch_bounds__(256)
 k_fp_pack(DevGeom g, int axis, const int* __restrict__ runTab, int runStride, const double* __restrict__ dfEmbed,
           double* __restrict__ bufM, double* __restrict__ bufP, long msgCap, int* __restrict__ cnt)
@@ -237,19 +207,28 @@ k_fp_unpack(DevGeom g, int axis, const int* __restrict__ runTab, int runStride, 
    }
 }
 
+// run starts, offsets and message sizes of all six faces; in list mode the sorted arrays do not move between
+// rebuilds, so the layout of the last sort stays valid (d->runLayoutValid) and is shared with the ghost refresh
+int comdHaloRunLayout(ComdDev* d, cudaStream_t s)
+{
+   if (d->useNL && d->runLayoutValid) return COMD_OK;
+   k_fp_layout<<<12, 1024, 0, s>>>(d->g, d->cellStart, d->runOff, haloRunStride(d->g), d->cnt); LAUNCH_CHECK(d);
+   if (d->useNL) d->runLayoutValid = 1;
+   return COMD_OK;
+}
+
 int comdFprimeHalo(ComdDev* d)
 {
    const DevGeom& g = d->g;
    cudaStream_t s = d->xs;
-   int maxRuns = g.n[1] * g.n[2];
-   if (g.n[2] > maxRuns) maxRuns = g.n[2];
-   const int runStride = maxRuns + 2;
-   k_fp_layout<<<12, 1024, 0, s>>>(g, d->cellStart, d->runOff, runStride, d->cnt); LAUNCH_CHECK(d);
+   const int runStride = haloRunStride(g);
+   int rc = comdHaloRunLayout(d, s);
+   if (rc != COMD_OK) return rc;
    for (int ax = 0; ax < 3; ++ax)
    {
       dim3 grid(d->nRanks > 1 ? 32 : 148, 2);   // ranks > 1: few CTAs, they must fit beside an overlapped force launch
       k_fp_pack<<<grid, 256, 0, s>>>(g, ax, d->runOff, runStride, d->dfEmbed, d->fpSend[0], d->fpSend[1], d->msgCap, d->cnt); LAUNCH_CHECK(d);
-      int rc = comdExchangeFprimePhase(d, ax);
+      rc = comdExchangeFprimePhase(d, ax);
       if (rc != COMD_OK) return rc;
       k_fp_unpack<<<grid, 256, 0, s>>>(g, ax, d->runOff, runStride, d->dfEmbed, d->fpRecv[0], d->fpRecv[1],
                                        d->cnt + C_FPGOT0 + 2 * ax, d->cnt + C_FPGOT0 + 2 * ax + 1, d->cnt, d->useNL ? d->A.rq : nullptr); LAUNCH_CHECK(d);

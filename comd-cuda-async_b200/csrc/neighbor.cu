@@ -12,6 +12,7 @@
 // row-major with a fixed stride, entries are indices into the sorted atom arrays (ghosts
 // included) in ascending order, i.e. cell-major / gid-minor: summation order stays canonical.
 #include "comd_dev.cuh"
+#include "halo_runs.cuh"
 #include <cmath>
 
 #define NL_G 8                  // lanes per atom in the build and force kernels
@@ -129,50 +130,58 @@ k_nl_check(double half2, const double* __restrict__ rx, const double* __restrict
    if (__any_sync(0xffffffffu, hit) && (threadIdx.x & 31) == 0) cnt[C_NLREBUILD] = 1;   // every writer stores the same value
 }
 
-// ---- index bookkeeping after the sort: pool index -> sorted index ---------------------------
-struct IdxLists { int* p[12]; };
+// ---- ghost refresh: positions only, through the canonical cell-run layout of the F' halo (halo_runs.cuh) -------
+// Between rebuilds the sorted arrays do not move, so every face's ghost cells hold exactly the atoms of the
+// neighbour's outermost local plane (incl. the halo cells already filled by the earlier axis phases), in the same
+// (cell, gid) order on both sides: the message is a straight concatenation of cell runs and needs no index lists.
+// This also covers an atom that crossed a rank (or periodic) face at the last rebuild: it lives on as a ghost in
+// the old owner's halo cell and as a local atom in the new owner's boundary cell -- two members of matching runs --
+// so the old owner's copy follows the live atom.  (The first version replayed the send/recv lists of the rebuild's
+// atom exchange; those listed the emigrant's stale halo-cell copy as the SOURCE and overwrote the live atom with it.
+// The reference avoids the case by forcing a second re-bin + exchange whenever a rank received a new local atom,
+// timestep.c:328-351; results are the same, the lists here simply never contain an emigrant.)
 __global__ void __launch_bounds__(256)
-k_nl_map_idx(IdxLists L, const int* __restrict__ poolToSorted, const int* __restrict__ cnt)
-{
-   const int which = blockIdx.y;                                    // 0..5 send faces, 6..11 recv faces
-   const int n = cnt[(which < 6 ? C_SEND0 : C_RECV0 - 6) + which];
-   int* a = L.p[which];
-   for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) a[k] = poolToSorted[a[k]];
-}
-
-// ---- ghost refresh: positions only, the atoms and the order of the last full exchange -------
-__global__ void __launch_bounds__(256)
-k_nl_refresh_pack(int axis, const double* __restrict__ rx, const double* __restrict__ ry, const double* __restrict__ rz,
-                  const int* __restrict__ idxM, const int* __restrict__ idxP, const int* __restrict__ cnt,
-                  double* __restrict__ bufM, double* __restrict__ bufP,
+k_nl_refresh_pack(DevGeom g, int axis, const int* __restrict__ runTab, int runStride,
+                  const double* __restrict__ rx, const double* __restrict__ ry, const double* __restrict__ rz,
+                  double* __restrict__ bufM, double* __restrict__ bufP, long msgCap, int* __restrict__ cnt,
                   double shMx, double shMy, double shMz, double shPx, double shPy, double shPz)
 {
-   const int d = blockIdx.y;
-   const int n = cnt[C_SEND0 + 2 * axis + d];
-   const int* idx = d ? idxP : idxM;
+   const int d = blockIdx.y, face = 2 * axis + d;
+   const FpFace F = fpFace(g, face, 0);
+   const int* runStart = runTab + (long)(2 * face) * 2 * runStride;
+   const int* runOff = runStart + runStride;
+   const int total = runOff[F.nRuns];
+   if (total > msgCap) { if (threadIdx.x == 0 && blockIdx.x == 0) atomicOr(&cnt[C_ERR], ERRB_CAPACITY); return; }
    double* out = d ? bufP : bufM;
    const double sx = d ? shPx : shMx, sy = d ? shPy : shMy, sz = d ? shPz : shMz;
-   for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x)
+   for (int m = blockIdx.x * blockDim.x + threadIdx.x; m < total; m += gridDim.x * blockDim.x)
    {
-      const int i = idx[k];
-      out[3 * (long)k + 0] = rx[i] + sx;                            // same add as loadAtomsBuffer (haloExchange.c:1603-1605)
-      out[3 * (long)k + 1] = ry[i] + sy;
-      out[3 * (long)k + 2] = rz[i] + sz;
+      const int k = fpLocate(runOff, F.nRuns, m);
+      const int i = runStart[k] + (m - runOff[k]);
+      out[3 * (long)m + 0] = rx[i] + sx;                            // same add as loadAtomsBuffer (haloExchange.c:1603-1605)
+      out[3 * (long)m + 1] = ry[i] + sy;
+      out[3 * (long)m + 2] = rz[i] + sz;
    }
 }
 __global__ void __launch_bounds__(256)
-k_nl_refresh_unpack(int axis, double* __restrict__ rx, double* __restrict__ ry, double* __restrict__ rz,
-                    const int* __restrict__ idxM, const int* __restrict__ idxP, const int* __restrict__ cnt,
-                    const double* __restrict__ bufM, const double* __restrict__ bufP, double4* __restrict__ rq)
+k_nl_refresh_unpack(DevGeom g, int axis, const int* __restrict__ runTab, int runStride,
+                    double* __restrict__ rx, double* __restrict__ ry, double* __restrict__ rz,
+                    const double* __restrict__ bufFromM, const double* __restrict__ bufFromP,
+                    const int* __restrict__ nFromM, const int* __restrict__ nFromP, int* __restrict__ cnt, double4* __restrict__ rq)
 {
-   const int d = blockIdx.y;
-   const int n = cnt[C_RECV0 + 2 * axis + d];
-   const int* idx = d ? idxP : idxM;
-   const double* in = d ? bufP : bufM;
-   for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x)
+   const int d = blockIdx.y, face = 2 * axis + d;
+   const FpFace F = fpFace(g, face, 1);
+   const int* runStart = runTab + (long)(2 * face + 1) * 2 * runStride;
+   const int* runOff = runStart + runStride;
+   const int total = runOff[F.nRuns];
+   const int got = d ? *nFromP : *nFromM;
+   if (got != total) { if (threadIdx.x == 0 && blockIdx.x == 0) atomicOr(&cnt[C_ERR], ERRB_FPMISMATCH); return; }
+   const double* in = d ? bufFromP : bufFromM;
+   for (int m = blockIdx.x * blockDim.x + threadIdx.x; m < total; m += gridDim.x * blockDim.x)
    {
-      const int i = idx[k];
-      const double x = in[3 * (long)k + 0], y = in[3 * (long)k + 1], z = in[3 * (long)k + 2];
+      const int k = fpLocate(runOff, F.nRuns, m);
+      const int i = runStart[k] + (m - runOff[k]);                  // a halo cell by construction: never a local atom
+      const double x = in[3 * (long)m + 0], y = in[3 * (long)m + 1], z = in[3 * (long)m + 2];
       rx[i] = x; ry[i] = y; rz[i] = z;
       rq[i] = make_double4(x, y, z, 0.0);
    }
@@ -194,7 +203,7 @@ static int nlAllocate(ComdDev* d)
    // Keep the first allocation: the row stride is sized once from the mean density (a row overflow is reported,
    // ERRB_NLFULL).  Re-deriving it at every rebuild made the stride depend on which counters happened to be
    // on the host (mid-redistribute they are not) and cost a 1.5 GB cudaFree + cudaMalloc inside a time step.
-   if (d->nlList && d->nlRows >= rows) return COMD_OK;
+   if (d->nlList && d->nlRows >= rows && d->nlStride >= stride) return COMD_OK;   // (a larger cutoff + skin re-sizes)
    if (d->nlList) { cudaFree(d->nlList); cudaFree(d->nlCount); cudaFree(d->nlCountHit); for (int k = 0; k < 3; ++k) cudaFree(d->nlLastR[k]); }
    d->nlList = nullptr;
    CUDA_TRY(cudaMalloc(&d->nlList, (size_t)rows * stride * sizeof(int)));
@@ -230,11 +239,8 @@ int comdNeighborBuildIfNeeded(ComdDev* d)
 
 int comdNeighborAfterSort(ComdDev* d)
 {
-   IdxLists L;
-   for (int f = 0; f < 6; ++f) { L.p[f] = d->sendIdx[f]; L.p[6 + f] = d->recvIdx[f]; }
-   dim3 grid(64, 12);
-   k_nl_map_idx<<<grid, 256, 0, d->stream>>>(L, d->poolToSorted, d->cnt); LAUNCH_CHECK(d);
-   return COMD_OK;
+   d->runLayoutValid = 0;                          // new sort: new cell runs (halo_runs.cuh); computed once per rebuild
+   return comdHaloRunLayout(d, d->stream);
 }
 
 // redistributeAtomsGpuNL (timestep.c:278-354): when no local atom has moved more than skin/2 the
@@ -268,17 +274,18 @@ int comdNeighborRefreshOrRebuild(ComdDev* d, int* didRefresh)
       d->xs = d->commStream;
    }
    cudaStream_t x = d->xs;
+   const int runStride = haloRunStride(d->g);
    for (int ax = 0; ax < 3; ++ax)
    {
       const int fM = 2 * ax, fP = fM + 1;
       dim3 grid(d->nRanks > 1 ? 32 : 148, 2);   // ranks > 1: few CTAs, they must fit beside an overlapped force launch
-      k_nl_refresh_pack<<<grid, 256, 0, x>>>(ax, d->A.r[0], d->A.r[1], d->A.r[2], d->sendIdx[fM], d->sendIdx[fP], d->cnt,
-         d->sendBuf[0], d->sendBuf[1], d->shift[fM][0], d->shift[fM][1], d->shift[fM][2],
+      k_nl_refresh_pack<<<grid, 256, 0, x>>>(d->g, ax, d->runOff, runStride, d->A.r[0], d->A.r[1], d->A.r[2],
+         d->sendBuf[0], d->sendBuf[1], d->msgCap, d->cnt, d->shift[fM][0], d->shift[fM][1], d->shift[fM][2],
          d->shift[fP][0], d->shift[fP][1], d->shift[fP][2]); LAUNCH_CHECK(d);
       rc = comdExchangeRefreshPhase(d, ax);
       if (rc != COMD_OK) { d->xs = d->stream; return rc; }
-      k_nl_refresh_unpack<<<grid, 256, 0, x>>>(ax, d->A.r[0], d->A.r[1], d->A.r[2], d->recvIdx[fM], d->recvIdx[fP], d->cnt,
-         d->recvBuf[0], d->recvBuf[1], d->A.rq); LAUNCH_CHECK(d);
+      k_nl_refresh_unpack<<<grid, 256, 0, x>>>(d->g, ax, d->runOff, runStride, d->A.r[0], d->A.r[1], d->A.r[2],
+         d->recvBuf[0], d->recvBuf[1], d->cnt + C_FPGOT0 + 2 * ax, d->cnt + C_FPGOT0 + 2 * ax + 1, d->cnt, d->A.rq); LAUNCH_CHECK(d);
    }
    if (overlap)
    {
@@ -296,7 +303,7 @@ extern "C" int comd_dev_set_neighbor_list(ComdDev* d, int useNeighborList, doubl
    if (!d || skinDistance < 0.0) { comdSetError("comd_dev_set_neighbor_list: bad argument"); return COMD_E_ARG; }
    d->useNL = useNeighborList ? 1 : 0;
    d->skin = skinDistance;
-   d->nlValid = 0;
+   d->nlValid = 0; d->runLayoutValid = 0;
    return COMD_OK;
 }
 

@@ -70,7 +70,13 @@ void initParallel(int* argc, char*** argv)
    const char* job = getenv("COMD_JOB");
    if (!job) job = getenv("MASTER_PORT");
    if (!job) { fprintf(stderr, "initParallel: COMD_JOB or MASTER_PORT must name the job for %d ranks\n", g_nRanks); exit(-1); }
-   snprintf(g_shmName, sizeof g_shmName, "/comd_b200_%s_%d", job, (int)getuid());
+   /* A per-launch nonce in the name: a segment left behind by a crashed run with the same MASTER_PORT and uid
+    * still carries a valid magic, and a non-root rank that opened it before rank 0 had re-created it would wait
+    * on stale counters for ever.  All ranks are children of one launcher (comd-launch, torchrun), so its pid
+    * tells launches apart; COMD_JOB_NONCE overrides it for launchers that interpose a shell per rank. */
+   const char* nonceEnv = getenv("COMD_JOB_NONCE");
+   const long nonce = nonceEnv ? atol(nonceEnv) : (long)getppid();
+   snprintf(g_shmName, sizeof g_shmName, "/comd_b200_%s_%d_%ld", job, (int)getuid(), nonce);
    int fd = -1;
    if (g_rank == 0)
    {
@@ -106,6 +112,8 @@ void initParallel(int* argc, char*** argv)
    else
       while (atomic_load(&g_shm->magic) != SHM_MAGIC) nanosleep(&nap, NULL);
    atomic_fetch_add(&g_shm->attached, 1);
+   /* nobody enters the first barrier before everybody is looking at THIS segment */
+   while (atomic_load(&g_shm->attached) < g_nRanks) nanosleep(&nap, NULL);
    barrierParallel();
 }
 

@@ -346,6 +346,45 @@ def test_neighbor_list_trajectory_matches_link_cell_path(kind):
     assert rel_err(d1["f"], d0["f"]) <= 1e-7
 
 
+@pytest.mark.parametrize("kind", list(KINDS))
+def test_neighbor_list_migration_across_faces_matches_link_cell_path(kind):
+    """The list-path twin of test_migration_and_conservation: a uniform drift carries every atom through cell and
+    periodic faces, so each rebuild ships emigrants and the steps in between run on the in-place ghost refresh.
+    An emigrant lives on as a ghost in its old owner's halo cell; the refresh must move that copy with the live
+    atom and never write a local one (round 1 replayed the rebuild's send lists and reset immigrants to their
+    rebuild-time position on every refresh step).  Same pair set as the link-cell path => same trajectory."""
+    n = 8
+    orc = oracle_sim(KINDS[kind], n, delta=0.05, temperature=600.0)
+    a = orc.atoms()
+    drift = orc.potential()["mass"] * np.array([0.02, 0.01, -0.005])
+    L = n * orc.potential()["lat"]
+    res = []
+    for skin in (None, 0.1):
+        dev, _ = device_for(orc, (n, n, n), nl_skin=skin)
+        dev.upload(a["gid"], a["r"], a["p"] + drift)
+        dev.compute_force()
+        box0 = by_gid(dev.download())["box"]
+        trace = []
+        for _ in range(4):
+            dev.timestep(40, 1.0)
+            d = by_gid(dev.download())
+            assert np.array_equal(d["gid"], np.sort(a["gid"]))            # all there, exactly once
+            assert dev.num_local() == len(a["gid"])
+            trace.append((d, dev.energy()))
+        moved = int(np.sum(trace[-1][0]["box"] != box0))
+        res.append((trace, dev.neighbor_stats() if skin else None, moved))
+        dev.close()
+    (t0, _, moved0), (t1, st, _) = res
+    assert moved0 > len(a["gid"]) // 4                                    # the test did exercise migration
+    assert 4 < st["builds"] < 160                                         # several rebuilds, refresh steps in between
+    for (d0, e0), (d1, e1) in zip(t0, t1):
+        assert abs(sum(e1) - sum(e0)) <= 1e-9 * abs(sum(e0))
+        dr = d1["r"] - d0["r"]
+        dr -= L * np.round(dr / L)                                        # the two paths re-bin (wrap) at different steps
+        assert np.max(np.abs(dr)) <= 1e-8
+        assert rel_err(d1["f"], d0["f"]) <= 1e-6
+
+
 def test_neighbor_list_energy_after_100_steps_vs_reference():
     """C2 (EAM Cu_u6 20^3, 100 steps) through the list path against the reference's own trace (-m cpu_nl)."""
     n = 20
