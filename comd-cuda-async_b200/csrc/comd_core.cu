@@ -485,7 +485,7 @@ extern "C" int comd_dev_create(ComdDev** out, int deviceId, const ComdGeometry* 
       CUDA_TRY(cudaEventCreateWithFlags(&d->evRefresh, cudaEventDisableTiming)); CUDA_TRY(cudaEventCreateWithFlags(&d->evPass1, cudaEventDisableTiming));
       CUDA_TRY(cudaEventCreateWithFlags(&d->evFp, cudaEventDisableTiming)); CUDA_TRY(cudaEventCreateWithFlags(&d->evStepBegin, cudaEventDisableTiming));
       d->xs = d->stream; d->optOverlap = 1; d->phStep = -1;
-      d->e2eSpecArmed = 1;
+      d->e2eSpecArmed = 0;             // opt-in (option e2e_speculate): it only pays when the caller hands back bit-identical buffers
    }
    const long cap = d->cap;
    int rc;
@@ -555,6 +555,8 @@ extern "C" int comd_dev_create(ComdDev** out, int deviceId, const ComdGeometry* 
    d->approxAtoms = 0;
    d->mass = 1.0;
    d->optForceVariant = 1;
+   d->optNlN3 = 1;
+   if (const char* ev = getenv("COMD_NL_N3")) d->optNlN3 = atoi(ev) != 0;
    d->optTileTx = 8;
    if (const char* ev = getenv("COMD_FORCE_VARIANT")) d->optForceVariant = atoi(ev);
    if (const char* ev = getenv("COMD_TILE_TX")) d->optTileTx = atoi(ev);
@@ -739,6 +741,7 @@ int comdCheckErrors(ComdDev* d, const char* where)
    if (e & ERRB_ESCAPE) { comdSetError("%s: an atom moved more than one link cell beyond the local domain in one step", where); return COMD_E_STATE; }
    if (e & ERRB_FPMISMATCH) { comdSetError("%s: F' halo message does not match the ghost population", where); return COMD_E_MISMATCH; }
    if (e & ERRB_TILE) { comdSetError("%s: a force tile exceeds its shared-memory staging capacity (density far above the lattice average)", where); return COMD_E_CAPACITY; }
+   if (e & ERRB_FIXED) { comdSetError("%s: a pair contribution left the fixed-point range of the in-block accumulators (atoms closer than ~1.5 A?)", where); return COMD_E_STATE; }
    if (e & ERRB_NLFULL) { comdSetError("%s: neighbour-list row overflow", where); return COMD_E_CAPACITY; }
    comdSetError("%s: device error bits 0x%x", where, e);
    return COMD_E_STATE;
@@ -774,6 +777,7 @@ extern "C" int comd_dev_redistribute(ComdDev* d)
       int rc = comdNeighborRefreshOrRebuild(d, &didRefresh);
       if (rc != COMD_OK || didRefresh) return rc;
    }
+   NVTX_RANGE("redistribute: re-bin + atom halo + sort");
    const int nGuess = d->approxAtoms > 0 ? d->approxAtoms : (int)d->cap;
    CUDA_TRY(cudaMemsetAsync(d->cellCount, 0, g.nCells * sizeof(int), s));
    CUDA_TRY(cudaMemsetAsync(d->cellFill, 0, g.nCells * sizeof(int), s));
@@ -785,6 +789,7 @@ extern "C" int comd_dev_redistribute(ComdDev* d)
    for (int ax = 0; ax < 3; ++ax)
    {
       const int fM = 2 * ax, fP = fM + 1;
+      NVTX_RANGE(ax == 0 ? "atom halo x: pack / exchange / unpack" : (ax == 1 ? "atom halo y: pack / exchange / unpack" : "atom halo z: pack / exchange / unpack"));
       k_pack_atoms<<<gridFor(nShellGuess, 256, 148 * 4), 256, 0, s>>>(ax, A.r[0], A.r[1], A.r[2], A.p[0], A.p[1], A.p[2],
          A.gid, A.spec, d->cellKey, d->cellType, d->shell, d->cnt, d->sendBuf[0], d->sendBuf[1], d->msgCap,
          d->shift[fM][0], d->shift[fM][1], d->shift[fM][2], d->shift[fP][0], d->shift[fP][1], d->shift[fP][2]); LAUNCH_CHECK(d);
@@ -938,6 +943,17 @@ extern "C" int comd_dev_cell_counts(ComdDev* d, int* nAtomsPerRefBox, int nTotal
    return COMD_OK;
 }
 
+extern "C" int comd_dev_halo_bytes(ComdDev* d, int kind, int face, long* sentBytes, long* receivedBytes)
+{
+   if (!d || face < 0 || face > 5 || kind < 0 || kind > 1) return COMD_E_ARG;
+   CUDA_TRY(cudaSetDevice(d->device));
+   int rc = syncCounters(d, "comd_dev_halo_bytes");
+   const long per = kind == 0 ? COMD_MSG_DOUBLES * (long)sizeof(double) : (long)sizeof(double);
+   if (sentBytes) *sentBytes = per * d->hCnt[(kind == 0 ? C_SEND0 : C_FPSEND0) + face];
+   if (receivedBytes) *receivedBytes = per * d->hCnt[(kind == 0 ? C_RECV0 : C_FPGOT0) + face];
+   return rc;
+}
+
 extern "C" int comd_dev_advance_velocity(ComdDev* d, double dt)
 {
    if (!d) return COMD_E_ARG;
@@ -982,6 +998,7 @@ static int computeForce(ComdDev* d, int wantEnergy)
    CUDA_TRY(cudaSetDevice(d->device));
    if (d->useNL) { int rc = comdNeighborBuildIfNeeded(d); if (rc != COMD_OK) return rc; }
    if (d->posDirty && !d->useNL && d->optForceVariant == 1) { int rc = comdRefreshShadow(d); if (rc != COMD_OK) return rc; }
+   NVTX_RANGE("computeForce");
    const int slot = d->nForceEv % 128;
    CUDA_TRY(cudaEventRecord(d->evForce[2 * slot], d->stream));
    d->wantEnergy = wantEnergy;
@@ -1022,6 +1039,7 @@ extern "C" int comd_dev_set_option(ComdDev* d, const char* key, long value)
    if (!d || !key) return COMD_E_ARG;
    if (!strcmp(key, "force_variant")) { if (value < 0 || value > 1) { comdSetError("force_variant: 0 or 1"); return COMD_E_ARG; } d->optForceVariant = (int)value; return COMD_OK; }
    if (!strcmp(key, "nl_chunks_per_cta")) { if (value < 0 || value > 64) { comdSetError("nl_chunks_per_cta: 0..64"); return COMD_E_ARG; } d->optNlChunksPerCta = (int)value; return COMD_OK; }
+   if (!strcmp(key, "nl_n3")) { d->optNlN3 = value != 0; d->nlValid = 0; return COMD_OK; }
    if (!strcmp(key, "overlap")) { d->optOverlap = value != 0; return COMD_OK; }
    if (!strcmp(key, "e2e_speculate")) { d->e2eSpecArmed = value != 0; return COMD_OK; }
    if (!strcmp(key, "overlap_sms")) { if (value < 0 || value > 148) { comdSetError("overlap_sms: 0..148"); return COMD_E_ARG; } d->optOverlapSms = (int)value; return COMD_OK; }
@@ -1035,7 +1053,9 @@ extern "C" int comd_dev_set_option(ComdDev* d, const char* key, long value)
    if (!strcmp(key, "nl_threads")) { if (value < 32 || value > 768 || value % 32) { comdSetError("nl_threads: multiple of 32 in 32..768"); return COMD_E_ARG; } d->optNlThreads = (int)value; return COMD_OK; }
    if (!strcmp(key, "nl_block")) { const int bx = (int)(value / 10000), by = (int)(value / 100 % 100), bz = (int)(value % 100);
       if (value != 0 && (bx < 1 || by < 1 || bz < 1 || by * bz > 32)) { comdSetError("nl_block: bx*10000 + by*100 + bz with by*bz <= 32, or 0 for auto"); return COMD_E_ARG; }
-      d->optNlBlock[0] = bx; d->optNlBlock[1] = by; d->optNlBlock[2] = bz; return COMD_OK; }
+      d->optNlBlock[0] = bx; d->optNlBlock[1] = by; d->optNlBlock[2] = bz;
+      if (d->optNlN3) d->nlValid = 0;              // in-block pairs are stored once: the list is tied to the block shape
+      return COMD_OK; }
    if (!strcmp(key, "tile_tx")) { if (value < 1 || value > 16) { comdSetError("tile_tx: 1..16"); return COMD_E_ARG; } d->optTileTx = (int)value; return COMD_OK; }
    comdSetError("comd_dev_set_option: unknown key '%s'", key);
    return COMD_E_ARG;
@@ -1044,6 +1064,7 @@ extern "C" int comd_dev_set_option(ComdDev* d, const char* key, long value)
 // first half of a step: p += dt/2 f ; r += dt p/m (timestep.c:62-68), gather copy refreshed
 static int launchKickDrift(ComdDev* d, double dt, bool two = false)
 {
+   NVTX_RANGE("kick + drift");
    const bool check = d->useNL && d->nlValid;
    const double h = 0.5 * d->skin;
    const int grid = gridFor(d->approxAtoms, 256);

@@ -10,10 +10,50 @@
 //     recovered by refBoxOfCell() whenever ids cross the C ABI.
 #pragma once
 #include <cuda_runtime.h>
+#include <nvtx3/nvToolsExt.h>
 #include <stdint.h>
 #include "../../include/comd_b200.h"
 
-#define COMD_MSG_DOUBLES 7          // AtomMsg on the wire: {gid|species}, r[3], p[3] = 56 B (haloExchange.h:32-38)
+// ---- precision (mytype.h:8-20; the reference's Makefile:73-77 switches -DCOMD_DOUBLE / -DCOMD_SINGLE) --------------
+// real_t is the type of every per-atom quantity, table and message on the device and across the C ABI (comd_real).
+// R(x) writes a literal of that type: in the double build it is the literal itself, so the FP64 code is unchanged.
+#ifdef COMD_SINGLE
+typedef float real_t; typedef float2 real2; typedef float4 real4;
+#define R(x) x##f
+#define make_real2 make_float2
+#define make_real4 make_float4
+#define COMD_NCCL_REAL 7            // ncclFloat32
+#define COMD_MSG_REALS 8            // AtomMsg on the wire: gid, species, r[3], p[3] = 32 B (haloExchange.h:32-38 with float real_t)
+__device__ __forceinline__ real_t mulRn(real_t a, real_t b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ real_t addRn(real_t a, real_t b) { return __fadd_rn(a, b); }
+#else
+typedef double real_t; typedef double2 real2; typedef double4 real4;
+#define R(x) x
+#define make_real2 make_double2
+#define make_real4 make_double4
+#define COMD_NCCL_REAL 8            // ncclFloat64
+#define COMD_MSG_REALS 7            // AtomMsg on the wire: {gid|species}, r[3], p[3] = 56 B (haloExchange.h:32-38)
+__device__ __forceinline__ real_t mulRn(real_t a, real_t b) { return __dmul_rn(a, b); }
+__device__ __forceinline__ real_t addRn(real_t a, real_t b) { return __dadd_rn(a, b); }
+#endif
+// identity of an atom inside a message: FP64 packs {gid, species} into one 8-byte slot, FP32 uses one 4-byte slot each
+__device__ __forceinline__ void msgPutId(real_t* o, int gid, int spec)
+{
+#ifdef COMD_SINGLE
+   o[0] = __int_as_float(gid); o[1] = __int_as_float(spec);
+#else
+   int2 id = make_int2(gid, spec); o[0] = *reinterpret_cast<double*>(&id);
+#endif
+}
+__device__ __forceinline__ void msgGetId(const real_t* in, int& gid, int& spec)
+{
+#ifdef COMD_SINGLE
+   gid = __float_as_int(in[0]); spec = __float_as_int(in[1]);
+#else
+   double w = in[0]; int2 id = *reinterpret_cast<int2*>(&w); gid = id.x; spec = id.y;
+#endif
+}
+#define COMD_MSG_R0 (COMD_MSG_REALS - 6)   // first position slot of a message record
 #define COMD_MAX_CELL_ATOMS 256     // sanity bound used by the in-cell rank sort
 
 // device counters (ints)
@@ -39,6 +79,7 @@ enum {
 #define ERRB_CELLFULL  4   // a cell holds more than COMD_MAX_CELL_ATOMS atoms
 #define ERRB_FPMISMATCH 8  // F' halo: message length != ghost population
 #define ERRB_NLFULL    16  // neighbour list row overflow
+#define ERRB_FIXED     64  // a pair contribution outside the fixed-point range of the in-block accumulators (force_n3.cuh)
 #define ERRB_TILE      32  // a force tile's stencil rows exceed the shared-memory staging capacity
 #define COMD_PAD       16  // slack elements behind every per-atom array (aligned TMA over-read)
 
@@ -52,17 +93,17 @@ struct DevGeom
    int n[3];            // local cells per axis
    int P[3];            // padded
    int nCells;          // padded total
-   double lMin[3], lMax[3], inv[3];
+   real_t lMin[3], lMax[3], inv[3];
 };
 
-struct DevTable { int n; double x0, invDx; const double* v; /* entry 0; valid [-1,n+1] */ };
+struct DevTable { int n; real_t x0, invDx; const real_t* v; /* entry 0; valid [-1,n+1] */ };
 
 struct AtomArrays
 {
-   double *r[3], *p[3];
+   real_t *r[3], *p[3];
    int *gid, *spec, *cell;
    float4 *rf;                  // FP32 shadow of r relative to localMin (filter stage of the force tiles)
-   double4 *rq;                 // gather copy {x, y, z, F'(rho)}: one 32-byte sector per neighbour visit (list kernels)
+   real4 *rq;                   // gather copy {x, y, z, F'(rho)}: one 32-byte sector per neighbour visit (list kernels)
 };
 
 struct ComdDev
@@ -71,12 +112,12 @@ struct ComdDev
    cudaStream_t stream;
    DevGeom g;
    ComdGeometry hostGeom;
-   double shift[6][3];          // PBC shift added when packing for face f (haloExchange.c:310-323)
+   real_t shift[6][3];          // PBC shift added when packing for face f (haloExchange.c:310-323)
    int nbrRank[6];
    int rank, nRanks;
    long cap;                    // atom capacity of every per-atom array
    AtomArrays A, B;             // current (sorted) and staging
-   double *f[3], *e;            // forces, per-atom potential energy (eV)
+   real_t *f[3], *e;            // forces, per-atom potential energy (eV)
    int *cellStart;              // nCells+1
    int *cellCount, *cellFill;   // nCells
    unsigned char* cellType;     // nCells
@@ -90,32 +131,34 @@ struct ComdDev
    int approxHasGhosts;         // approxAtoms counts ghosts too (set from the device counter) or only locals (set from an upload)
    // messages
    long msgCap;                 // atoms per face message
-   double *sendBuf[2], *recvBuf[2];
-   double *fpSend[2], *fpRecv[2];
+   real_t *sendBuf[2], *recvBuf[2];
+   real_t *fpSend[2], *fpRecv[2];
    int *runOff;                 // F' run offsets scratch
    // potential
    int potKind;                 // 0 none, 1 LJ, 2 EAM
    double mass;
    double ljSigma, ljEps, cutoff;
    DevTable tPhi, tRho, tF;
-   double *tabMem;
-   double2 *tPRmem, *tPR;                // interleaved {phi,rho} when both tables share one grid (entry 0), else NULL
-   double2 *tW[2];                       // two copies of the interleaved table, the second shifted by one entry: the 64-byte
+   real_t *tabMem;
+   real2 *tPRmem, *tPR;                // interleaved {phi,rho} when both tables share one grid (entry 0), else NULL
+   real2 *tW[2];                        // two copies of the interleaved table, the second shifted by one entry: the 64-byte
                                          // window [i-1, i+2] of any lookup is 32-byte aligned in one of them (two 256-bit loads)
-   double2 *tDR;                         // pass 3: {g1, g2-g1} of rho per interval (one 128-bit load), entry 0
+   real2 *tDR;                           // pass 3: {g1, g2-g1} of rho per interval (one 128-bit load), entry 0
    // list path: one 32-byte record per interval, so every table lookup is ONE sector (LDG.E.256)
-   double4 *rvPhi, *rvRho;               // {T[i], g1, T[i+1]+T[i-1]-2T[i], g2-g1}: value and derivative of one table
-   double4 *r3;                          // {g1, g2-g1} of phi and of rho side by side (same grid only, else NULL)
+   real4 *rvPhi, *rvRho;                 // {T[i], g1, T[i+1]+T[i-1]-2T[i], g2-g1}: value and derivative of one table
+   real4 *r3;                            // {g1, g2-g1} of phi and of rho side by side (same grid only, else NULL)
    int wantEnergy;                       // this force evaluation also produces per-atom potential energies
    int eValid;                           // d->e holds the energies of the current configuration
    int optEnergyEveryStep;               // comd_dev_timestep: energies at every step (1) or only at the last one (0, default)
    int optNlThreads;                     // CTA size of the list force kernels
    int optNlBlock[3];                    // cells per work block of the list force kernels (0 = auto)
-   double *rhobar, *dfEmbed;
+   real_t *rhobar, *dfEmbed;
    // neighbour list
    int useNL; double skin;
-   int *nlList; int *nlCount; int nlStride; int nlMax; double* nlLastR[3]; int nlBuilds; int nlValid;
+   int *nlList; int *nlCount; int nlStride; int nlMax; real_t* nlLastR[3]; int nlBuilds; int nlValid;
    long nlRows;                 // rows allocated in nlList
+   int optNlN3;                          // 1 (default): pairs inside a work block are evaluated once for both atoms (force_n3.cuh)
+   int nlN3Shape[3];                     // block shape the current list was built for (0 = full list)
    int optNlChunksPerCta;                // target work chunks per CTA of the list force kernels (0 = default 32)
    int *nlWork; unsigned nlWorkSeq;      // work counters of the list force kernels (one per launch, ring of 64)
    int *nlCountHit;             // per atom: list prefix that held every in-cutoff entry in the last pass 1
@@ -127,10 +170,10 @@ struct ComdDev
    // stats
    cudaEvent_t evForce[2 * 128]; int nForceEv; cudaEvent_t evT0, evT1; double lastForceMs; long nLaunches;   // force-time ring (128 calls) + user timer
    // e2e staging
-   double* hStage; long hStageDoubles;
+   real_t* hStage; long hStageDoubles;
    int* rowTab;                          // local-row table of the device-side compaction
-   double* e2eU; int* e2eUgid;           // landing area of the uploaded inputs (9 slabs of cap doubles + gids)
-   double* e2eOut[2]; int* e2eOutGid[2]; // compacted results (10 slabs each) of this call and of the previous one
+   real_t* e2eU; int* e2eUgid;           // landing area of the uploaded inputs (9 slabs of cap doubles + gids)
+   real_t* e2eOut[2]; int* e2eOutGid[2]; // compacted results (10 slabs each) of this call and of the previous one
    int e2eCur;                           // which of the two holds what the caller was handed last
    int e2eLastM;                         // ... and how many atoms that was
    cudaStream_t copyStream; cudaEvent_t evCopy;   // results that are final early leave on their own stream (comd_dev_step_host)
@@ -163,6 +206,11 @@ struct ComdDev
 };
 #define PH_MARK(d, id) do { if ((d)->optPhaseTiming && (d)->phStep >= 0 && (d)->phStep < 32) cudaEventRecord((d)->evPh[(d)->phStep][id], (d)->stream); } while (0)
 
+// NVTX ranges around the phases of a step, as the reference brackets its halo phases (PUSH_RANGE / POP_RANGE,
+// haloExchange.c:60-90,1503-1521): visible in Nsight Systems / ncu --nvtx, one pointer check when no tool is attached.
+struct NvtxRange { explicit NvtxRange(const char* name) { nvtxRangePushA(name); } ~NvtxRange() { nvtxRangePop(); } };
+#define NVTX_RANGE(name) NvtxRange nvtxRange_##__LINE__(name)
+
 // ---- geometry helpers -----------------------------------------------------------
 __host__ __device__ inline int cellIndex(const DevGeom& g, int ix, int iy, int iz)   // unpadded coords in [-1, n]
 {
@@ -172,7 +220,7 @@ __host__ __device__ inline int cellIndex(const DevGeom& g, int ix, int iy, int i
 // Owner cell of a position: the reference's getBoxFromCoord (linkCells.c:448-480) on the
 // padded grid.  (x - lMin) * inv is a subtract followed by a multiply, which nvcc cannot
 // contract into an FMA, so the floor() argument is bit-identical to the host's.
-__device__ inline int axisCell(double x, double lMin, double lMax, double inv, int n, int& err)
+__device__ inline int axisCell(real_t x, real_t lMin, real_t lMax, real_t inv, int n, int& err)
 {
    int i = (int)floor((x - lMin) * inv);
    if (x < lMax) { if (i == n) i = n - 1; }
@@ -182,7 +230,7 @@ __device__ inline int axisCell(double x, double lMin, double lMax, double inv, i
    return i;
 }
 
-__device__ inline int cellOfPos(const DevGeom& g, double x, double y, double z, int& err)
+__device__ inline int cellOfPos(const DevGeom& g, real_t x, real_t y, real_t z, int& err)
 {
    int ix = axisCell(x, g.lMin[0], g.lMax[0], g.inv[0], g.n[0], err);
    int iy = axisCell(y, g.lMin[1], g.lMax[1], g.inv[1], g.n[1], err);

@@ -9,7 +9,7 @@
 //   pass 2  per local atom     : (F,F') = interp(F, rhobar_i) ; U_i += F ; dfEmbed_i = F'
 //   halo    F' of ghost atoms  : three axis phases, plane by plane (haloExchange.c:1712-1860)
 //   pass 3  per pair r2 <  rc2 : f_i -= (F'_i + F'_j) rho' dr/r
-#include "force_nl.cuh"
+#include "force_n3.cuh"
 #include "halo_runs.cuh"
 
 // interpolate(), eam.c:557-579, incl. its one-sided clamps
@@ -219,6 +219,7 @@ int comdHaloRunLayout(ComdDev* d, cudaStream_t s)
 
 int comdFprimeHalo(ComdDev* d)
 {
+   NVTX_RANGE("F'(rho) halo: pack / exchange / unpack x,y,z");
    const DevGeom& g = d->g;
    cudaStream_t s = d->xs;
    const int runStride = haloRunStride(g);
@@ -243,20 +244,31 @@ int comdForceEAM(ComdDev* d)
    PairParams Q = {};
    Q.rc2 = rc2; Q.tPhi = d->tPhi; Q.tRho = d->tRho; Q.tF = d->tF; Q.tPR = d->tPR; Q.tW0 = d->tPR ? d->tW[0] : nullptr; Q.tW1 = d->tW[1]; Q.tDR = d->tDR;
    Q.rvPhi = d->rvPhi; Q.rvRho = d->rvRho; Q.r3 = d->r3;
+   {  // rhobar never exceeds the domain of F (beyond it the lookup clamps, eam.c:561-571): 2^53 quanta over that domain
+      // leave a factor 4 to the 32-bit high word and let one pair contribute up to 1/4 of the domain
+      const double rhoMax = fabs(d->tF.x0) + (d->tF.n + 1) / d->tF.invDx;
+      int ex = 0; frexp(rhoMax, &ex);                   // rhoMax < 2^ex
+      Q.n3ScaleRho = ldexp(1.0, 53 - ex);
+   }
    if (d->useNL)
    {  // list path: rhobar, F' halo, then every pair force in pass 3 (force_nl.cuh); pair energies on request
       d->eValid = d->wantEnergy;
       const bool overlap = d->nRanks > 1 && d->optOverlap;
       int rc;
-      if (d->refreshInFlight) { rc = launchForceNLSplit<PK_RHO>(d, Q, d->evRefresh); d->refreshInFlight = 0; }
-      else rc = launchForceNL<PK_RHO>(d, Q);
+      nvtxRangePushA("EAM pass 1+2: rhobar, F, F'");
+      const bool n3 = d->nlN3Shape[0] > 0;             // the list stores in-block pairs once (force_n3.cuh)
+      if (d->refreshInFlight) { rc = n3 ? launchForceN3Split<PK_RHO>(d, Q, d->evRefresh) : launchForceNLSplit<PK_RHO>(d, Q, d->evRefresh); d->refreshInFlight = 0; }
+      else rc = n3 ? launchForceN3<PK_RHO>(d, Q) : launchForceNL<PK_RHO>(d, Q);
+      nvtxRangePop();
       if (rc != COMD_OK) return rc;
       PH_MARK(d, 3);
+      NVTX_RANGE("EAM F' halo + pass 3");
       if (!overlap)
       {
          rc = comdFprimeHalo(d);
          if (rc != COMD_OK) return rc;
          PH_MARK(d, 4);
+         if (n3) return d->wantEnergy ? launchForceN3<PK_EAMFE>(d, Q) : launchForceN3<PK_EAMF>(d, Q);
          return d->wantEnergy ? launchForceNL<PK_EAMFE>(d, Q) : launchForceNL<PK_EAMF>(d, Q);
       }
       // F'(rhobar) of the ghosts travels on the exchange stream while pass 3 works on the interior blocks
@@ -268,6 +280,7 @@ int comdForceEAM(ComdDev* d)
       if (rc != COMD_OK) return rc;
       CUDA_TRY(cudaEventRecord(d->evFp, d->commStream));
       PH_MARK(d, 4);
+      if (n3) return d->wantEnergy ? launchForceN3Split<PK_EAMFE>(d, Q, d->evFp) : launchForceN3Split<PK_EAMF>(d, Q, d->evFp);
       return d->wantEnergy ? launchForceNLSplit<PK_EAMFE>(d, Q, d->evFp) : launchForceNLSplit<PK_EAMF>(d, Q, d->evFp);
    }
    d->eValid = 1;

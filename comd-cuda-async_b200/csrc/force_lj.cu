@@ -7,7 +7,7 @@
 //    fr = -4*eps*r6*ir2*(12*r6-6); f_i -= dr*fr; U_i += eLocal       (U in units of 4 eps, halved at the end)
 // Full-neighbour ("gather") form: every local atom accumulates its own force, so no
 // atomics and a fixed summation order (cell-major, gid-minor).
-#include "force_nl.cuh"
+#include "force_n3.cuh"
 
 struct LjParams { double s6, eps, rc2, eShift; };
 
@@ -71,6 +71,14 @@ int comdForceLJ(ComdDev* d)
    {
       PairParams Q = {};
       Q.s6 = P.s6; Q.eps = P.eps; Q.eShift = P.eShift; Q.rc2 = P.rc2;
+      if (d->useNL && d->nlN3Shape[0] > 0)
+      {  // in-block pairs once (force_n3.cuh); the per-atom energies only when somebody can read them
+         d->eValid = d->wantEnergy;
+         const bool split = d->refreshInFlight != 0;
+         d->refreshInFlight = 0;
+         if (d->wantEnergy) return split ? launchForceN3Split<PK_LJ>(d, Q, d->evRefresh) : launchForceN3<PK_LJ>(d, Q);
+         return split ? launchForceN3Split<PK_LJF>(d, Q, d->evRefresh) : launchForceN3<PK_LJF>(d, Q);
+      }
       if (d->useNL && d->refreshInFlight) { d->refreshInFlight = 0; return launchForceNLSplit<PK_LJ>(d, Q, d->evRefresh); }
       return d->useNL ? launchForceNL<PK_LJ>(d, Q) : launchForceTile<PK_LJ>(d, Q, nullptr);
    }

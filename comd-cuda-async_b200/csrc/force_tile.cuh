@@ -64,6 +64,7 @@ struct PairParams
    const double2* tDR;                // pass 3: {g1, g2-g1} of rho per interval
    // list path (force_nl.cuh): 32-byte records, one sector per lookup
    const double4* rvPhi; const double4* rvRho; const double4* r3;
+   double n3ScaleRho;                 // fixed-point scale of the rhobar accumulators (force_n3.cuh)
 };
 
 // ---- PTX helpers: mbarrier + 1-D bulk copy (TMA engine, UBLKCP in SASS) -----------------

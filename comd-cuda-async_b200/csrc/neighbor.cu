@@ -13,6 +13,7 @@
 // included) in ascending order, i.e. cell-major / gid-minor: summation order stays canonical.
 #include "comd_dev.cuh"
 #include "halo_runs.cuh"
+#include "nl_blocks.cuh"
 #include <cmath>
 
 #define NL_G 8                  // lanes per atom in the build and force kernels
@@ -28,11 +29,18 @@
 // Row layout: chunks of 32 entries, each stored transposed -- entry e = 8u + l of a chunk (round u, lane l of
 // the force kernels) sits at 4l + u, so a lane reads the indices of four rounds with one 128-bit load.
 __device__ __forceinline__ int nlSlot(int pos) { return (pos & ~31) | ((pos & 7) << 2) | ((pos >> 3) & 3); }
+// N3 (bx > 0): a pair whose two atoms belong to the same work block of bx*by*bz cells is stored ONCE, on the row of
+// the lower sorted index, tagged with N3_FLAG and the neighbour's (y,z) row inside the block (force_n3.cuh); the
+// row of the higher index skips it -- without loading the position.  Pairs across a block face, and every pair with
+// a ghost, stay on both rows as before.
+#define N3_FLAG     0x80000000u
+#define N3_ROWSHIFT 26
 __global__ void __launch_bounds__(256)
 k_nl_build(DevGeom g, double rc2, double rl2, const double4* __restrict__ rq,
            const int* __restrict__ cell, const unsigned char* __restrict__ cellType, const int* __restrict__ cellStart,
            int* __restrict__ cnt, int* __restrict__ list, int* __restrict__ count, int stride, long rows,
-           double* __restrict__ lx, double* __restrict__ ly, double* __restrict__ lz, unsigned long long* __restrict__ stat)
+           double* __restrict__ lx, double* __restrict__ ly, double* __restrict__ lz, unsigned long long* __restrict__ stat,
+           int bx, int by, int bz)
 {
    __shared__ int farBuf[8][4][NL_FARCAP];
    const unsigned full = 0xffffffffu;
@@ -52,16 +60,34 @@ k_nl_build(DevGeom g, double rc2, double rl2, const double4* __restrict__ rq,
       double4 pi = make_double4(0.0, 0.0, 0.0, 0.0);
       const int i0 = act ? i : 0;                      // a lane without a candidate re-reads its own atom
       if (act) pi = rq[i];
-      int nNear = 0, nFar = 0;
+      // block membership of the 27 stencil cells relative to the atom's own cell (N3)
+      int cx = 0, cy = 0, cz = 0, xSame = 0;
+      if (bx > 0 && act)
+      {
+         cx = c % g.P[0] - 1; cy = (c / g.P[0]) % g.P[1] - 1; cz = c / rowZ - 1;
+         for (int dxc = -1; dxc <= 1; ++dxc)
+         {
+            const int x = cx + dxc;
+            if (x >= 0 && x < g.n[0] && x / bx == cx / bx) xSame |= 1 << (dxc + 1);
+         }
+      }
+      int nNear = 0, nFar = 0, nTwice = 0;
       int* row = list + (long)(act ? i : 0) * stride;
       #pragma unroll 1
       for (int r = 0; r < 9; ++r)
       {
-         int jb = 0, je = 0;
+         int jb = 0, je = 0, b1 = 0, b2 = 0;
+         unsigned tag = 0; bool rowSame = false;
          if (act)
          {
             const int rc = c + ((r % 3) - 1) * rowY + ((r / 3) - 1) * rowZ;
             jb = cellStart[rc - 1]; je = cellStart[rc + 2];
+            if (bx > 0)
+            {
+               const int y = cy + (r % 3) - 1, z = cz + (r / 3) - 1;
+               rowSame = y >= 0 && y < g.n[1] && z >= 0 && z < g.n[2] && y / by == cy / by && z / bz == cz / bz;
+               if (rowSame) { b1 = cellStart[rc]; b2 = cellStart[rc + 1]; tag = N3_FLAG | (unsigned)((y % by) + by * (z % bz)) << N3_ROWSHIFT; }
+            }
          }
          const int maxlen = __reduce_max_sync(full, je - jb);
          // four rounds of 8 candidates per trip: the four 32-byte position loads are issued before any of
@@ -69,11 +95,20 @@ k_nl_build(DevGeom g, double rc2, double rl2, const double4* __restrict__ rq,
          for (int base = 0; base < maxlen; base += NL_U * NL_G)
          {
             double4 pj[NL_U];
+            bool ok[NL_U], both[NL_U];
             #pragma unroll
             for (int u = 0; u < NL_U; ++u)
             {
                const int j = jb + base + u * NL_G + gl;
-               pj[u] = rq[j < je ? j : i0];
+               ok[u] = j < je && j != i;
+               both[u] = false;
+               if (rowSame && ok[u])
+               {  // same block iff the candidate's x cell is (row and block in y,z already are)
+                  const int xs = j < b1 ? 1 : (j < b2 ? 2 : 4);
+                  both[u] = (xSame & xs) != 0;
+                  if (both[u] && j < i) ok[u] = false;             // stored on row j
+               }
+               pj[u] = rq[ok[u] ? j : i0];
             }
             #pragma unroll
             for (int u = 0; u < NL_U; ++u)
@@ -81,16 +116,17 @@ k_nl_build(DevGeom g, double rc2, double rl2, const double4* __restrict__ rq,
                const int j = jb + base + u * NL_G + gl;
                const double dx = pi.x - pj[u].x, dy = pi.y - pj[u].y, dz = pi.z - pj[u].z;
                const double r2 = dx * dx + dy * dy + dz * dz;
-               const bool ok = j < je && j != i;
-               const bool near = ok && r2 <= rc2;
-               const bool far = ok && !near && r2 <= rl2;
+               const bool near = ok[u] && r2 <= rc2;
+               const bool far = ok[u] && !near && r2 <= rl2;
                const unsigned below = (1u << gl) - 1u, grp = (1u << NL_G) - 1u;
                const unsigned mN = (__ballot_sync(full, near) >> (g4 * NL_G)) & grp;
                const unsigned mF = (__ballot_sync(full, far) >> (g4 * NL_G)) & grp;
-               if (near) { const int pos = nNear + __popc(mN & below); if (pos < stride) row[nlSlot(pos)] = j; }
-               if (far) { const int pos = nFar + __popc(mF & below); if (pos < NL_FARCAP) myFar[pos] = j; }
+               const int ent = both[u] ? (int)((unsigned)j | tag) : j;
+               if (near) { const int pos = nNear + __popc(mN & below); if (pos < stride) row[nlSlot(pos)] = ent; }
+               if (far) { const int pos = nFar + __popc(mF & below); if (pos < NL_FARCAP) myFar[pos] = ent; }
                nNear += __popc(mN);
                nFar += __popc(mF);
+               nTwice += (near || far) && both[u];
             }
          }
       }
@@ -105,8 +141,10 @@ k_nl_build(DevGeom g, double rc2, double rl2, const double4* __restrict__ rq,
          if (over) atomicOr(&cnt[C_ERR], ERRB_NLFULL);
          lx[i] = pi.x; ly[i] = pi.y; lz[i] = pi.z;            // lastR snapshot (neighborList.c:176-183)
       }
-      // statistics: one atomic per warp
-      int tot = (act && gl == 0) ? nn : 0, mx = tot;
+      // statistics (pairs counted as a full list would hold them: an in-block pair is two entries' worth): one atomic per warp
+      #pragma unroll
+      for (int o = NL_G / 2; o > 0; o >>= 1) nTwice += __shfl_xor_sync(full, nTwice, o);
+      int tot = (act && gl == 0) ? nn + nTwice : 0, mx = (act && gl == 0) ? nn : 0;
       #pragma unroll
       for (int o = 16; o > 0; o >>= 1) { tot += __shfl_xor_sync(full, tot, o); mx = max(mx, __shfl_xor_sync(full, mx, o)); }
       if (lane == 0) { atomicAdd(&stat[0], (unsigned long long)tot); atomicMax(&stat[1], (unsigned long long)mx); }
@@ -224,13 +262,20 @@ int comdNeighborBuildIfNeeded(ComdDev* d)
       if (d->hostGeom.boxSize[a] < rl)
       { comdSetError("neighbour list: cell size %g < cutoff + skin %g on axis %d (size the link cells on cutoff+skin, CoMD.c:257-268)",
                      d->hostGeom.boxSize[a], rl, a); return COMD_E_ARG; }
+   NVTX_RANGE("neighbour list build");
    int rc = nlAllocate(d);
    if (rc != COMD_OK) return rc;
    cudaStream_t s = d->stream;
    CUDA_TRY(cudaMemsetAsync(d->nlStat, 0, 2 * sizeof(unsigned long long), s));
    const int n = d->approxAtoms > 0 ? d->approxAtoms : (int)d->cap;
+   // N3: the list is tied to the work-block shape of the force kernels (in-block pairs are stored once)
+   const NlBlocks B = nlBlocksFor(d);
+   const bool n3 = d->optNlN3 != 0;
+   if (n3 && d->cap > (1L << N3_ROWSHIFT)) { comdSetError("neighbour list: more than %ld atoms per GPU", 1L << N3_ROWSHIFT); return COMD_E_CAPACITY; }
+   d->nlN3Shape[0] = n3 ? B.bx : 0; d->nlN3Shape[1] = n3 ? B.by : 0; d->nlN3Shape[2] = n3 ? B.bz : 0;
    k_nl_build<<<gridFor((n + 3) / 4, 8, 148 * 8), 256, 0, s>>>(d->g, d->cutoff * d->cutoff, rl * rl, d->A.rq, d->A.cell, d->cellType,
-      d->cellStart, d->cnt, d->nlList, d->nlCount, d->nlStride, d->nlRows, d->nlLastR[0], d->nlLastR[1], d->nlLastR[2], d->nlStat);
+      d->cellStart, d->cnt, d->nlList, d->nlCount, d->nlStride, d->nlRows, d->nlLastR[0], d->nlLastR[1], d->nlLastR[2], d->nlStat,
+      d->nlN3Shape[0], d->nlN3Shape[1], d->nlN3Shape[2]);
    LAUNCH_CHECK(d);
    d->nlValid = 1;
    d->nlBuilds++;
@@ -275,6 +320,7 @@ int comdNeighborRefreshOrRebuild(ComdDev* d, int* didRefresh)
    }
    cudaStream_t x = d->xs;
    const int runStride = haloRunStride(d->g);
+   NVTX_RANGE("ghost refresh: pack / exchange / unpack x,y,z");
    for (int ax = 0; ax < 3; ++ax)
    {
       const int fM = 2 * ax, fP = fM + 1;
@@ -317,5 +363,13 @@ extern "C" int comd_dev_neighbor_stats(ComdDev* d, long* nPairsStored, int* maxP
    if (nPairsStored) *nPairsStored = (long)st[0];
    if (maxPerAtom) *maxPerAtom = (int)st[1];
    if (nBuilds) *nBuilds = d->nlBuilds;
+   return COMD_OK;
+}
+
+extern "C" int comd_dev_neighbor_counters(ComdDev* d, long* nBuilds, long* nRefreshes)
+{
+   if (!d) return COMD_E_ARG;
+   if (nBuilds) *nBuilds = d->nlBuilds;
+   if (nRefreshes) *nRefreshes = d->nlRefreshes;
    return COMD_OK;
 }

@@ -96,6 +96,12 @@ SimFlat* initSimulation(Command cmd)
       exit(-1);
    }
    const int useNL = sim->method == THREAD_ATOM_NL || sim->method == WARP_ATOM_NL;
+   if (printRank())
+   {  /* the reference's method names select two very different kernels here: say which, and what it costs */
+      if (useNL) printf("Force path: neighbour list (-m %s): once-per-pair list kernels, the fast path of this build\n", cmd.method);
+      else printf("Force path: link cells (-m %s): 27-cell stencil over TMA-staged tiles, re-binned every step; expect ~2.5-3x the step time of "
+                  "-m thread_atom_nl (measured on B200: C3 2.49 vs 0.91 ms/step, C5 41 vs 15 ms/step)\n", cmd.method);
+   }
    if ((cmd.ljInterpolation || cmd.spline || cmd.usePairlist) && printRank())
       printf("Note: -I / -P / -L select experimental kernels of the reference that this build does not carry; ignored.\n");
 
@@ -335,6 +341,20 @@ int main(int argc, char** argv)
 
    validateResult(validate, sim);
    profileStop(totalTimer);
+   {  /* algorithmic flop per atom-step: neighbours of an FCC site inside the cutoff x (27 LJ | 93 EAM) + integrator (+ embedding) */
+      const real_t lat = cmd.lat < 0.0 ? sim->pot->lat : cmd.lat, rc = sim->pot->cutoff;
+      int nNbr = 0;
+      const int m = (int)(rc / lat) + 2;
+      for (int i = -2 * m; i <= 2 * m; ++i) for (int j = -2 * m; j <= 2 * m; ++j) for (int k = -2 * m; k <= 2 * m; ++k)
+      {  /* FCC sites = half-integer triples (in units of lat/2) with an even coordinate sum */
+         if ((i + j + k) & 1 || (i == 0 && j == 0 && k == 0)) continue;
+         const real_t r2 = 0.25 * lat * lat * (real_t)(i * i + j * j + k * k);
+         if (r2 <= rc * rc) ++nNbr;
+      }
+      double peak = 0.0;
+      DEV_TRY(comd_dev_fp64_peak(sim->dev, &peak));
+      setRooflineInfo(cmd.doeam ? 93.0 * nNbr + 42.0 : 27.0 * nNbr + 22.0, peak, getNRanks());
+   }
    printPerformanceResults(sim->atoms->nGlobal, sim->printRate);
    printPerformanceResultsYaml(yamlFile);
 

@@ -171,14 +171,21 @@ BasePotential* initEamPot(const char* dir, const char* file, const char* type);
 void eamBcastPotential(EamPotential* pot);
 void interpolate(InterpolationObject* table, real_t r, real_t* f, real_t* df);
 
-/* ---- haloExchange.h: the exchange itself runs on the device; these keep the call sites ---- */
+/* ---- haloExchange.h:63-145: the exchange itself runs on the device; the struct keeps the call sites and the members a
+ * CoMD.c-style caller may touch.  The message buffers live in HBM (the reference's sendBufM/P, recvBufM/P and their _Async
+ * twins have no host counterpart here), so loadBuffer / unloadBuffer do not move data: loadBuffer reports the bytes the
+ * device packed for `face` in the last exchange (the return value haloExchange.h:84 documents), unloadBuffer is a no-op. ---- */
+struct HashTableSt;
 typedef struct HaloExchangeSt
 {
    int nbrRank[6];
    int bufCapacity;
-   int kind;                    /* 0 atoms, 1 F'(rho) */
+   int  (*loadBuffer)(void* parms, void* data, int face, char* buf);
+   void (*unloadBuffer)(void* parms, void* data, int face, int bufSize, char* buf);
    void (*destroy)(void* parms);
    void* parms;
+   struct HashTableSt* hashTable;   /* always NULL: the device keys ghosts by (cell, gid) order, not by a gid hash */
+   int type;                    /* 0 atoms, 1 F'(rho)  (haloExchange.h:111) */
 } HaloExchange;
 HaloExchange* initAtomHaloExchange(Domain* domain, LinkCell* boxes);
 HaloExchange* initForceHaloExchange(Domain* domain, LinkCell* boxes, int useGPU);
@@ -239,6 +246,7 @@ void profileStop(enum TimerHandle handle);
 double getElapsedTime(enum TimerHandle handle);
 void printPerformanceResults(int nGlobalAtoms, int printRate);
 void printPerformanceResultsYaml(FILE* file);
+void setRooflineInfo(double flopPerAtomStep, double fp64PeakTflopsPerGpu, int nRanks);
 #define startTimer(h) profileStart(h)
 #define stopTimer(h)  profileStop(h)
 

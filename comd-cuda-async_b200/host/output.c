@@ -36,7 +36,15 @@ typedef struct
    double minValue, maxValue, average, stdev;
 } Timer;
 static Timer perfTimer[numberOfTimers];
-static struct { double atomRate, atomAllRate, atomsPerUSec; } perfGlobal;
+static struct { double atomRate, atomAllRate, atomsPerUSec, flopPerAtomStep, fp64PeakTflops; int nRanks; } perfGlobal;
+
+/* Figure of merit beside the timers: the algorithmic work of one atom-step (full-neighbour form, FMA = 2,
+ * div = sqrt = 1: 27 flop per LJ neighbour, 93 per EAM neighbour, + integrator / embedding) and the FP64 FMA-pipe peak
+ * measured on this GPU; printPerformanceResults turns the atom rate into a roofline fraction. */
+void setRooflineInfo(double flopPerAtomStep, double fp64PeakTflopsPerGpu, int nRanks)
+{
+   perfGlobal.flopPerAtomStep = flopPerAtomStep; perfGlobal.fp64PeakTflops = fp64PeakTflopsPerGpu; perfGlobal.nRanks = nRanks;
+}
 
 static double now(void)
 {
@@ -120,6 +128,13 @@ void printPerformanceResults(int nGlobalAtoms, int printRate)
    fprintf(screenOut, "\n%s\n Average atom rate:            %6.2f atoms/us\n%s\n\n", bar, perfGlobal.atomsPerUSec, bar);
    /* the headline metric of BASELINE.json in its own unit */
    fprintf(screenOut, " Atom-steps per second:        %.6e\n\n", perfGlobal.atomsPerUSec * 1e6);
+   if (perfGlobal.fp64PeakTflops > 0.0)
+   {
+      const double tf = perfGlobal.atomsPerUSec * 1e6 * perfGlobal.flopPerAtomStep * 1e-12;
+      fprintf(screenOut, " FP64 roofline:                %.3f TFLOP/s algorithmic (%.0f flop/atom-step) of %.2f TFLOP/s measured DFMA peak on %d GPU%s = %.4f\n\n",
+              tf, perfGlobal.flopPerAtomStep, perfGlobal.fp64PeakTflops * perfGlobal.nRanks, perfGlobal.nRanks, perfGlobal.nRanks > 1 ? "s" : "",
+              tf / (perfGlobal.fp64PeakTflops * perfGlobal.nRanks));
+   }
 }
 
 void printPerformanceResultsYaml(FILE* file)
@@ -158,6 +173,12 @@ void printPerformanceResultsYaml(FILE* file)
    fprintf(file, "  AllAtomUpdateRate:\n    AverageRate: %6.2f\n    Units: us/atom\n", perfGlobal.atomAllRate);
    fprintf(file, "  AtomRate:\n    AverageRate: %6.2f\n    Units: atoms/us\n", perfGlobal.atomsPerUSec);
    fprintf(file, "  AtomStepsPerSecond: %.6e\n", perfGlobal.atomsPerUSec * 1e6);
+   if (perfGlobal.fp64PeakTflops > 0.0)
+   {
+      const double tf = perfGlobal.atomsPerUSec * 1e6 * perfGlobal.flopPerAtomStep * 1e-12;
+      fprintf(file, "  RooflineFP64:\n    AlgorithmicFlopPerAtomStep: %.0f\n    AchievedTFlops: %.4f\n    MeasuredPeakTFlopsPerGpu: %.3f\n    Gpus: %d\n    Fraction: %.4f\n",
+              perfGlobal.flopPerAtomStep, tf, perfGlobal.fp64PeakTflops, perfGlobal.nRanks, tf / (perfGlobal.fp64PeakTflops * perfGlobal.nRanks));
+   }
    fprintf(file, "\n");
 }
 

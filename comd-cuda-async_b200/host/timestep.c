@@ -94,10 +94,28 @@ void syncAtomsFromDevice(SimFlat* s)
 }
 
 /* ---- haloExchange.h shims ---- */
+/* loadBuffer / unloadBuffer (haloExchange.h:84,98): `data` is the SimFlat, as for haloExchange() */
+static int loadDeviceBuffer(void* parms, void* data, int face, char* buf)
+{
+   (void)buf;
+   const HaloExchange* h = parms;
+   SimFlat* s = data;
+   long sent = 0, got = 0;
+   if (!s || face < 0 || face > 5) return 0;
+   DEV_TRY(comd_dev_halo_bytes(s->dev, h->type, face, &sent, &got));
+   return (int)sent;
+}
+static void unloadDeviceBuffer(void* parms, void* data, int face, int bufSize, char* buf)
+{
+   (void)parms; (void)data; (void)face; (void)bufSize; (void)buf;   /* unpacked on the device by the exchange itself */
+}
+
 static HaloExchange* makeExchange(Domain* dom, int kind)
 {
    HaloExchange* h = calloc(1, sizeof *h);
-   h->kind = kind;
+   h->type = kind;
+   h->loadBuffer = loadDeviceBuffer; h->unloadBuffer = unloadDeviceBuffer;
+   h->parms = h;                                  /* the sub-class data of this exchange is the exchange itself */
    /* face order x-, x+, y-, y+, z-, z+ (haloExchange.h:20-22) */
    h->nbrRank[0] = processorNum(dom, -1, 0, 0); h->nbrRank[1] = processorNum(dom, +1, 0, 0);
    h->nbrRank[2] = processorNum(dom, 0, -1, 0); h->nbrRank[3] = processorNum(dom, 0, +1, 0);
@@ -125,7 +143,7 @@ HaloExchange* initForceHaloExchange(Domain* dom, LinkCell* boxes, int useGPU)
 void haloExchange(HaloExchange* h, void* data)
 {
    SimFlat* s = data;
-   if (h && h->kind == 1) return;              /* F'(rho): exchanged between pass 2 and pass 3 inside comd_dev_compute_force */
+   if (h && h->type == 1) return;              /* F'(rho): exchanged between pass 2 and pass 3 inside comd_dev_compute_force */
    DEV_TRY(comd_dev_redistribute(s->dev));
 }
 

@@ -47,7 +47,7 @@ ABI_SYMBOLS = [
     "comd_dev_set_neighbor_list", "comd_dev_neighbor_stats", "comd_comm_unique_id", "comd_comm_init",
     "comd_comm_allreduce_sum", "comd_comm_allreduce_sum_int", "comd_comm_barrier", "comd_dev_sync",
     "comd_dev_kernel_stats", "comd_dev_step_host", "comd_dev_fp64_peak", "comd_dev_timer_start", "comd_dev_timer_stop",
-    "comd_dev_set_option", "comd_host_alloc", "comd_host_free", "comd_dev_step_host_stats",
+    "comd_dev_set_option", "comd_host_alloc", "comd_host_free", "comd_dev_step_host_stats", "comd_dev_neighbor_counters", "comd_dev_halo_bytes",
 ]
 
 _lib = None
@@ -82,6 +82,8 @@ def lib():
         L.comd_dev_timestep.argtypes = [C.c_void_p, C.c_int, C.c_double]
         L.comd_dev_set_neighbor_list.argtypes = [C.c_void_p, C.c_int, C.c_double]
         L.comd_dev_neighbor_stats.argtypes = [C.c_void_p, C.POINTER(C.c_long), _ip, _ip]
+        L.comd_dev_neighbor_counters.argtypes = [C.c_void_p, C.POINTER(C.c_long), C.POINTER(C.c_long)]
+        L.comd_dev_halo_bytes.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_long), C.POINTER(C.c_long)]
         L.comd_comm_unique_id.argtypes = [C.c_char_p]
         L.comd_comm_init.argtypes = [C.c_void_p, C.c_char_p, C.c_int, C.c_int]
         L.comd_comm_allreduce_sum.argtypes = [C.c_void_p, _dp, C.c_int]
@@ -280,6 +282,16 @@ class Device:
         a = C.c_long(); b = C.c_int(); c = C.c_int()
         _chk(lib().comd_dev_neighbor_stats(self.h, C.byref(a), C.byref(b), C.byref(c)))
         return dict(pairs=a.value, max_per_atom=b.value, builds=c.value)
+
+    def neighbor_counters(self):
+        a = C.c_long(); b = C.c_long()
+        _chk(lib().comd_dev_neighbor_counters(self.h, C.byref(a), C.byref(b)))
+        return dict(builds=a.value, refreshes=b.value)
+
+    def halo_bytes(self, kind, face):
+        a = C.c_long(); b = C.c_long()
+        _chk(lib().comd_dev_halo_bytes(self.h, kind, face, C.byref(a), C.byref(b)))
+        return a.value, b.value
 
     def kernel_stats(self):
         ms = C.c_double(); n = C.c_long()

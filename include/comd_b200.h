@@ -133,6 +133,9 @@ int  comd_dev_timestep(ComdDev* dev, int nSteps, double dt);
  * useNeighborList != 0 switches force + redistribute to the list variants. */
 int  comd_dev_set_neighbor_list(ComdDev* dev, int useNeighborList, double skinDistance);
 int  comd_dev_neighbor_stats(ComdDev* dev, long* nPairsStored, int* maxPerAtom, int* nBuilds);
+/* list builds and in-place ghost refreshes since creation (the two outcomes of redistributeAtomsGpuNL,
+ * timestep.c:278-354); bench.py reports how many of each fell into its timed window */
+int  comd_dev_neighbor_counters(ComdDev* dev, long* nBuilds, long* nRefreshes);
 
 /* ---- multi-GPU: replaces the MPI wrappers of parallel.h:17-63 for the halo path and
  * the libmp layer of comm.h:40-74.  The 128-byte id is made on rank 0 and handed to
@@ -149,15 +152,24 @@ int  comd_comm_barrier(ComdDev* dev);                               /* barrierPa
  *                        stencil loop (the shape of LJ_Force_thread_atom, gpu_lj_thread_atom.h:31-143)
  *   "tile_tx"            link-cell path: target cells per force tile along x (1..16)
  *   "energy_every_step"  list path: per-atom EAM pair energies at every step of comd_dev_timestep (default 0)
+ *   "nl_n3"              list path: 1 (default) pairs inside a work block are stored and evaluated once, for both
+ *                        atoms (half-list form of neighborList.c:123,142 / eam.c:311-345 inside the block, shared-memory
+ *                        fixed-point accumulators); 0 = full list, every pair met from both ends.  Invalidates the list.
  *   "nl_block"           list path: cells per work block as bx*10000 + by*100 + bz (by*bz <= 32), 0 = auto
  *   "nl_threads"         list path: cap on the CTA size of the force kernels (multiple of 32)
  *   "nl_chunks_per_cta"  list path: work chunks per persistent CTA handed out through the global counter (default 32)
  *   "overlap"            list path, N > 1: halo exchange overlapped with the interior blocks (default 1)
  *   "overlap_sms"        SMs an overlapped interior launch may fill (default 140 of 148)
  *   "phase_timing"       per-phase CUDA-event timing of comd_dev_timestep, reported on stderr by comd_dev_destroy
- *   "e2e_speculate"      1 (default): a comd_dev_step_host call that follows another one may start from the atoms the
- *                        device still holds while its inputs are uploaded (see there); 0: always wait for the upload */
+ *   "e2e_speculate"      0 (default): comd_dev_step_host waits for its upload before the step starts.  1: a call that
+ *                        follows another one may start from the atoms the device still holds while its inputs are
+ *                        uploaded (see there) -- pays only when the caller hands back bit-identical buffers */
 int  comd_dev_set_option(ComdDev* dev, const char* key, long value);
+
+/* Bytes of the last halo message packed for / received across `face` (x-,x+,y-,y+,z-,z+): kind 0 = atom exchange
+ * (56-byte AtomMsg per atom, haloExchange.h:32-38), kind 1 = F'(rho) exchange (8 bytes per atom).  What the
+ * reference's loadBuffer returns and unloadBuffer is handed (haloExchange.h:84,98); the buffers themselves stay in HBM. */
+int  comd_dev_halo_bytes(ComdDev* dev, int kind, int face, long* sentBytes, long* receivedBytes);
 
 /* ---- measurement hooks (bench.py / tests) ---------------------------------------- */
 int  comd_dev_sync(ComdDev* dev);

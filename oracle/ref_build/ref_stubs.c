@@ -15,7 +15,7 @@ NOOP(emptyNeighborListGpu) NOOP(initHashTableGpu) NOOP(emptyHashTableGpu)
 DEAD(advancePositionGpu) DEAD(advanceVelocityGpu) DEAD(buildAtomListGpu) DEAD(buildNeighborListGpu)
 DEAD(comm_flush) DEAD(comm_irecv) DEAD(comm_isend) DEAD(comm_isend_on_stream) DEAD(comm_progress)
 DEAD(comm_send_ready) DEAD(comm_send_ready_on_stream) DEAD(comm_wait_all) DEAD(comm_wait_all_on_stream)
-DEAD(comm_wait_ready_on_stream) DEAD(comm_init) DEAD(comm_finalize) DEAD(comm_select_device)
+DEAD(comm_wait_ready_on_stream) DEAD(comm_init) DEAD(comm_finalize) ZERO(comm_select_device)   /* -DDO_MPI main asks it for a device id (CoMD.c:112) */
 DEAD(compactCellsGpu) DEAD(computeEnergy)
 DEAD(eamForce1Gpu) DEAD(eamForce1GpuAsync) DEAD(eamForce2Gpu) DEAD(eamForce2GpuAsync)
 DEAD(eamForce3Gpu) DEAD(eamForce3GpuAsync) DEAD(getAtomMsgSoAPtr) DEAD(ljForceGpu)

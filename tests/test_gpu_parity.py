@@ -433,24 +433,57 @@ def test_neighbor_list_energy_on_demand_does_not_change_the_trajectory(kind):
 
 @pytest.mark.parametrize("kind", list(KINDS))
 @pytest.mark.parametrize("block", [10101, 20302, 80804, 40116])
-def test_neighbor_list_work_block_shape_is_invisible(kind, block):
+@pytest.mark.parametrize("n3", [0, 1])
+def test_neighbor_list_work_block_shape_is_invisible(kind, block, n3):
     """The list kernels walk blocks of bx*by*bz cells per CTA; the shape (also ragged against the grid, also
-    a single block for the whole domain) is a scheduling choice and must not change one bit of the result."""
+    a single block for the whole domain) is a scheduling choice.  Full-list kernels (nl_n3 0): not one bit of the
+    result may change.  Once-per-pair kernels (default): the shape decides which pairs are added in 2^-46 fixed
+    point instead of FP64, so results agree to that resolution -- and stay bit-reproducible for a given shape."""
     n = 10
     orc = oracle_sim(KINDS[kind], n, delta=0.08, temperature=600.0)
     a = orc.atoms()
     res = []
-    for b in (0, block):
+    for b in (0, block, block):
         dev, _ = device_for(orc, (n, n, n), nl_skin=0.1)
+        dev.set_option("nl_n3", n3)
         dev.set_option("nl_block", b)
         dev.upload(a["gid"], a["r"], a["p"])
         dev.compute_force()
         dev.timestep(3, 1.0)
         res.append(by_gid(dev.download()))
         dev.close()
-    o = by_gid(a)
     for k in ("r", "p", "f", "U"):
-        assert np.array_equal(res[0][k], res[1][k]), k
+        assert np.array_equal(res[1][k], res[2][k]), k                  # run-to-run: same bits
+        if n3 == 0:
+            assert np.array_equal(res[0][k], res[1][k]), k
+        else:
+            assert rel_err(res[1][k], res[0][k]) <= 2e-13, k
+
+
+@pytest.mark.parametrize("kind", list(KINDS))
+def test_neighbor_list_full_list_kernels_still_match(kind):
+    """nl_n3 0 keeps round 1's full-list kernels (every pair met from both ends, no shared-memory accumulators):
+    same parity gate, and the same trajectory as the once-per-pair default."""
+    n = 8
+    orc = oracle_sim(KINDS[kind], n, delta=0.1, temperature=600.0)
+    a = orc.atoms()
+    out = []
+    for n3 in (0, 1):
+        dev, _ = device_for(orc, (n, n, n), nl_skin=0.1)
+        dev.set_option("nl_n3", n3)
+        dev.upload(a["gid"], a["r"], a["p"])
+        dev.compute_force()
+        d = by_gid(dev.download()); o = by_gid(a)
+        assert rel_err(d["f"], o["f"]) <= FORCE_TOL
+        assert rel_err(d["U"], o["U"] * u_scale(kind)) <= FORCE_TOL
+        dev.timestep(30, 1.0)
+        out.append((by_gid(dev.download()), dev.energy(), dev.neighbor_stats()))
+        dev.close()
+    (d0, e0, s0), (d1, e1, s1) = out
+    assert s0["pairs"] == s1["pairs"] and s0["builds"] == s1["builds"]
+    assert abs(sum(e1) - sum(e0)) <= 1e-11 * abs(sum(e0))
+    assert rel_err(d1["r"], d0["r"]) <= 1e-12
+    assert rel_err(d1["f"], d0["f"]) <= 1e-9
 
 
 @pytest.mark.parametrize("kind", ["lj", "setfl"])
