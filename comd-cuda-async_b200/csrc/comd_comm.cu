@@ -14,7 +14,7 @@
 typedef struct ncclComm* ncclComm_t;
 typedef struct { char internal[128]; } ncclUniqueId;
 typedef int ncclResult_t;
-enum { ncclInt32 = 2, ncclInt64 = 4, ncclFloat64 = 8 };   // ncclDataType_t values
+enum { ncclInt32 = 2, ncclInt64 = 4, ncclFloat32 = 7, ncclFloat64 = 8 };   // ncclDataType_t values
 enum { ncclSum = 0 };
 
 struct NcclApi
@@ -119,7 +119,7 @@ template <typename T> static inline void swapPtr(T*& a, T*& b) { T* t = a; a = b
 // `cache`: 12 host ints (6 send counts, 6 receive counts) of this message family.  When `useCache`
 // is set the counts are the ones of the previous exchange (list mode between rebuilds: same atoms,
 // same order), so neither the count messages nor the host synchronisation are needed.
-static int exchangePhase(ComdDev* d, int ax, double* sendBuf[2], double* recvBuf[2], int sendBase, int recvBase, int doublesPerItem,
+static int exchangePhase(ComdDev* d, int ax, real_t* sendBuf[2], real_t* recvBuf[2], int sendBase, int recvBase, int doublesPerItem,
                          int* cache = nullptr, bool useCache = false)
 {
    const int fM = 2 * ax, fP = fM + 1;
@@ -138,10 +138,10 @@ static int exchangePhase(ComdDev* d, int ax, double* sendBuf[2], double* recvBuf
    {
       const long nSM = cache[fM], nSP = cache[fP], nRM = cache[6 + fM], nRP = cache[6 + fP];
       NCCL_TRY(g_nccl.GroupStart());
-      if (nSP) NCCL_TRY(g_nccl.Send(sendBuf[1], nSP * doublesPerItem, ncclFloat64, nbrP, comm, s));
-      if (nSM) NCCL_TRY(g_nccl.Send(sendBuf[0], nSM * doublesPerItem, ncclFloat64, nbrM, comm, s));
-      if (nRM) NCCL_TRY(g_nccl.Recv(recvBuf[0], nRM * doublesPerItem, ncclFloat64, nbrM, comm, s));
-      if (nRP) NCCL_TRY(g_nccl.Recv(recvBuf[1], nRP * doublesPerItem, ncclFloat64, nbrP, comm, s));
+      if (nSP) NCCL_TRY(g_nccl.Send(sendBuf[1], nSP * doublesPerItem, COMD_NCCL_REAL, nbrP, comm, s));
+      if (nSM) NCCL_TRY(g_nccl.Send(sendBuf[0], nSM * doublesPerItem, COMD_NCCL_REAL, nbrM, comm, s));
+      if (nRM) NCCL_TRY(g_nccl.Recv(recvBuf[0], nRM * doublesPerItem, COMD_NCCL_REAL, nbrM, comm, s));
+      if (nRP) NCCL_TRY(g_nccl.Recv(recvBuf[1], nRP * doublesPerItem, COMD_NCCL_REAL, nbrP, comm, s));
       NCCL_TRY(g_nccl.GroupEnd());
       return COMD_OK;
    }
@@ -163,10 +163,10 @@ static int exchangePhase(ComdDev* d, int ax, double* sendBuf[2], double* recvBuf
    if (cache) { cache[fM] = (int)nSM; cache[fP] = (int)nSP; cache[6 + fM] = (int)nRM; cache[6 + fP] = (int)nRP; }
    // 2. payload
    NCCL_TRY(g_nccl.GroupStart());
-   if (nSP) NCCL_TRY(g_nccl.Send(sendBuf[1], nSP * doublesPerItem, ncclFloat64, nbrP, comm, s));
-   if (nSM) NCCL_TRY(g_nccl.Send(sendBuf[0], nSM * doublesPerItem, ncclFloat64, nbrM, comm, s));
-   if (nRM) NCCL_TRY(g_nccl.Recv(recvBuf[0], nRM * doublesPerItem, ncclFloat64, nbrM, comm, s));
-   if (nRP) NCCL_TRY(g_nccl.Recv(recvBuf[1], nRP * doublesPerItem, ncclFloat64, nbrP, comm, s));
+   if (nSP) NCCL_TRY(g_nccl.Send(sendBuf[1], nSP * doublesPerItem, COMD_NCCL_REAL, nbrP, comm, s));
+   if (nSM) NCCL_TRY(g_nccl.Send(sendBuf[0], nSM * doublesPerItem, COMD_NCCL_REAL, nbrM, comm, s));
+   if (nRM) NCCL_TRY(g_nccl.Recv(recvBuf[0], nRM * doublesPerItem, COMD_NCCL_REAL, nbrM, comm, s));
+   if (nRP) NCCL_TRY(g_nccl.Recv(recvBuf[1], nRP * doublesPerItem, COMD_NCCL_REAL, nbrP, comm, s));
    NCCL_TRY(g_nccl.GroupEnd());
    return COMD_OK;
 }
@@ -174,7 +174,7 @@ static int exchangePhase(ComdDev* d, int ax, double* sendBuf[2], double* recvBuf
 int comdExchangeAtomsPhase(ComdDev* d, int ax)
 {
    d->fpCntValid = 0;                                        // a full atom exchange changes the ghost population
-   return exchangePhase(d, ax, d->sendBuf, d->recvBuf, C_SEND0, C_RECV0, COMD_MSG_DOUBLES, d->hAtomCnt, false);
+   return exchangePhase(d, ax, d->sendBuf, d->recvBuf, C_SEND0, C_RECV0, COMD_MSG_REALS, d->hAtomCnt, false);
 }
 
 int comdExchangeFprimePhase(ComdDev* d, int ax)

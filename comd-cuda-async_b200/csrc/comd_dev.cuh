@@ -54,6 +54,7 @@ __device__ __forceinline__ void msgGetId(const real_t* in, int& gid, int& spec)
 #endif
 }
 #define COMD_MSG_R0 (COMD_MSG_REALS - 6)   // first position slot of a message record
+#define COMD_MSG_DOUBLES COMD_MSG_REALS
 #define COMD_MAX_CELL_ATOMS 256     // sanity bound used by the in-cell rank sort
 
 // device counters (ints)
