@@ -1039,6 +1039,7 @@ extern "C" int comd_dev_set_option(ComdDev* d, const char* key, long value)
    if (!d || !key) return COMD_E_ARG;
    if (!strcmp(key, "force_variant")) { if (value < 0 || value > 1) { comdSetError("force_variant: 0 or 1"); return COMD_E_ARG; } d->optForceVariant = (int)value; return COMD_OK; }
    if (!strcmp(key, "nl_chunks_per_cta")) { if (value < 0 || value > 64) { comdSetError("nl_chunks_per_cta: 0..64"); return COMD_E_ARG; } d->optNlChunksPerCta = (int)value; return COMD_OK; }
+   if (!strcmp(key, "nl_lanes")) { if (value != 4 && value != 8) { comdSetError("nl_lanes: 4 or 8"); return COMD_E_ARG; } d->optNlLanes = (int)value; d->nlValid = 0; return COMD_OK; }
    if (!strcmp(key, "nl_n3")) { d->optNlN3 = value != 0; d->nlValid = 0; return COMD_OK; }
    if (!strcmp(key, "overlap")) { d->optOverlap = value != 0; return COMD_OK; }
    if (!strcmp(key, "e2e_speculate")) { d->e2eSpecArmed = value != 0; return COMD_OK; }

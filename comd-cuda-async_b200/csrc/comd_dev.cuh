@@ -159,6 +159,7 @@ struct ComdDev
    int *nlList; int *nlCount; int nlStride; int nlMax; real_t* nlLastR[3]; int nlBuilds; int nlValid;
    long nlRows;                 // rows allocated in nlList
    int optNlN3;                          // 1 (default): pairs inside a work block are evaluated once for both atoms (force_n3.cuh)
+   int optNlLanes, nlLanes;              // lanes per atom of the once-per-pair kernels (option nl_lanes: 4 default, 8) / of the current list
    int nlN3Shape[3];                     // block shape the current list was built for (0 = full list)
    int optNlChunksPerCta;                // target work chunks per CTA of the list force kernels (0 = default 32)
    int *nlWork; unsigned nlWorkSeq;      // work counters of the list force kernels (one per launch, ring of 64)

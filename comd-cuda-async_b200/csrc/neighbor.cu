@@ -28,7 +28,8 @@
 #define NL_U 4                  // candidate rounds in flight per trip
 // Row layout: chunks of 32 entries, each stored transposed -- entry e = 8u + l of a chunk (round u, lane l of
 // the force kernels) sits at 4l + u, so a lane reads the indices of four rounds with one 128-bit load.
-__device__ __forceinline__ int nlSlot(int pos) { return (pos & ~31) | ((pos & 7) << 2) | ((pos >> 3) & 3); }
+// (G = lanes per atom of the force kernel that will walk the list: 8, or 4 for the once-per-pair kernels; chunk = 4 G entries)
+__device__ __forceinline__ int nlSlot(int pos, int G) { return G == 8 ? ((pos & ~31) | ((pos & 7) << 2) | ((pos >> 3) & 3)) : ((pos & ~15) | ((pos & 3) << 2) | ((pos >> 2) & 3)); }
 // N3 (bx > 0): a pair whose two atoms belong to the same work block of bx*by*bz cells is stored ONCE, on the row of
 // the lower sorted index, tagged with N3_FLAG and the neighbour's (y,z) row inside the block (force_n3.cuh); the
 // row of the higher index skips it -- without loading the position.  Pairs across a block face, and every pair with
@@ -40,7 +41,7 @@ k_nl_build(DevGeom g, double rc2, double rl2, const double4* __restrict__ rq,
            const int* __restrict__ cell, const unsigned char* __restrict__ cellType, const int* __restrict__ cellStart,
            int* __restrict__ cnt, int* __restrict__ list, int* __restrict__ count, int stride, long rows,
            double* __restrict__ lx, double* __restrict__ ly, double* __restrict__ lz, unsigned long long* __restrict__ stat,
-           int bx, int by, int bz)
+           int bx, int by, int bz, int G)
 {
    __shared__ int farBuf[8][4][NL_FARCAP];
    const unsigned full = 0xffffffffu;
@@ -122,7 +123,7 @@ k_nl_build(DevGeom g, double rc2, double rl2, const double4* __restrict__ rq,
                const unsigned mN = (__ballot_sync(full, near) >> (g4 * NL_G)) & grp;
                const unsigned mF = (__ballot_sync(full, far) >> (g4 * NL_G)) & grp;
                const int ent = both[u] ? (int)((unsigned)j | tag) : j;
-               if (near) { const int pos = nNear + __popc(mN & below); if (pos < stride) row[nlSlot(pos)] = ent; }
+               if (near) { const int pos = nNear + __popc(mN & below); if (pos < stride) row[nlSlot(pos, G)] = ent; }
                if (far) { const int pos = nFar + __popc(mF & below); if (pos < NL_FARCAP) myFar[pos] = ent; }
                nNear += __popc(mN);
                nFar += __popc(mF);
@@ -133,7 +134,7 @@ k_nl_build(DevGeom g, double rc2, double rl2, const double4* __restrict__ rq,
       __syncwarp();
       const int nn = nNear + nFar;
       const bool over = nn > stride || nFar > NL_FARCAP;
-      if (act && !over) for (int k = gl; k < nFar; k += NL_G) row[nlSlot(nNear + k)] = myFar[k];
+      if (act && !over) for (int k = gl; k < nFar; k += NL_G) row[nlSlot(nNear + k, G)] = myFar[k];
       __syncwarp();
       if (act && gl == 0)
       {
@@ -273,9 +274,10 @@ int comdNeighborBuildIfNeeded(ComdDev* d)
    const bool n3 = d->optNlN3 != 0;
    if (n3 && d->cap > (1L << N3_ROWSHIFT)) { comdSetError("neighbour list: more than %ld atoms per GPU", 1L << N3_ROWSHIFT); return COMD_E_CAPACITY; }
    d->nlN3Shape[0] = n3 ? B.bx : 0; d->nlN3Shape[1] = n3 ? B.by : 0; d->nlN3Shape[2] = n3 ? B.bz : 0;
+   d->nlLanes = n3 && d->optNlLanes != 8 ? 4 : 8;
    k_nl_build<<<gridFor((n + 3) / 4, 8, 148 * 8), 256, 0, s>>>(d->g, d->cutoff * d->cutoff, rl * rl, d->A.rq, d->A.cell, d->cellType,
       d->cellStart, d->cnt, d->nlList, d->nlCount, d->nlStride, d->nlRows, d->nlLastR[0], d->nlLastR[1], d->nlLastR[2], d->nlStat,
-      d->nlN3Shape[0], d->nlN3Shape[1], d->nlN3Shape[2]);
+      d->nlN3Shape[0], d->nlN3Shape[1], d->nlN3Shape[2], d->nlLanes);
    LAUNCH_CHECK(d);
    d->nlValid = 1;
    d->nlBuilds++;

@@ -155,6 +155,7 @@ int  comd_comm_barrier(ComdDev* dev);                               /* barrierPa
  *   "nl_n3"              list path: 1 (default) pairs inside a work block are stored and evaluated once, for both
  *                        atoms (half-list form of neighborList.c:123,142 / eam.c:311-345 inside the block, shared-memory
  *                        fixed-point accumulators); 0 = full list, every pair met from both ends.  Invalidates the list.
+ *   "nl_lanes"           once-per-pair kernels: lanes that walk one atom's list row, 4 (default) or 8.  Invalidates the list.
  *   "nl_block"           list path: cells per work block as bx*10000 + by*100 + bz (by*bz <= 32), 0 = auto
  *   "nl_threads"         list path: cap on the CTA size of the force kernels (multiple of 32)
  *   "nl_chunks_per_cta"  list path: work chunks per persistent CTA handed out through the global counter (default 32)

@@ -462,15 +462,17 @@ def test_neighbor_list_work_block_shape_is_invisible(kind, block, n3):
 
 @pytest.mark.parametrize("kind", list(KINDS))
 def test_neighbor_list_full_list_kernels_still_match(kind):
-    """nl_n3 0 keeps round 1's full-list kernels (every pair met from both ends, no shared-memory accumulators):
-    same parity gate, and the same trajectory as the once-per-pair default."""
+    """nl_n3 0 keeps round 1's full-list kernels (every pair met from both ends, no shared-memory accumulators) and
+    nl_lanes 8 the eight-lanes-per-row form of the once-per-pair kernels: same parity gate, and the same trajectory
+    as the default (once per pair, four lanes per row)."""
     n = 8
     orc = oracle_sim(KINDS[kind], n, delta=0.1, temperature=600.0)
     a = orc.atoms()
     out = []
-    for n3 in (0, 1):
+    for opts in ({"nl_n3": 0}, {}, {"nl_lanes": 8}):
         dev, _ = device_for(orc, (n, n, n), nl_skin=0.1)
-        dev.set_option("nl_n3", n3)
+        for k, v in opts.items():
+            dev.set_option(k, v)
         dev.upload(a["gid"], a["r"], a["p"])
         dev.compute_force()
         d = by_gid(dev.download()); o = by_gid(a)
@@ -479,11 +481,12 @@ def test_neighbor_list_full_list_kernels_still_match(kind):
         dev.timestep(30, 1.0)
         out.append((by_gid(dev.download()), dev.energy(), dev.neighbor_stats()))
         dev.close()
-    (d0, e0, s0), (d1, e1, s1) = out
-    assert s0["pairs"] == s1["pairs"] and s0["builds"] == s1["builds"]
-    assert abs(sum(e1) - sum(e0)) <= 1e-11 * abs(sum(e0))
-    assert rel_err(d1["r"], d0["r"]) <= 1e-12
-    assert rel_err(d1["f"], d0["f"]) <= 1e-9
+    (d0, e0, s0) = out[0]
+    for (d1, e1, s1) in out[1:]:
+        assert s0["pairs"] == s1["pairs"] and s0["builds"] == s1["builds"]
+        assert abs(sum(e1) - sum(e0)) <= 1e-11 * abs(sum(e0))
+        assert rel_err(d1["r"], d0["r"]) <= 1e-12
+        assert rel_err(d1["f"], d0["f"]) <= 1e-9
 
 
 @pytest.mark.parametrize("kind", ["lj", "setfl"])
