@@ -44,7 +44,7 @@ __global__ void k_redist_begin(int* cnt)
 // 448-480); last step's ghosts are dropped (emptyHaloCells, linkCells.c:483-487).
 // Atoms whose new cell lies in the 2-plane shell are remembered for the exchange.
 __global__ void __launch_bounds__(256)
-k_rebin(DevGeom g, const double* __restrict__ rx, const double* __restrict__ ry, const double* __restrict__ rz,
+k_rebin(DevGeom g, const real_t* __restrict__ rx, const real_t* __restrict__ ry, const real_t* __restrict__ rz,
         const int* __restrict__ cellOld, const unsigned char* __restrict__ cellType,
         int* __restrict__ cellKey, int* __restrict__ cellCount, int* __restrict__ shell, int* __restrict__ cnt)
 {
@@ -83,13 +83,13 @@ k_rebin(DevGeom g, const double* __restrict__ rx, const double* __restrict__ ry,
 // outermost planes incl. halo cells (mkAtomCellList, haloExchange.c:1543-1567) goes out,
 // shifted by +-globalExtent across a periodic face (loadAtomsBuffer, :1576-1611).
 __global__ void __launch_bounds__(256)
-k_pack_atoms(int axis, const double* __restrict__ rx, const double* __restrict__ ry, const double* __restrict__ rz,
-             const double* __restrict__ px, const double* __restrict__ py, const double* __restrict__ pz,
+k_pack_atoms(int axis, const real_t* __restrict__ rx, const real_t* __restrict__ ry, const real_t* __restrict__ rz,
+             const real_t* __restrict__ px, const real_t* __restrict__ py, const real_t* __restrict__ pz,
              const int* __restrict__ gid, const int* __restrict__ spec,
              const int* __restrict__ cellKey, const unsigned char* __restrict__ cellType,
              const int* __restrict__ shell, int* __restrict__ cnt,
-             double* __restrict__ bufM, double* __restrict__ bufP, long msgCap,
-             double shMx, double shMy, double shMz, double shPx, double shPy, double shPz)
+             real_t* __restrict__ bufM, real_t* __restrict__ bufP, long msgCap,
+             real_t shMx, real_t shMy, real_t shMz, real_t shPx, real_t shPy, real_t shPz)
 {
    const int n = cnt[C_NSHELL];
    const int lane = threadIdx.x & 31;
@@ -114,13 +114,13 @@ k_pack_atoms(int axis, const double* __restrict__ rx, const double* __restrict__
          {
             const long k = b + __popc(m & ((1u << lane) - 1));
             if (k >= msgCap) { atomicOr(&cnt[C_ERR], ERRB_CAPACITY); continue; }
-            double* o = (d ? bufP : bufM) + k * COMD_MSG_DOUBLES;
-            int2 id = make_int2(gid[i], spec[i]);
-            o[0] = *reinterpret_cast<double*>(&id);
-            o[1] = rx[i] + (d ? shPx : shMx);
-            o[2] = ry[i] + (d ? shPy : shMy);
-            o[3] = rz[i] + (d ? shPz : shMz);
-            o[4] = px[i]; o[5] = py[i]; o[6] = pz[i];
+            real_t* o = (d ? bufP : bufM) + k * COMD_MSG_REALS;
+            msgPutId(o, gid[i], spec[i]);
+            o += COMD_MSG_R0;
+            o[0] = rx[i] + (d ? shPx : shMx);
+            o[1] = ry[i] + (d ? shPy : shMy);
+            o[2] = rz[i] + (d ? shPz : shMz);
+            o[3] = px[i]; o[4] = py[i]; o[5] = pz[i];
          }
       }
    }
@@ -130,9 +130,9 @@ k_pack_atoms(int axis, const double* __restrict__ rx, const double* __restrict__
 // haloExchange.c:1649-1688; linkCells.c:228-256): it joins the source pool with the cell its
 // coordinates select, so ownership transfers by position alone.
 __global__ void __launch_bounds__(256)
-k_unpack_atoms(DevGeom g, const double* __restrict__ buf, const int* __restrict__ nRecvPtr,
-               double* __restrict__ rx, double* __restrict__ ry, double* __restrict__ rz,
-               double* __restrict__ px, double* __restrict__ py, double* __restrict__ pz,
+k_unpack_atoms(DevGeom g, const real_t* __restrict__ buf, const int* __restrict__ nRecvPtr,
+               real_t* __restrict__ rx, real_t* __restrict__ ry, real_t* __restrict__ rz,
+               real_t* __restrict__ px, real_t* __restrict__ py, real_t* __restrict__ pz,
                int* __restrict__ gid, int* __restrict__ spec,
                int* __restrict__ cellKey, int* __restrict__ cellCount, int* __restrict__ shell,
                int* __restrict__ cnt, long cap)
@@ -152,16 +152,17 @@ k_unpack_atoms(DevGeom g, const double* __restrict__ buf, const int* __restrict_
       if (!have) continue;
       const long j = b + lane;            // lanes with `have` are a prefix of the warp
       if (j >= cap) { atomicOr(&cnt[C_ERR], ERRB_CAPACITY); continue; }
-      const double* in = buf + (long)k * COMD_MSG_DOUBLES;
-      double w = in[0];
-      int2 id = *reinterpret_cast<int2*>(&w);
-      const double x = in[1], y = in[2], z = in[3];
+      const real_t* in = buf + (long)k * COMD_MSG_REALS;
+      int2 id;
+      msgGetId(in, id.x, id.y);
+      in += COMD_MSG_R0;
+      const real_t x = in[0], y = in[1], z = in[2];
       int err = 0;
       const int c = cellOfPos(g, x, y, z, err);
       if (err) atomicOr(&cnt[C_ERR], ERRB_ESCAPE);
       gid[j] = id.x; spec[j] = id.y;
       rx[j] = x; ry[j] = y; rz[j] = z;
-      px[j] = in[4]; py[j] = in[5]; pz[j] = in[6];
+      px[j] = in[3]; py[j] = in[4]; pz[j] = in[5];
       cellKey[j] = c;
       atomicAdd(&cellCount[c], 1);
       shell[bs + lane] = (int)j;
@@ -276,10 +277,10 @@ k_rank_gather(DevGeom geo, const int* __restrict__ tmpSrc, const int* __restrict
          int rank = 0;
          for (int u = b; u < e; ++u) { const int gu = tmpGid[u]; rank += (gu < g) || (gu == g && u < t); }
          const int d = b + rank, s = tmpSrc[t];
-         const double x = src.r[0][s], y = src.r[1][s], z = src.r[2][s];
+         const real_t x = src.r[0][s], y = src.r[1][s], z = src.r[2][s];
          dst.r[0][d] = x; dst.r[1][d] = y; dst.r[2][d] = z;
          dst.rf[d] = make_float4((float)(x - geo.lMin[0]), (float)(y - geo.lMin[1]), (float)(z - geo.lMin[2]), 0.f);
-         dst.rq[d] = make_double4(x, y, z, 0.0);
+         dst.rq[d] = make_real4(x, y, z, R(0.0));
          dst.p[0][d] = src.p[0][s]; dst.p[1][d] = src.p[1][s]; dst.p[2][d] = src.p[2][s];
          dst.gid[d] = g; dst.spec[d] = src.spec[s]; dst.cell[d] = c;
          isLocal = cellType[c] & CT_LOCAL;
@@ -293,35 +294,35 @@ k_rank_gather(DevGeom geo, const int* __restrict__ tmpSrc, const int* __restrict
 // order (no FMA contraction) so positions, hence cell ids, track the CPU path bit by bit
 // for as long as the forces do.
 __global__ void __launch_bounds__(256)
-k_advance_velocity(double dt, const int* __restrict__ cell, const unsigned char* __restrict__ cellType,
-                   double* __restrict__ px, double* __restrict__ py, double* __restrict__ pz,
-                   const double* __restrict__ fx, const double* __restrict__ fy, const double* __restrict__ fz,
+k_advance_velocity(real_t dt, const int* __restrict__ cell, const unsigned char* __restrict__ cellType,
+                   real_t* __restrict__ px, real_t* __restrict__ py, real_t* __restrict__ pz,
+                   const real_t* __restrict__ fx, const real_t* __restrict__ fy, const real_t* __restrict__ fz,
                    const int* __restrict__ cnt)
 {
    const int n = cnt[C_NATOMS];
    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
    {
       if (!(cellType[cell[i]] & CT_LOCAL)) continue;
-      px[i] = __dadd_rn(px[i], __dmul_rn(dt, fx[i]));
-      py[i] = __dadd_rn(py[i], __dmul_rn(dt, fy[i]));
-      pz[i] = __dadd_rn(pz[i], __dmul_rn(dt, fz[i]));
+      px[i] = addRn(px[i], mulRn(dt, fx[i]));
+      py[i] = addRn(py[i], mulRn(dt, fy[i]));
+      pz[i] = addRn(pz[i], mulRn(dt, fz[i]));
    }
 }
 __global__ void __launch_bounds__(256)
-k_advance_position(double dt, double invMass, const int* __restrict__ cell, const unsigned char* __restrict__ cellType,
-                   double* __restrict__ rx, double* __restrict__ ry, double* __restrict__ rz,
-                   const double* __restrict__ px, const double* __restrict__ py, const double* __restrict__ pz,
-                   const int* __restrict__ cnt, double4* __restrict__ rq)
+k_advance_position(real_t dt, real_t invMass, const int* __restrict__ cell, const unsigned char* __restrict__ cellType,
+                   real_t* __restrict__ rx, real_t* __restrict__ ry, real_t* __restrict__ rz,
+                   const real_t* __restrict__ px, const real_t* __restrict__ py, const real_t* __restrict__ pz,
+                   const int* __restrict__ cnt, real4* __restrict__ rq)
 {
    const int n = cnt[C_NATOMS];
    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
    {
       if (!(cellType[cell[i]] & CT_LOCAL)) continue;
-      const double x = __dadd_rn(rx[i], __dmul_rn(__dmul_rn(dt, px[i]), invMass));
-      const double y = __dadd_rn(ry[i], __dmul_rn(__dmul_rn(dt, py[i]), invMass));
-      const double z = __dadd_rn(rz[i], __dmul_rn(__dmul_rn(dt, pz[i]), invMass));
+      const real_t x = addRn(rx[i], mulRn(mulRn(dt, px[i]), invMass));
+      const real_t y = addRn(ry[i], mulRn(mulRn(dt, py[i]), invMass));
+      const real_t z = addRn(rz[i], mulRn(mulRn(dt, pz[i]), invMass));
       rx[i] = x; ry[i] = y; rz[i] = z;
-      rq[i] = make_double4(x, y, z, 0.0);
+      rq[i] = make_real4(x, y, z, R(0.0));
    }
 }
 // first half of a step in one pass: p += dt/2 f ; r += dt p / m
@@ -331,31 +332,31 @@ k_advance_position(double dt, double invMass, const int* __restrict__ cell, cons
 // list was built on, neighborList.c:212-234) is evaluated on the new position while it is in registers.
 template <bool TWO, bool CHECK>
 __global__ void __launch_bounds__(256)
-k_kick_drift(double dtHalf, double dt, double invMass, const int* __restrict__ cell, const unsigned char* __restrict__ cellType,
-             double* __restrict__ rx, double* __restrict__ ry, double* __restrict__ rz,
-             double* __restrict__ px, double* __restrict__ py, double* __restrict__ pz,
-             const double* __restrict__ fx, const double* __restrict__ fy, const double* __restrict__ fz,
-             int* __restrict__ cnt, double4* __restrict__ rq,
-             const double* __restrict__ lx, const double* __restrict__ ly, const double* __restrict__ lz, double half2)
+k_kick_drift(real_t dtHalf, real_t dt, real_t invMass, const int* __restrict__ cell, const unsigned char* __restrict__ cellType,
+             real_t* __restrict__ rx, real_t* __restrict__ ry, real_t* __restrict__ rz,
+             real_t* __restrict__ px, real_t* __restrict__ py, real_t* __restrict__ pz,
+             const real_t* __restrict__ fx, const real_t* __restrict__ fy, const real_t* __restrict__ fz,
+             int* __restrict__ cnt, real4* __restrict__ rq,
+             const real_t* __restrict__ lx, const real_t* __restrict__ ly, const real_t* __restrict__ lz, real_t half2)
 {
    const int n = cnt[C_NATOMS];
    bool hit = false;
    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
    {
       if (!(cellType[cell[i]] & CT_LOCAL)) continue;
-      const double hx = __dmul_rn(dtHalf, fx[i]), hy = __dmul_rn(dtHalf, fy[i]), hz = __dmul_rn(dtHalf, fz[i]);
-      double a = px[i], b = py[i], c = pz[i];
-      if (TWO) { a = __dadd_rn(a, hx); b = __dadd_rn(b, hy); c = __dadd_rn(c, hz); }
-      a = __dadd_rn(a, hx); b = __dadd_rn(b, hy); c = __dadd_rn(c, hz);
+      const real_t hx = mulRn(dtHalf, fx[i]), hy = mulRn(dtHalf, fy[i]), hz = mulRn(dtHalf, fz[i]);
+      real_t a = px[i], b = py[i], c = pz[i];
+      if (TWO) { a = addRn(a, hx); b = addRn(b, hy); c = addRn(c, hz); }
+      a = addRn(a, hx); b = addRn(b, hy); c = addRn(c, hz);
       px[i] = a; py[i] = b; pz[i] = c;
-      const double x = __dadd_rn(rx[i], __dmul_rn(__dmul_rn(dt, a), invMass));
-      const double y = __dadd_rn(ry[i], __dmul_rn(__dmul_rn(dt, b), invMass));
-      const double z = __dadd_rn(rz[i], __dmul_rn(__dmul_rn(dt, c), invMass));
+      const real_t x = addRn(rx[i], mulRn(mulRn(dt, a), invMass));
+      const real_t y = addRn(ry[i], mulRn(mulRn(dt, b), invMass));
+      const real_t z = addRn(rz[i], mulRn(mulRn(dt, c), invMass));
       rx[i] = x; ry[i] = y; rz[i] = z;
-      rq[i] = make_double4(x, y, z, 0.0);
+      rq[i] = make_real4(x, y, z, R(0.0));
       if (CHECK)
       {
-         const double dx = lx[i] - x, dy = ly[i] - y, dz = lz[i] - z;
+         const real_t dx = lx[i] - x, dy = ly[i] - y, dz = lz[i] - z;
          hit |= dx * dx + dy * dy + dz * dz > half2;
       }
    }
@@ -366,13 +367,13 @@ k_kick_drift(double dtHalf, double dt, double invMass, const int* __restrict__ c
 // ReduceEnergy's atomicAdd(double) (gpu_reduce.h:32-98).
 #define RED_BLOCKS 592
 __global__ void __launch_bounds__(256)
-k_energy_partial(double halfInvMass, const int* __restrict__ cell, const unsigned char* __restrict__ cellType,
-                 const double* __restrict__ e, const double* __restrict__ px, const double* __restrict__ py,
-                 const double* __restrict__ pz, const int* __restrict__ cnt, double* __restrict__ partial)
+k_energy_partial(real_t halfInvMass, const int* __restrict__ cell, const unsigned char* __restrict__ cellType,
+                 const real_t* __restrict__ e, const real_t* __restrict__ px, const real_t* __restrict__ py,
+                 const real_t* __restrict__ pz, const int* __restrict__ cnt, double* __restrict__ partial)
 {
    __shared__ double sU[8], sK[8];
    const int n = cnt[C_NATOMS];
-   double u = 0.0, k = 0.0;
+   double u = 0.0, k = 0.0;                        // sums in double in both builds
    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
    {
       if (!(cellType[cell[i]] & CT_LOCAL)) continue;
@@ -395,7 +396,7 @@ __global__ void __launch_bounds__(1024)
 k_energy_final(const double* __restrict__ partial, int nPart, double* __restrict__ out)
 {
    __shared__ double sU[32], sK[32];
-   double u = 0.0, k = 0.0;
+   double u = 0.0, k = 0.0;                        // sums in double in both builds
    for (int i = threadIdx.x; i < nPart; i += 1024) { u += partial[2 * i]; k += partial[2 * i + 1]; }
    #pragma unroll
    for (int o = 16; o > 0; o >>= 1) { u += __shfl_down_sync(0xffffffffu, u, o); k += __shfl_down_sync(0xffffffffu, k, o); }
@@ -416,17 +417,17 @@ static int allocAtoms(AtomArrays& a, long cap)
    const long capP = cap + COMD_PAD;
    for (int k = 0; k < 3; ++k)
    {
-      CUDA_TRY(cudaMalloc(&a.r[k], capP * sizeof(double)));
-      CUDA_TRY(cudaMalloc(&a.p[k], capP * sizeof(double)));
-      CUDA_TRY(cudaMemset(a.r[k], 0, capP * sizeof(double)));
+      CUDA_TRY(cudaMalloc(&a.r[k], capP * sizeof(real_t)));
+      CUDA_TRY(cudaMalloc(&a.p[k], capP * sizeof(real_t)));
+      CUDA_TRY(cudaMemset(a.r[k], 0, capP * sizeof(real_t)));
    }
    CUDA_TRY(cudaMalloc(&a.gid, capP * sizeof(int)));
    CUDA_TRY(cudaMalloc(&a.spec, capP * sizeof(int)));
    CUDA_TRY(cudaMalloc(&a.cell, capP * sizeof(int)));
    CUDA_TRY(cudaMalloc(&a.rf, capP * sizeof(float4)));
    CUDA_TRY(cudaMemset(a.rf, 0, capP * sizeof(float4)));
-   CUDA_TRY(cudaMalloc(&a.rq, capP * sizeof(double4)));
-   CUDA_TRY(cudaMemset(a.rq, 0, capP * sizeof(double4)));
+   CUDA_TRY(cudaMalloc(&a.rq, capP * sizeof(real4)));
+   CUDA_TRY(cudaMemset(a.rq, 0, capP * sizeof(real4)));
    return COMD_OK;
 }
 static void freeAtoms(AtomArrays& a)
@@ -468,9 +469,9 @@ extern "C" int comd_dev_create(ComdDev** out, int deviceId, const ComdGeometry* 
       int pc[3] = { geom->procCoord[0], geom->procCoord[1], geom->procCoord[2] };
       pc[ax] = (pc[ax] + dir + geom->procGrid[ax]) % geom->procGrid[ax];
       d->nbrRank[f] = pc[0] + geom->procGrid[0] * (pc[1] + geom->procGrid[1] * pc[2]);
-      for (int a = 0; a < 3; ++a) d->shift[f][a] = 0.0;
-      if (dir < 0 && geom->procCoord[ax] == 0) d->shift[f][ax] = +1.0 * geom->globalExtent[ax];
-      if (dir > 0 && geom->procCoord[ax] == geom->procGrid[ax] - 1) d->shift[f][ax] = -1.0 * geom->globalExtent[ax];
+      for (int a = 0; a < 3; ++a) d->shift[f][a] = R(0.0);
+      if (dir < 0 && geom->procCoord[ax] == 0) d->shift[f][ax] = +R(1.0) * geom->globalExtent[ax];
+      if (dir > 0 && geom->procCoord[ax] == geom->procGrid[ax] - 1) d->shift[f][ax] = -R(1.0) * geom->globalExtent[ax];
    }
    d->rank = geom->procCoord[0] + geom->procGrid[0] * (geom->procCoord[1] + geom->procGrid[1] * geom->procCoord[2]);
    d->nRanks = geom->procGrid[0] * geom->procGrid[1] * geom->procGrid[2];
@@ -491,8 +492,8 @@ extern "C" int comd_dev_create(ComdDev** out, int deviceId, const ComdGeometry* 
    int rc;
    if ((rc = allocAtoms(d->A, cap)) != COMD_OK) return rc;
    if ((rc = allocAtoms(d->B, cap)) != COMD_OK) return rc;
-   for (int k = 0; k < 3; ++k) { CUDA_TRY(cudaMalloc(&d->f[k], (cap + COMD_PAD) * sizeof(double))); CUDA_TRY(cudaMemset(d->f[k], 0, (cap + COMD_PAD) * sizeof(double))); }
-   CUDA_TRY(cudaMalloc(&d->e, cap * sizeof(double))); CUDA_TRY(cudaMemset(d->e, 0, cap * sizeof(double)));
+   for (int k = 0; k < 3; ++k) { CUDA_TRY(cudaMalloc(&d->f[k], (cap + COMD_PAD) * sizeof(real_t))); CUDA_TRY(cudaMemset(d->f[k], 0, (cap + COMD_PAD) * sizeof(real_t))); }
+   CUDA_TRY(cudaMalloc(&d->e, cap * sizeof(real_t))); CUDA_TRY(cudaMemset(d->e, 0, cap * sizeof(real_t)));
    CUDA_TRY(cudaMalloc(&d->cellStart, (g.nCells + 1) * sizeof(int)));
    CUDA_TRY(cudaMemset(d->cellStart, 0, (g.nCells + 1) * sizeof(int)));
    CUDA_TRY(cudaMalloc(&d->cellCount, g.nCells * sizeof(int)));
@@ -507,12 +508,12 @@ extern "C" int comd_dev_create(ComdDev** out, int deviceId, const ComdGeometry* 
    CUDA_TRY(cudaMalloc(&d->cnt, C_COUNT * sizeof(int)));
    CUDA_TRY(cudaMemset(d->cnt, 0, C_COUNT * sizeof(int)));
    CUDA_TRY(cudaMallocHost(&d->hCnt, C_COUNT * sizeof(int)));
-   CUDA_TRY(cudaMalloc(&d->redPartial, 2 * RED_BLOCKS * sizeof(double)));
-   CUDA_TRY(cudaMalloc(&d->redOut, 2 * sizeof(double)));
-   CUDA_TRY(cudaMallocHost(&d->hRed, 2 * sizeof(double)));
-   CUDA_TRY(cudaMalloc(&d->rhobar, (cap + COMD_PAD) * sizeof(double)));
-   CUDA_TRY(cudaMalloc(&d->dfEmbed, (cap + COMD_PAD) * sizeof(double)));
-   CUDA_TRY(cudaMemset(d->dfEmbed, 0, (cap + COMD_PAD) * sizeof(double)));
+   CUDA_TRY(cudaMalloc(&d->redPartial, 2 * RED_BLOCKS * sizeof(real_t)));
+   CUDA_TRY(cudaMalloc(&d->redOut, 2 * sizeof(real_t)));
+   CUDA_TRY(cudaMallocHost(&d->hRed, 2 * sizeof(real_t)));
+   CUDA_TRY(cudaMalloc(&d->rhobar, (cap + COMD_PAD) * sizeof(real_t)));
+   CUDA_TRY(cudaMalloc(&d->dfEmbed, (cap + COMD_PAD) * sizeof(real_t)));
+   CUDA_TRY(cudaMemset(d->dfEmbed, 0, (cap + COMD_PAD) * sizeof(real_t)));
 
    // message capacity: the two largest planes of cells, generously populated
    // (bufCapacity, haloExchange.c:202-207, sized without MAXATOMS padding)
@@ -523,14 +524,14 @@ extern "C" int comd_dev_create(ComdDev** out, int deviceId, const ComdGeometry* 
       if (p > plane) plane = p;
    }
    const double perCell = (double)cap / (double)g.nCells;
-   d->msgCap = (long)(2 * plane * (perCell * 1.5 + 8)) + 1024;
+   d->msgCap = (long)(2 * plane * (perCell * R(1.5) + 8)) + 1024;
    if (d->msgCap > cap) d->msgCap = cap;
    for (int k = 0; k < 2; ++k)
    {
-      CUDA_TRY(cudaMalloc(&d->sendBuf[k], d->msgCap * COMD_MSG_DOUBLES * sizeof(double)));
-      CUDA_TRY(cudaMalloc(&d->recvBuf[k], d->msgCap * COMD_MSG_DOUBLES * sizeof(double)));
-      CUDA_TRY(cudaMalloc(&d->fpSend[k], d->msgCap * sizeof(double)));
-      CUDA_TRY(cudaMalloc(&d->fpRecv[k], d->msgCap * sizeof(double)));
+      CUDA_TRY(cudaMalloc(&d->sendBuf[k], d->msgCap * COMD_MSG_REALS * sizeof(real_t)));
+      CUDA_TRY(cudaMalloc(&d->recvBuf[k], d->msgCap * COMD_MSG_REALS * sizeof(real_t)));
+      CUDA_TRY(cudaMalloc(&d->fpSend[k], d->msgCap * sizeof(real_t)));
+      CUDA_TRY(cudaMalloc(&d->fpRecv[k], d->msgCap * sizeof(real_t)));
    }
    CUDA_TRY(cudaMalloc(&d->runOff, (plane + 2) * 24 * sizeof(int)));
    CUDA_TRY(cudaMalloc(&d->nlStat, 2 * sizeof(unsigned long long)));
@@ -553,7 +554,7 @@ extern "C" int comd_dev_create(ComdDev** out, int deviceId, const ComdGeometry* 
    }
    CUDA_TRY(cudaMemcpy(d->cellType, ct.data(), g.nCells, cudaMemcpyHostToDevice));
    d->approxAtoms = 0;
-   d->mass = 1.0;
+   d->mass = R(1.0);
    d->optForceVariant = 1;
    d->optNlN3 = 1;
    if (const char* ev = getenv("COMD_NL_N3")) d->optNlN3 = atoi(ev) != 0;
@@ -617,7 +618,7 @@ extern "C" int comd_dev_destroy(ComdDev* d)
 
 extern "C" int comd_dev_set_mass(ComdDev* d, double m)
 {
-   if (!d || !(m > 0.0)) { comdSetError("comd_dev_set_mass: bad argument"); return COMD_E_ARG; }
+   if (!d || !(m > R(0.0))) { comdSetError("comd_dev_set_mass: bad argument"); return COMD_E_ARG; }
    d->e2ePristine = 0;
    d->mass = m;
    return COMD_OK;
@@ -625,7 +626,7 @@ extern "C" int comd_dev_set_mass(ComdDev* d, double m)
 
 extern "C" int comd_dev_set_lj(ComdDev* d, double sigma, double epsilon, double cutoff)
 {
-   if (!d || !(cutoff > 0.0)) { comdSetError("comd_dev_set_lj: bad argument"); return COMD_E_ARG; }
+   if (!d || !(cutoff > R(0.0))) { comdSetError("comd_dev_set_lj: bad argument"); return COMD_E_ARG; }
    for (int a = 0; a < 3; ++a)
       if (d->hostGeom.boxSize[a] < cutoff)
       { comdSetError("comd_dev_set_lj: cell size %g < cutoff %g on axis %d", d->hostGeom.boxSize[a], cutoff, a); return COMD_E_ARG; }
@@ -636,7 +637,7 @@ extern "C" int comd_dev_set_lj(ComdDev* d, double sigma, double epsilon, double 
 
 extern "C" int comd_dev_set_eam(ComdDev* d, double cutoff, const ComdTable* phi, const ComdTable* rho, const ComdTable* f)
 {
-   if (!d || !phi || !rho || !f || !(cutoff > 0.0)) { comdSetError("comd_dev_set_eam: bad argument"); return COMD_E_ARG; }
+   if (!d || !phi || !rho || !f || !(cutoff > R(0.0))) { comdSetError("comd_dev_set_eam: bad argument"); return COMD_E_ARG; }
    for (int a = 0; a < 3; ++a)
       if (d->hostGeom.boxSize[a] < cutoff)
       { comdSetError("comd_dev_set_eam: cell size %g < cutoff %g on axis %d", d->hostGeom.boxSize[a], cutoff, a); return COMD_E_ARG; }
@@ -645,13 +646,15 @@ extern "C" int comd_dev_set_eam(ComdDev* d, double cutoff, const ComdTable* phi,
    long total = 0;
    for (int k = 0; k < 3; ++k) total += t[k]->n + 3 + 1;
    if (d->tabMem) cudaFree(d->tabMem);
-   CUDA_TRY(cudaMalloc(&d->tabMem, total * sizeof(double)));
+   CUDA_TRY(cudaMalloc(&d->tabMem, total * sizeof(real_t)));
    DevTable* out[3] = { &d->tPhi, &d->tRho, &d->tF };
    long off = 0;
    for (int k = 0; k < 3; ++k)
    {
       const int n = t[k]->n;
-      CUDA_TRY(cudaMemcpy(d->tabMem + off, t[k]->values - 1, (n + 3) * sizeof(double), cudaMemcpyHostToDevice));
+      std::vector<real_t> hv((size_t)n + 3);               // the padded table values[-1..n+1] in the device's precision
+      for (int i = 0; i < n + 3; ++i) hv[i] = (real_t)t[k]->values[i - 1];
+      CUDA_TRY(cudaMemcpy(d->tabMem + off, hv.data(), (n + 3) * sizeof(real_t), cudaMemcpyHostToDevice));
       out[k]->n = n; out[k]->x0 = t[k]->x0; out[k]->invDx = t[k]->invDx; out[k]->v = d->tabMem + off + 1;
       off += n + 3 + ((n + 3) & 1);      // keep every table 16-byte aligned
    }
@@ -662,46 +665,46 @@ extern "C" int comd_dev_set_eam(ComdDev* d, double cutoff, const ComdTable* phi,
    if (phi->n == rho->n && phi->x0 == rho->x0 && phi->invDx == rho->invDx)
    {
       const int n = phi->n;
-      std::vector<double> h(2 * (size_t)(n + 3));
+      std::vector<real_t> h(2 * (size_t)(n + 3));
       for (int i = -1; i < n + 2; ++i) { h[2 * (i + 1)] = phi->values[i]; h[2 * (i + 1) + 1] = rho->values[i]; }
-      CUDA_TRY(cudaMalloc(&d->tPRmem, h.size() * sizeof(double)));
-      CUDA_TRY(cudaMemcpy(d->tPRmem, h.data(), h.size() * sizeof(double), cudaMemcpyHostToDevice));
+      CUDA_TRY(cudaMalloc(&d->tPRmem, h.size() * sizeof(real_t)));
+      CUDA_TRY(cudaMemcpy(d->tPRmem, h.data(), h.size() * sizeof(real_t), cudaMemcpyHostToDevice));
       d->tPR = d->tPRmem + 1;
       // shifted copies: tW[0][k] = entry k-1, tW[1][k] = entry k; entries past n+1 repeat the last one
       for (int c = 0; c < 2; ++c)
       {
          if (d->tW[c]) { cudaFree(d->tW[c]); d->tW[c] = nullptr; }
          const int len = n + 8;
-         std::vector<double> w(2 * (size_t)len);
+         std::vector<real_t> w(2 * (size_t)len);
          for (int k = 0; k < len; ++k)
          {
             int e = k - 1 + c; if (e > n + 1) e = n + 1;
             w[2 * k] = phi->values[e]; w[2 * k + 1] = rho->values[e];
          }
-         CUDA_TRY(cudaMalloc(&d->tW[c], w.size() * sizeof(double)));
-         CUDA_TRY(cudaMemcpy(d->tW[c], w.data(), w.size() * sizeof(double), cudaMemcpyHostToDevice));
+         CUDA_TRY(cudaMalloc(&d->tW[c], w.size() * sizeof(real_t)));
+         CUDA_TRY(cudaMemcpy(d->tW[c], w.data(), w.size() * sizeof(real_t), cudaMemcpyHostToDevice));
       }
    }
    {  // pass-3 records: g1 = T[i+1]-T[i-1], q = (T[i+2]-T[i]) - g1, the two differences interpolate()
       // (eam.c:573-578) forms for the derivative, in the same IEEE operations
       if (d->tDR) { cudaFree(d->tDR); d->tDR = nullptr; }
       const int n = rho->n;
-      std::vector<double> w(2 * (size_t)(n + 2));
+      std::vector<real_t> w(2 * (size_t)(n + 2));
       for (int i = 0; i <= n; ++i)
       {
-         const double tm = rho->values[i - 1], t0 = rho->values[i], t1 = rho->values[i + 1];
-         const double t2 = rho->values[i + 2 > n + 1 ? n + 1 : i + 2];
-         const double g1 = t1 - tm, g2 = t2 - t0;
+         const real_t tm = rho->values[i - 1], t0 = rho->values[i], t1 = rho->values[i + 1];
+         const real_t t2 = rho->values[i + 2 > n + 1 ? n + 1 : i + 2];
+         const real_t g1 = t1 - tm, g2 = t2 - t0;
          w[2 * i] = g1; w[2 * i + 1] = g2 - g1;
       }
-      CUDA_TRY(cudaMalloc(&d->tDR, w.size() * sizeof(double)));
-      CUDA_TRY(cudaMemcpy(d->tDR, w.data(), w.size() * sizeof(double), cudaMemcpyHostToDevice));
+      CUDA_TRY(cudaMalloc(&d->tDR, w.size() * sizeof(real_t)));
+      CUDA_TRY(cudaMemcpy(d->tDR, w.data(), w.size() * sizeof(real_t), cudaMemcpyHostToDevice));
    }
    {  // list path: per interval i the four numbers interpolate() (eam.c:573-578) forms from T[i-1..i+2], in the
       // same IEEE operations, as one 32-byte record: value = a + 0.5 t (g1 + t c2), slope = 0.5 (g1 + t q) invDx
       const ComdTable* tv[2] = { phi, rho };
-      double4** dst[2] = { &d->rvPhi, &d->rvRho };
-      std::vector<double> w3;
+      real4** dst[2] = { &d->rvPhi, &d->rvRho };
+      std::vector<real_t> w3;
       const bool sameGrid = phi->n == rho->n && phi->x0 == rho->x0 && phi->invDx == rho->invDx;
       if (d->r3) { cudaFree(d->r3); d->r3 = nullptr; }
       if (sameGrid) w3.resize(4 * (size_t)(phi->n + 2));
@@ -710,21 +713,21 @@ extern "C" int comd_dev_set_eam(ComdDev* d, double cutoff, const ComdTable* phi,
          if (*dst[k]) { cudaFree(*dst[k]); *dst[k] = nullptr; }
          const int n = tv[k]->n;
          const double* T = tv[k]->values;
-         std::vector<double> w(4 * (size_t)(n + 2));
+         std::vector<real_t> w(4 * (size_t)(n + 2));
          for (int i = 0; i <= n; ++i)
          {
-            const double tm = T[i - 1], t0 = T[i], t1 = T[i + 1], t2 = T[i + 2 > n + 1 ? n + 1 : i + 2];
-            const double g1 = t1 - tm, g2 = t2 - t0;
-            w[4 * i] = t0; w[4 * i + 1] = g1; w[4 * i + 2] = t1 + tm - 2.0 * t0; w[4 * i + 3] = g2 - g1;
+            const real_t tm = T[i - 1], t0 = T[i], t1 = T[i + 1], t2 = T[i + 2 > n + 1 ? n + 1 : i + 2];
+            const real_t g1 = t1 - tm, g2 = t2 - t0;
+            w[4 * i] = t0; w[4 * i + 1] = g1; w[4 * i + 2] = t1 + tm - R(2.0) * t0; w[4 * i + 3] = g2 - g1;
             if (sameGrid) { w3[4 * i + 2 * k] = g1; w3[4 * i + 2 * k + 1] = g2 - g1; }
          }
-         CUDA_TRY(cudaMalloc(dst[k], w.size() * sizeof(double)));
-         CUDA_TRY(cudaMemcpy(*dst[k], w.data(), w.size() * sizeof(double), cudaMemcpyHostToDevice));
+         CUDA_TRY(cudaMalloc(dst[k], w.size() * sizeof(real_t)));
+         CUDA_TRY(cudaMemcpy(*dst[k], w.data(), w.size() * sizeof(real_t), cudaMemcpyHostToDevice));
       }
       if (sameGrid)
       {
-         CUDA_TRY(cudaMalloc(&d->r3, w3.size() * sizeof(double)));
-         CUDA_TRY(cudaMemcpy(d->r3, w3.data(), w3.size() * sizeof(double), cudaMemcpyHostToDevice));
+         CUDA_TRY(cudaMalloc(&d->r3, w3.size() * sizeof(real_t)));
+         CUDA_TRY(cudaMemcpy(d->r3, w3.data(), w3.size() * sizeof(real_t), cudaMemcpyHostToDevice));
       }
    }
    d->potKind = 2; d->cutoff = cutoff; d->eValid = 0;
@@ -821,8 +824,8 @@ extern "C" int comd_dev_redistribute(ComdDev* d)
 }
 
 extern "C" int comd_dev_upload_atoms(ComdDev* d, int n, const int* gid, const int* species,
-                                     const double* rx, const double* ry, const double* rz,
-                                     const double* px, const double* py, const double* pz)
+                                     const real_t* rx, const real_t* ry, const real_t* rz,
+                                     const real_t* px, const real_t* py, const real_t* pz)
 {
    if (!d || n < 0 || !gid || !rx || !ry || !rz) { comdSetError("comd_dev_upload_atoms: bad argument"); return COMD_E_ARG; }
    if (n > d->cap) { comdSetError("comd_dev_upload_atoms: %d atoms > capacity %ld", n, d->cap); return COMD_E_CAPACITY; }
@@ -830,16 +833,16 @@ extern "C" int comd_dev_upload_atoms(ComdDev* d, int n, const int* gid, const in
    CUDA_TRY(cudaSetDevice(d->device));
    cudaStream_t s = d->stream;
    AtomArrays& A = d->A;
-   const double* hr[3] = { rx, ry, rz };
-   const double* hp[3] = { px, py, pz };
+   const real_t* hr[3] = { rx, ry, rz };
+   const real_t* hp[3] = { px, py, pz };
    for (int k = 0; k < 3; ++k)
    {
-      CUDA_TRY(cudaMemcpyAsync(A.r[k], hr[k], n * sizeof(double), cudaMemcpyHostToDevice, s));
-      if (hp[k]) CUDA_TRY(cudaMemcpyAsync(A.p[k], hp[k], n * sizeof(double), cudaMemcpyHostToDevice, s));
-      else CUDA_TRY(cudaMemsetAsync(A.p[k], 0, n * sizeof(double), s));
-      CUDA_TRY(cudaMemsetAsync(d->f[k], 0, d->cap * sizeof(double), s));
+      CUDA_TRY(cudaMemcpyAsync(A.r[k], hr[k], n * sizeof(real_t), cudaMemcpyHostToDevice, s));
+      if (hp[k]) CUDA_TRY(cudaMemcpyAsync(A.p[k], hp[k], n * sizeof(real_t), cudaMemcpyHostToDevice, s));
+      else CUDA_TRY(cudaMemsetAsync(A.p[k], 0, n * sizeof(real_t), s));
+      CUDA_TRY(cudaMemsetAsync(d->f[k], 0, d->cap * sizeof(real_t), s));
    }
-   CUDA_TRY(cudaMemsetAsync(d->e, 0, d->cap * sizeof(double), s));
+   CUDA_TRY(cudaMemsetAsync(d->e, 0, d->cap * sizeof(real_t), s));
    CUDA_TRY(cudaMemcpyAsync(A.gid, gid, n * sizeof(int), cudaMemcpyHostToDevice, s));
    if (species) CUDA_TRY(cudaMemcpyAsync(A.spec, species, n * sizeof(int), cudaMemcpyHostToDevice, s));
    else CUDA_TRY(cudaMemsetAsync(A.spec, 0, n * sizeof(int), s));
@@ -872,7 +875,7 @@ extern "C" int comd_dev_num_total(ComdDev* d, int* n)
 }
 
 static int downloadCommon(ComdDev* d, bool localOnly, int* nOut, int capacity, int* gid, int* species, int* refBox,
-                          double* r[3], double* p[3], double* f[3], double* U)
+                          real_t* r[3], real_t* p[3], real_t* f[3], real_t* U)
 {
    CUDA_TRY(cudaSetDevice(d->device));
    int rc = syncCounters(d, "comd_dev_download");
@@ -880,7 +883,7 @@ static int downloadCommon(ComdDev* d, bool localOnly, int* nOut, int capacity, i
    const int n = d->hCnt[C_NATOMS];
    std::vector<int> cell(n), tmpI(n);
    std::vector<unsigned char> ct(d->g.nCells);
-   std::vector<double> tmpD(n);
+   std::vector<real_t> tmpD(n);
    CUDA_TRY(cudaMemcpy(cell.data(), d->A.cell, n * sizeof(int), cudaMemcpyDeviceToHost));
    CUDA_TRY(cudaMemcpy(ct.data(), d->cellType, d->g.nCells, cudaMemcpyDeviceToHost));
    std::vector<int> keep; keep.reserve(n);
@@ -894,9 +897,9 @@ static int downloadCommon(ComdDev* d, bool localOnly, int* nOut, int capacity, i
       CUDA_TRY(cudaMemcpy(tmpI.data(), src, n * sizeof(int), cudaMemcpyDeviceToHost));
       for (int k = 0; k < m; ++k) dst[k] = tmpI[keep[k]];
       return COMD_OK; };
-   auto pullD = [&](const double* src, double* dst) -> int {
+   auto pullD = [&](const real_t* src, real_t* dst) -> int {
       if (!dst) return COMD_OK;
-      CUDA_TRY(cudaMemcpy(tmpD.data(), src, n * sizeof(double), cudaMemcpyDeviceToHost));
+      CUDA_TRY(cudaMemcpy(tmpD.data(), src, n * sizeof(real_t), cudaMemcpyDeviceToHost));
       for (int k = 0; k < m; ++k) dst[k] = tmpD[keep[k]];
       return COMD_OK; };
    if ((rc = pullI(d->A.gid, gid))) return rc;
@@ -912,19 +915,19 @@ static int downloadCommon(ComdDev* d, bool localOnly, int* nOut, int capacity, i
 }
 
 extern "C" int comd_dev_download_atoms(ComdDev* d, int* nLocalOut, int capacity, int* gid, int* species, int* refBox,
-                                       double* rx, double* ry, double* rz, double* px, double* py, double* pz,
-                                       double* fx, double* fy, double* fz, double* U)
+                                       real_t* rx, real_t* ry, real_t* rz, real_t* px, real_t* py, real_t* pz,
+                                       real_t* fx, real_t* fy, real_t* fz, real_t* U)
 {
    if (!d) return COMD_E_ARG;
-   double* r[3] = { rx, ry, rz }; double* p[3] = { px, py, pz }; double* f[3] = { fx, fy, fz };
+   real_t* r[3] = { rx, ry, rz }; real_t* p[3] = { px, py, pz }; real_t* f[3] = { fx, fy, fz };
    return downloadCommon(d, true, nLocalOut, capacity, gid, species, refBox, r, p, f, U);
 }
 
 extern "C" int comd_dev_download_all(ComdDev* d, int* nOut, int capacity, int* gid, int* refBox,
-                                     double* rx, double* ry, double* rz)
+                                     real_t* rx, real_t* ry, real_t* rz)
 {
    if (!d) return COMD_E_ARG;
-   double* r[3] = { rx, ry, rz };
+   real_t* r[3] = { rx, ry, rz };
    return downloadCommon(d, false, nOut, capacity, gid, nullptr, refBox, r, nullptr, nullptr, nullptr);
 }
 
@@ -948,7 +951,7 @@ extern "C" int comd_dev_halo_bytes(ComdDev* d, int kind, int face, long* sentByt
    if (!d || face < 0 || face > 5 || kind < 0 || kind > 1) return COMD_E_ARG;
    CUDA_TRY(cudaSetDevice(d->device));
    int rc = syncCounters(d, "comd_dev_halo_bytes");
-   const long per = kind == 0 ? COMD_MSG_DOUBLES * (long)sizeof(double) : (long)sizeof(double);
+   const long per = kind == 0 ? COMD_MSG_REALS * (long)sizeof(real_t) : (long)sizeof(real_t);
    if (sentBytes) *sentBytes = per * d->hCnt[(kind == 0 ? C_SEND0 : C_FPSEND0) + face];
    if (receivedBytes) *receivedBytes = per * d->hCnt[(kind == 0 ? C_RECV0 : C_FPGOT0) + face];
    return rc;
@@ -970,7 +973,7 @@ extern "C" int comd_dev_advance_position(ComdDev* d, double dt)
    d->e2ePristine = 0;
    CUDA_TRY(cudaSetDevice(d->device));
    d->checkFused = 0;
-   k_advance_position<<<gridFor(d->approxAtoms, 256), 256, 0, d->stream>>>(dt, 1.0 / d->mass, d->A.cell, d->cellType,
+   k_advance_position<<<gridFor(d->approxAtoms, 256), 256, 0, d->stream>>>(dt, R(1.0) / d->mass, d->A.cell, d->cellType,
       d->A.r[0], d->A.r[1], d->A.r[2], d->A.p[0], d->A.p[1], d->A.p[2], d->cnt, d->A.rq); LAUNCH_CHECK(d);
    d->posDirty = 1;
    return COMD_OK;
@@ -981,10 +984,10 @@ extern "C" int comd_dev_energy(ComdDev* d, double eLocal[2])
    if (!d || !eLocal) return COMD_E_ARG;
    if (d->potKind != 0 && !d->eValid) { comdSetError("comd_dev_energy: no force evaluation with energies since the atoms last moved"); return COMD_E_STATE; }
    CUDA_TRY(cudaSetDevice(d->device));
-   k_energy_partial<<<RED_BLOCKS, 256, 0, d->stream>>>(0.5 / d->mass, d->A.cell, d->cellType, d->e, d->A.p[0], d->A.p[1], d->A.p[2],
+   k_energy_partial<<<RED_BLOCKS, 256, 0, d->stream>>>(R(0.5) / d->mass, d->A.cell, d->cellType, d->e, d->A.p[0], d->A.p[1], d->A.p[2],
       d->cnt, d->redPartial); LAUNCH_CHECK(d);
    k_energy_final<<<1, 1024, 0, d->stream>>>(d->redPartial, RED_BLOCKS, d->redOut); LAUNCH_CHECK(d);
-   CUDA_TRY(cudaMemcpyAsync(d->hRed, d->redOut, 2 * sizeof(double), cudaMemcpyDeviceToHost, d->stream));
+   CUDA_TRY(cudaMemcpyAsync(d->hRed, d->redOut, 2 * sizeof(real_t), cudaMemcpyDeviceToHost, d->stream));
    int rc = syncCounters(d, "comd_dev_energy");
    eLocal[0] = d->hRed[0]; eLocal[1] = d->hRed[1];
    return rc;
@@ -1019,7 +1022,7 @@ extern "C" int comd_dev_compute_force(ComdDev* d)
 
 // FP32 shadow positions after a drift that was not followed by a redistribute
 __global__ void __launch_bounds__(256)
-k_refresh_shadow(DevGeom g, const double* __restrict__ rx, const double* __restrict__ ry, const double* __restrict__ rz,
+k_refresh_shadow(DevGeom g, const real_t* __restrict__ rx, const real_t* __restrict__ ry, const real_t* __restrict__ rz,
                  float4* __restrict__ rf, const int* __restrict__ cnt)
 {
    const int n = cnt[C_NATOMS];
@@ -1067,9 +1070,9 @@ static int launchKickDrift(ComdDev* d, double dt, bool two = false)
 {
    NVTX_RANGE("kick + drift");
    const bool check = d->useNL && d->nlValid;
-   const double h = 0.5 * d->skin;
+   const real_t h = R(0.5) * d->skin;
    const int grid = gridFor(d->approxAtoms, 256);
-#define KD_ARGS 0.5 * dt, dt, 1.0 / d->mass, d->A.cell, d->cellType, d->A.r[0], d->A.r[1], d->A.r[2], d->A.p[0], d->A.p[1], d->A.p[2], \
+#define KD_ARGS R(0.5) * dt, dt, R(1.0) / d->mass, d->A.cell, d->cellType, d->A.r[0], d->A.r[1], d->A.r[2], d->A.p[0], d->A.p[1], d->A.p[2], \
    d->f[0], d->f[1], d->f[2], d->cnt, d->A.rq, d->nlLastR[0], d->nlLastR[1], d->nlLastR[2], h * h
    if (check) CUDA_TRY(cudaMemsetAsync(d->cnt + C_NLREBUILD, 0, sizeof(int), d->stream));
    if (two && check) k_kick_drift<true, true><<<grid, 256, 0, d->stream>>>(KD_ARGS);
@@ -1103,7 +1106,7 @@ extern "C" int comd_dev_timestep(ComdDev* d, int nSteps, double dt)
       PH_MARK(d, 5);
       if (it == nSteps - 1)
       {
-         rc = comd_dev_advance_velocity(d, 0.5 * dt);
+         rc = comd_dev_advance_velocity(d, R(0.5) * dt);
          if (rc != COMD_OK) { d->inTimestep = 0; return rc; }
       }
       PH_MARK(d, 6);
@@ -1215,7 +1218,7 @@ k_local_rows(DevGeom g, const int* __restrict__ cellStart, int* __restrict__ row
    if (t == 0) rowOff[nRows] = carry;
 }
 
-struct CompactArrays { const double* in[10]; double* out[10]; const int* gidIn; int* gidOut; };
+struct CompactArrays { const real_t* in[10]; real_t* out[10]; const int* gidIn; int* gidOut; };
 // arrays K0..K1-1 (0-2 r, 3-5 p, 6-8 f, 9 U) of the local atoms, row by row, into dense output arrays
 template <int K0, int K1, bool GID>
 __global__ void __launch_bounds__(256)
@@ -1238,9 +1241,9 @@ k_compact_local(CompactArrays A, const int* __restrict__ rowBeg, const int* __re
 // check: same gids in the same order, and no input position further than skin/2 from the snapshot the
 // neighbour list was built on -> the sort and the list are still valid for these inputs.
 __global__ void __launch_bounds__(256)
-k_e2e_check(const int* __restrict__ rowBeg, const int* __restrict__ rowOff, int nRows, int n, double half2,
-            const int* __restrict__ gidIn, const double* __restrict__ xin, const double* __restrict__ yin, const double* __restrict__ zin,
-            const int* __restrict__ gid, const double* __restrict__ lx, const double* __restrict__ ly, const double* __restrict__ lz,
+k_e2e_check(const int* __restrict__ rowBeg, const int* __restrict__ rowOff, int nRows, int n, real_t half2,
+            const int* __restrict__ gidIn, const real_t* __restrict__ xin, const real_t* __restrict__ yin, const real_t* __restrict__ zin,
+            const int* __restrict__ gid, const real_t* __restrict__ lx, const real_t* __restrict__ ly, const real_t* __restrict__ lz,
             int* __restrict__ flag)
 {
    bool bad = false;
@@ -1251,15 +1254,15 @@ k_e2e_check(const int* __restrict__ rowBeg, const int* __restrict__ rowOff, int 
       for (int t = threadIdx.x; t < len; t += blockDim.x)
       {
          if (o + t >= n) { bad = true; break; }
-         const double dx = xin[o + t] - lx[b + t], dy = yin[o + t] - ly[b + t], dz = zin[o + t] - lz[b + t];
+         const real_t dx = xin[o + t] - lx[b + t], dy = yin[o + t] - ly[b + t], dz = zin[o + t] - lz[b + t];
          bad |= gidIn[o + t] != gid[b + t] || !(dx * dx + dy * dy + dz * dz <= half2);
       }
    }
    if (bad) *flag = 1;
 }
-struct ScatterArrays { const double* in[9]; double* out[9]; };
+struct ScatterArrays { const real_t* in[9]; real_t* out[9]; };
 __global__ void __launch_bounds__(256)
-k_e2e_scatter(ScatterArrays A, const int* __restrict__ rowBeg, const int* __restrict__ rowOff, int nRows, double4* __restrict__ rq)
+k_e2e_scatter(ScatterArrays A, const int* __restrict__ rowBeg, const int* __restrict__ rowOff, int nRows, real4* __restrict__ rq)
 {
    for (int row = blockIdx.x; row < nRows; row += gridDim.x)
    {
@@ -1268,7 +1271,7 @@ k_e2e_scatter(ScatterArrays A, const int* __restrict__ rowBeg, const int* __rest
       {
          #pragma unroll
          for (int k = 0; k < 9; ++k) A.out[k][b + t] = A.in[k][o + t];
-         rq[b + t] = make_double4(A.in[0][o + t], A.in[1][o + t], A.in[2][o + t], 0.0);
+         rq[b + t] = make_real4(A.in[0][o + t], A.in[1][o + t], A.in[2][o + t], R(0.0));
       }
    }
 }
@@ -1294,7 +1297,7 @@ extern "C" int comd_host_free(void* p)
 }
 
 // the inputs of a speculative call against what the previous call handed out, bit for bit
-struct EqualArrays { const double* a[9]; const double* b[9]; };
+struct EqualArrays { const real_t* a[9]; const real_t* b[9]; };
 __global__ void __launch_bounds__(256)
 k_e2e_equal(EqualArrays Q, const int* __restrict__ ga, const int* __restrict__ gb, int n, int* __restrict__ flag)
 {
@@ -1332,13 +1335,13 @@ static bool rangesOverlap(const void* a, const void* b, size_t bytes)
 //    inputs are scattered to their rows, sort and list are kept.
 //  * full: new atoms; re-bin, sort, rebuild.
 static int stepHostImpl(ComdDev* d, int n, double dt, bool inputsOnDevice,
-                        const int* gidIn, const double* const in[9],
+                        const int* gidIn, const real_t* const in[9],
                         int* nOut, int* gidOut, double* const outPtr[10], double eLocal[2])
 {
    cudaStream_t s = d->stream;
    const long cap = d->cap;
    AtomArrays& A = d->A;
-   double* devIn[9] = { A.r[0], A.r[1], A.r[2], A.p[0], A.p[1], A.p[2], d->f[0], d->f[1], d->f[2] };
+   real_t* devIn[9] = { A.r[0], A.r[1], A.r[2], A.p[0], A.p[1], A.p[2], d->f[0], d->f[1], d->f[2] };
    bool pinnedIn = inputsOnDevice || isPinned(gidIn);
    for (int k = 0; k < 9 && !inputsOnDevice; ++k) pinnedIn = pinnedIn && isPinned(in[k]);
    bool pinnedOut = !gidOut || isPinned(gidOut);
@@ -1350,20 +1353,20 @@ static int stepHostImpl(ComdDev* d, int n, double dt, bool inputsOnDevice,
       {
          if (d->hStage) cudaFreeHost(d->hStage);
          d->hStage = nullptr; d->hStageDoubles = 0;
-         CUDA_TRY(cudaMallocHost(&d->hStage, need * sizeof(double)));
+         CUDA_TRY(cudaMallocHost(&d->hStage, need * sizeof(real_t)));
          d->hStageDoubles = need;
       }
    }
-   double* st = d->hStage;
+   real_t* st = d->hStage;
    const int nRows = d->g.n[1] * d->g.n[2];
    if (!d->rowTab) CUDA_TRY(cudaMalloc(&d->rowTab, (2 * (size_t)nRows + 2) * sizeof(int)));
    if (!d->e2eU)
    {
-      CUDA_TRY(cudaMalloc(&d->e2eU, (size_t)cap * 9 * sizeof(double)));
+      CUDA_TRY(cudaMalloc(&d->e2eU, (size_t)cap * 9 * sizeof(real_t)));
       CUDA_TRY(cudaMalloc(&d->e2eUgid, (size_t)cap * sizeof(int)));
       for (int k = 0; k < 2; ++k)
       {
-         CUDA_TRY(cudaMalloc(&d->e2eOut[k], (size_t)cap * 10 * sizeof(double)));
+         CUDA_TRY(cudaMalloc(&d->e2eOut[k], (size_t)cap * 10 * sizeof(real_t)));
          CUDA_TRY(cudaMalloc(&d->e2eOutGid[k], (size_t)cap * sizeof(int)));
       }
       CUDA_TRY(cudaMalloc(&d->e2eFlag, sizeof(int)));
@@ -1377,7 +1380,7 @@ static int stepHostImpl(ComdDev* d, int n, double dt, bool inputsOnDevice,
    }
    int* rowBeg = d->rowTab; int* rowOff = d->rowTab + nRows;
    const int prev = d->e2eCur, nxt = prev ^ 1;
-   double* scr[9]; double* cout[10]; EqualArrays Q;
+   real_t* scr[9]; real_t* cout[10]; EqualArrays Q;
    for (int k = 0; k < 9; ++k) { scr[k] = d->e2eU + k * cap; Q.a[k] = scr[k]; Q.b[k] = d->e2eOut[prev] + k * cap; }
    for (int k = 0; k < 10; ++k) cout[k] = d->e2eOut[nxt] + k * cap;
    int* ugid = d->e2eUgid; int* coutGid = d->e2eOutGid[nxt];
@@ -1392,9 +1395,9 @@ static int stepHostImpl(ComdDev* d, int n, double dt, bool inputsOnDevice,
    if (!inputsOnDevice)
       for (int k = 0; k < 10; ++k)
       {
-         for (int j = 0; j < 9; ++j) cross = cross || (j != k && rangesOverlap(outPtr[k], in[j], n * sizeof(double)));
+         for (int j = 0; j < 9; ++j) cross = cross || (j != k && rangesOverlap(outPtr[k], in[j], n * sizeof(real_t)));
          cross = cross || rangesOverlap(outPtr[k], gidIn, n * sizeof(int));
-         if (k < 9) cross = cross || rangesOverlap(gidOut, in[k], n * sizeof(double));
+         if (k < 9) cross = cross || rangesOverlap(gidOut, in[k], n * sizeof(real_t));
       }
    const bool spec = tryResume && d->e2ePristine && d->e2eSpecArmed && d->nRanks == 1 && pinnedIn && pinnedOut && !cross && n == d->e2eLastM;
    cudaStream_t u = spec ? d->upStream : s;
@@ -1408,15 +1411,15 @@ static int stepHostImpl(ComdDev* d, int n, double dt, bool inputsOnDevice,
       }
       for (int k = 0; k < 9; ++k)
       {
-         const double* src = in[k];
-         if (!pinnedIn) { memcpy(st + k * cap, in[k], n * sizeof(double)); src = st + k * cap; }
-         CUDA_TRY(cudaMemcpyAsync(scr[k], src, n * sizeof(double), cudaMemcpyHostToDevice, u));
+         const real_t* src = in[k];
+         if (!pinnedIn) { memcpy(st + k * cap, in[k], n * sizeof(real_t)); src = st + k * cap; }
+         CUDA_TRY(cudaMemcpyAsync(scr[k], src, n * sizeof(real_t), cudaMemcpyHostToDevice, u));
          if (spec && k == 2) CUDA_TRY(cudaEventRecord(d->evUpR, u));
          if (spec && k == 5) CUDA_TRY(cudaEventRecord(d->evUpP, u));
          if (!spec && k == 2 && tryResume)
          {
             CUDA_TRY(cudaMemsetAsync(d->cnt + C_NLREBUILD, 0, sizeof(int), s));
-            const double h = 0.5 * d->skin;
+            const real_t h = R(0.5) * d->skin;
             k_e2e_check<<<gridFor(nRows, 1, 148 * 8), 256, 0, s>>>(rowBeg, rowOff, nRows, n, h * h, ugid, scr[0], scr[1], scr[2],
                A.gid, d->nlLastR[0], d->nlLastR[1], d->nlLastR[2], d->cnt + C_NLREBUILD); LAUNCH_CHECK(d);
             int rcf = comdAllreduceFlagDevice(d, d->cnt + C_NLREBUILD);
@@ -1447,7 +1450,7 @@ static int stepHostImpl(ComdDev* d, int n, double dt, bool inputsOnDevice,
    }
    else
    {
-      for (int k = 0; k < 9; ++k) CUDA_TRY(cudaMemcpyAsync(devIn[k], scr[k], n * sizeof(double), cudaMemcpyDeviceToDevice, s));
+      for (int k = 0; k < 9; ++k) CUDA_TRY(cudaMemcpyAsync(devIn[k], scr[k], n * sizeof(real_t), cudaMemcpyDeviceToDevice, s));
       CUDA_TRY(cudaMemcpyAsync(A.gid, ugid, n * sizeof(int), cudaMemcpyDeviceToDevice, s));
       CUDA_TRY(cudaMemsetAsync(A.spec, 0, n * sizeof(int), s));
       k_set_int<<<gridFor(n, 256), 256, 0, s>>>(A.cell, cellIndex(d->g, 0, 0, 0), n); LAUNCH_CHECK(d);
@@ -1462,7 +1465,7 @@ static int stepHostImpl(ComdDev* d, int n, double dt, bool inputsOnDevice,
    int rc = launchKickDrift(d, dt);
    if (rc == COMD_OK) rc = comd_dev_redistribute(d);
    if (rc != COMD_OK) { d->inTimestep = 0; return rc; }
-   const double* cin[10] = { d->A.r[0], d->A.r[1], d->A.r[2], d->A.p[0], d->A.p[1], d->A.p[2], d->f[0], d->f[1], d->f[2], d->e };
+   const real_t* cin[10] = { d->A.r[0], d->A.r[1], d->A.r[2], d->A.p[0], d->A.p[1], d->A.p[2], d->f[0], d->f[1], d->f[2], d->e };
    k_local_rows<<<1, 1024, 0, s>>>(d->g, d->cellStart, rowBeg, rowOff); LAUNCH_CHECK(d);
    {
       CompactArrays C;
@@ -1485,8 +1488,8 @@ static int stepHostImpl(ComdDev* d, int n, double dt, bool inputsOnDevice,
       for (int k = 0; k < 3; ++k)
       {
          if (!outPtr[k]) continue;
-         double* dst = pinnedOut ? outPtr[k] : st + k * cap;
-         CUDA_TRY(cudaMemcpyAsync(dst, cout[k], n * sizeof(double), cudaMemcpyDeviceToHost, d->copyStream));
+         real_t* dst = pinnedOut ? outPtr[k] : st + k * cap;
+         CUDA_TRY(cudaMemcpyAsync(dst, cout[k], n * sizeof(real_t), cudaMemcpyDeviceToHost, d->copyStream));
       }
       if (gidOut)
       {
@@ -1495,7 +1498,7 @@ static int stepHostImpl(ComdDev* d, int n, double dt, bool inputsOnDevice,
       }
    }
    rc = computeForce(d, 1);
-   if (rc == COMD_OK) rc = comd_dev_advance_velocity(d, 0.5 * dt);
+   if (rc == COMD_OK) rc = comd_dev_advance_velocity(d, R(0.5) * dt);
    d->inTimestep = 0;
    if (rc != COMD_OK) return rc;
    {
@@ -1514,8 +1517,8 @@ static int stepHostImpl(ComdDev* d, int n, double dt, bool inputsOnDevice,
       if (spec && k == 3) CUDA_TRY(cudaStreamWaitEvent(s, d->evUpP, 0));     // p leaves after p has arrived,
       if (spec && k == 6) CUDA_TRY(cudaStreamWaitEvent(s, d->evUp, 0));      // f and U after everything has
       if (!outPtr[k]) continue;
-      double* dst = pinnedOut ? outPtr[k] : st + k * cap;
-      CUDA_TRY(cudaMemcpyAsync(dst, cout[k], m * sizeof(double), cudaMemcpyDeviceToHost, s));
+      real_t* dst = pinnedOut ? outPtr[k] : st + k * cap;
+      CUDA_TRY(cudaMemcpyAsync(dst, cout[k], m * sizeof(real_t), cudaMemcpyDeviceToHost, s));
    }
    if (gidOut && !earlyCopy)
    {
@@ -1540,23 +1543,23 @@ static int stepHostImpl(ComdDev* d, int n, double dt, bool inputsOnDevice,
    d->e2ePristine = 1;
    if (!pinnedOut)
    {
-      for (int k = 0; k < 10; ++k) if (outPtr[k]) memcpy(outPtr[k], st + k * cap, m * sizeof(double));
+      for (int k = 0; k < 10; ++k) if (outPtr[k]) memcpy(outPtr[k], st + k * cap, m * sizeof(real_t));
       if (gidOut) memcpy(gidOut, st + 10 * cap, m * sizeof(int));
    }
    return COMD_OK;
 }
 
 extern "C" int comd_dev_step_host(ComdDev* d, int n, double dt,
-                                  const int* gidIn, const double* rIn[3], const double* pIn[3], const double* fIn[3],
-                                  int* nOut, int* gidOut, double* rOut[3], double* pOut[3], double* fOut[3], double* UOut,
+                                  const int* gidIn, const real_t* rIn[3], const real_t* pIn[3], const real_t* fIn[3],
+                                  int* nOut, int* gidOut, real_t* rOut[3], real_t* pOut[3], real_t* fOut[3], real_t* UOut,
                                   double eLocal[2])
 {
    if (!d || n <= 0 || !gidIn || !rIn || !pIn || !fIn) { comdSetError("comd_dev_step_host: bad argument"); return COMD_E_ARG; }
    if (n > d->cap) { comdSetError("comd_dev_step_host: %d atoms > capacity %ld", n, d->cap); return COMD_E_CAPACITY; }
    if (d->potKind == 0) { comdSetError("comd_dev_step_host: no potential set"); return COMD_E_STATE; }
    CUDA_TRY(cudaSetDevice(d->device));
-   const double* in[9] = { rIn[0], rIn[1], rIn[2], pIn[0], pIn[1], pIn[2], fIn[0], fIn[1], fIn[2] };
-   double* outPtr[10] = { rOut ? rOut[0] : nullptr, rOut ? rOut[1] : nullptr, rOut ? rOut[2] : nullptr,
+   const real_t* in[9] = { rIn[0], rIn[1], rIn[2], pIn[0], pIn[1], pIn[2], fIn[0], fIn[1], fIn[2] };
+   real_t* outPtr[10] = { rOut ? rOut[0] : nullptr, rOut ? rOut[1] : nullptr, rOut ? rOut[2] : nullptr,
                           pOut ? pOut[0] : nullptr, pOut ? pOut[1] : nullptr, pOut ? pOut[2] : nullptr,
                           fOut ? fOut[0] : nullptr, fOut ? fOut[1] : nullptr, fOut ? fOut[2] : nullptr, UOut };
    return stepHostImpl(d, n, dt, false, gidIn, in, nOut, gidOut, outPtr, eLocal);

@@ -13,28 +13,28 @@
 #include "halo_runs.cuh"
 
 // interpolate(), eam.c:557-579, incl. its one-sided clamps
-__device__ __forceinline__ void tableLookup(const DevTable& t, double r, double& f, double& df)
+__device__ __forceinline__ void tableLookup(const DevTable& t, real_t r, real_t& f, real_t& df)
 {
-   const double* __restrict__ tt = t.v;
+   const real_t* __restrict__ tt = t.v;
    if (r < t.x0) r = t.x0;
    r = (r - t.x0) * t.invDx;
    int ii = (int)floor(r);
    if (ii > t.n) { ii = t.n; r = t.n / t.invDx; }
    r = r - floor(r);
-   const double tm = __ldg(tt + ii - 1), t0 = __ldg(tt + ii), t1 = __ldg(tt + ii + 1), t2 = __ldg(tt + ii + 2);
-   const double g1 = t1 - tm;
-   const double g2 = t2 - t0;
-   f = t0 + 0.5 * r * (g1 + r * (t1 + tm - 2.0 * t0));
-   df = 0.5 * (g1 + r * (g2 - g1)) * t.invDx;
+   const real_t tm = __ldg(tt + ii - 1), t0 = __ldg(tt + ii), t1 = __ldg(tt + ii + 1), t2 = __ldg(tt + ii + 2);
+   const real_t g1 = t1 - tm;
+   const real_t g2 = t2 - t0;
+   f = t0 + R(0.5) * r * (g1 + r * (t1 + tm - R(2.0) * t0));
+   df = R(0.5) * (g1 + r * (g2 - g1)) * t.invDx;
 }
 
 __global__ void __launch_bounds__(128)
-k_eam_pass1(DevGeom g, DevTable tPhi, DevTable tRho, DevTable tF, double rc2,
-            const double* __restrict__ rx, const double* __restrict__ ry, const double* __restrict__ rz,
+k_eam_pass1(DevGeom g, DevTable tPhi, DevTable tRho, DevTable tF, real_t rc2,
+            const real_t* __restrict__ rx, const real_t* __restrict__ ry, const real_t* __restrict__ rz,
             const int* __restrict__ cell, const unsigned char* __restrict__ cellType,
             const int* __restrict__ cellStart, const int* __restrict__ cnt,
-            double* __restrict__ fx, double* __restrict__ fy, double* __restrict__ fz, double* __restrict__ e,
-            double* __restrict__ rhobar, double* __restrict__ dfEmbed)
+            real_t* __restrict__ fx, real_t* __restrict__ fy, real_t* __restrict__ fz, real_t* __restrict__ e,
+            real_t* __restrict__ rhobar, real_t* __restrict__ dfEmbed)
 {
    const int n = cnt[C_NATOMS];
    const int rowY = g.P[0], rowZ = g.P[0] * g.P[1];
@@ -42,8 +42,8 @@ k_eam_pass1(DevGeom g, DevTable tPhi, DevTable tRho, DevTable tF, double rc2,
    {
       const int c = cell[i];
       if (!(cellType[c] & CT_LOCAL)) continue;
-      const double xi = rx[i], yi = ry[i], zi = rz[i];
-      double ax = 0.0, ay = 0.0, az = 0.0, u = 0.0, rb = 0.0;
+      const real_t xi = rx[i], yi = ry[i], zi = rz[i];
+      real_t ax = R(0.0), ay = R(0.0), az = R(0.0), u = R(0.0), rb = R(0.0);
       #pragma unroll 1
       for (int dz = -1; dz <= 1; ++dz)
       {
@@ -54,23 +54,23 @@ k_eam_pass1(DevGeom g, DevTable tPhi, DevTable tRho, DevTable tF, double rc2,
             const int jb = cellStart[rc - 1], je = cellStart[rc + 2];
             for (int j = jb; j < je; ++j)
             {
-               const double dx = xi - rx[j], dyy = yi - ry[j], dzz = zi - rz[j];
-               const double r2 = dx * dx + dyy * dyy + dzz * dzz;
+               const real_t dx = xi - rx[j], dyy = yi - ry[j], dzz = zi - rz[j];
+               const real_t r2 = dx * dx + dyy * dyy + dzz * dzz;
                if (r2 <= rc2 && j != i)
                {
-                  const double r = sqrt(r2);
-                  double phi, dphi, rho, drho;
+                  const real_t r = sqrt(r2);
+                  real_t phi, dphi, rho, drho;
                   tableLookup(tPhi, r, phi, dphi);
                   tableLookup(tRho, r, rho, drho);
-                  const double s = dphi / r;
+                  const real_t s = dphi / r;
                   ax -= s * dx; ay -= s * dyy; az -= s * dzz;
-                  u += 0.5 * phi;
+                  u += R(0.5) * phi;
                   rb += rho;
                }
             }
          }
       }
-      double fe, dfe;
+      real_t fe, dfe;
       tableLookup(tF, rb, fe, dfe);
       fx[i] = ax; fy[i] = ay; fz[i] = az;
       e[i] = u + fe;
@@ -80,11 +80,11 @@ k_eam_pass1(DevGeom g, DevTable tPhi, DevTable tRho, DevTable tF, double rc2,
 }
 
 __global__ void __launch_bounds__(128)
-k_eam_pass3(DevGeom g, DevTable tRho, double rc2,
-            const double* __restrict__ rx, const double* __restrict__ ry, const double* __restrict__ rz,
+k_eam_pass3(DevGeom g, DevTable tRho, real_t rc2,
+            const real_t* __restrict__ rx, const real_t* __restrict__ ry, const real_t* __restrict__ rz,
             const int* __restrict__ cell, const unsigned char* __restrict__ cellType,
-            const int* __restrict__ cellStart, const int* __restrict__ cnt, const double* __restrict__ dfEmbed,
-            double* __restrict__ fx, double* __restrict__ fy, double* __restrict__ fz)
+            const int* __restrict__ cellStart, const int* __restrict__ cnt, const real_t* __restrict__ dfEmbed,
+            real_t* __restrict__ fx, real_t* __restrict__ fy, real_t* __restrict__ fz)
 {
    const int n = cnt[C_NATOMS];
    const int rowY = g.P[0], rowZ = g.P[0] * g.P[1];
@@ -92,9 +92,9 @@ k_eam_pass3(DevGeom g, DevTable tRho, double rc2,
    {
       const int c = cell[i];
       if (!(cellType[c] & CT_LOCAL)) continue;
-      const double xi = rx[i], yi = ry[i], zi = rz[i];
-      const double dfi = dfEmbed[i];
-      double ax = 0.0, ay = 0.0, az = 0.0;
+      const real_t xi = rx[i], yi = ry[i], zi = rz[i];
+      const real_t dfi = dfEmbed[i];
+      real_t ax = R(0.0), ay = R(0.0), az = R(0.0);
       #pragma unroll 1
       for (int dz = -1; dz <= 1; ++dz)
       {
@@ -105,14 +105,14 @@ k_eam_pass3(DevGeom g, DevTable tRho, double rc2,
             const int jb = cellStart[rc - 1], je = cellStart[rc + 2];
             for (int j = jb; j < je; ++j)
             {
-               const double dx = xi - rx[j], dyy = yi - ry[j], dzz = zi - rz[j];
-               const double r2 = dx * dx + dyy * dyy + dzz * dzz;
+               const real_t dx = xi - rx[j], dyy = yi - ry[j], dzz = zi - rz[j];
+               const real_t r2 = dx * dx + dyy * dyy + dzz * dzz;
                if (r2 < rc2 && j != i)
                {
-                  const double r = sqrt(r2);
-                  double rho, drho;
+                  const real_t r = sqrt(r2);
+                  real_t rho, drho;
                   tableLookup(tRho, r, rho, drho);
-                  const double s = (dfi + dfEmbed[j]) * drho / r;
+                  const real_t s = (dfi + dfEmbed[j]) * drho / r;
                   ax -= s * dx; ay -= s * dyy; az -= s * dzz;
                }
             }
@@ -168,8 +168,8 @@ k_fp_layout(DevGeom g, const int* __restrict__ cellStart, int* __restrict__ runT
 }
 
 __global__ void __launch_bounds__(256)
-k_fp_pack(DevGeom g, int axis, const int* __restrict__ runTab, int runStride, const double* __restrict__ dfEmbed,
-          double* __restrict__ bufM, double* __restrict__ bufP, long msgCap, int* __restrict__ cnt)
+k_fp_pack(DevGeom g, int axis, const int* __restrict__ runTab, int runStride, const real_t* __restrict__ dfEmbed,
+          real_t* __restrict__ bufM, real_t* __restrict__ bufP, long msgCap, int* __restrict__ cnt)
 {
    const int d = blockIdx.y, face = 2 * axis + d;
    const FpFace F = fpFace(g, face, 0);
@@ -177,7 +177,7 @@ k_fp_pack(DevGeom g, int axis, const int* __restrict__ runTab, int runStride, co
    const int* runOff = runStart + runStride;
    const int total = runOff[F.nRuns];
    if (total > msgCap) { if (threadIdx.x == 0 && blockIdx.x == 0) atomicOr(&cnt[C_ERR], ERRB_CAPACITY); return; }
-   double* out = d ? bufP : bufM;
+   real_t* out = d ? bufP : bufM;
    for (int m = blockIdx.x * blockDim.x + threadIdx.x; m < total; m += gridDim.x * blockDim.x)
    {
       const int k = fpLocate(runOff, F.nRuns, m);
@@ -186,9 +186,9 @@ k_fp_pack(DevGeom g, int axis, const int* __restrict__ runTab, int runStride, co
 }
 
 __global__ void __launch_bounds__(256)
-k_fp_unpack(DevGeom g, int axis, const int* __restrict__ runTab, int runStride, double* __restrict__ dfEmbed,
-            const double* __restrict__ bufFromM, const double* __restrict__ bufFromP,
-            const int* __restrict__ nFromM, const int* __restrict__ nFromP, int* __restrict__ cnt, double4* __restrict__ rq)
+k_fp_unpack(DevGeom g, int axis, const int* __restrict__ runTab, int runStride, real_t* __restrict__ dfEmbed,
+            const real_t* __restrict__ bufFromM, const real_t* __restrict__ bufFromP,
+            const int* __restrict__ nFromM, const int* __restrict__ nFromP, int* __restrict__ cnt, real4* __restrict__ rq)
 {
    const int d = blockIdx.y, face = 2 * axis + d;
    const FpFace F = fpFace(g, face, 1);
@@ -197,7 +197,7 @@ k_fp_unpack(DevGeom g, int axis, const int* __restrict__ runTab, int runStride, 
    const int total = runOff[F.nRuns];
    const int got = d ? *nFromP : *nFromM;
    if (got != total) { if (threadIdx.x == 0 && blockIdx.x == 0) atomicOr(&cnt[C_ERR], ERRB_FPMISMATCH); return; }
-   const double* in = d ? bufFromP : bufFromM;
+   const real_t* in = d ? bufFromP : bufFromM;
    for (int m = blockIdx.x * blockDim.x + threadIdx.x; m < total; m += gridDim.x * blockDim.x)
    {
       const int k = fpLocate(runOff, F.nRuns, m);
@@ -248,7 +248,7 @@ int comdForceEAM(ComdDev* d)
       // leave a factor 4 to the 32-bit high word and let one pair contribute up to 1/4 of the domain
       const double rhoMax = fabs(d->tF.x0) + (d->tF.n + 1) / d->tF.invDx;
       int ex = 0; frexp(rhoMax, &ex);                   // rhoMax < 2^ex
-      Q.n3ScaleRho = ldexp(1.0, 53 - ex);
+      Q.n3ScaleRho = ldexp(R(1.0), 53 - ex);
    }
    if (d->useNL)
    {  // list path: rhobar, F' halo, then every pair force in pass 3 (force_nl.cuh); pair energies on request

@@ -9,17 +9,17 @@
 // atomics and a fixed summation order (cell-major, gid-minor).
 #include "force_n3.cuh"
 
-struct LjParams { double s6, eps, rc2, eShift; };
+struct LjParams { real_t s6, eps, rc2, eShift; };
 
 // One thread per atom; the 27-cell stencil is 9 contiguous atom runs thanks to the padded
 // x-fastest cell order.  All lanes of a warp that share a cell read the same j -> one
 // broadcast transaction per load.
 __global__ void __launch_bounds__(128)
 k_lj_force_rows(DevGeom g, LjParams P,
-                const double* __restrict__ rx, const double* __restrict__ ry, const double* __restrict__ rz,
+                const real_t* __restrict__ rx, const real_t* __restrict__ ry, const real_t* __restrict__ rz,
                 const int* __restrict__ cell, const unsigned char* __restrict__ cellType,
                 const int* __restrict__ cellStart, const int* __restrict__ cnt,
-                double* __restrict__ fx, double* __restrict__ fy, double* __restrict__ fz, double* __restrict__ e)
+                real_t* __restrict__ fx, real_t* __restrict__ fy, real_t* __restrict__ fz, real_t* __restrict__ e)
 {
    const int n = cnt[C_NATOMS];
    const int rowY = g.P[0], rowZ = g.P[0] * g.P[1];
@@ -27,8 +27,8 @@ k_lj_force_rows(DevGeom g, LjParams P,
    {
       const int c = cell[i];
       if (!(cellType[c] & CT_LOCAL)) continue;
-      const double xi = rx[i], yi = ry[i], zi = rz[i];
-      double ax = 0.0, ay = 0.0, az = 0.0, u = 0.0;
+      const real_t xi = rx[i], yi = ry[i], zi = rz[i];
+      real_t ax = R(0.0), ay = R(0.0), az = R(0.0), u = R(0.0);
       #pragma unroll 1
       for (int dz = -1; dz <= 1; ++dz)
       {
@@ -39,21 +39,21 @@ k_lj_force_rows(DevGeom g, LjParams P,
             const int jb = cellStart[rc - 1], je = cellStart[rc + 2];
             for (int j = jb; j < je; ++j)
             {
-               const double dx = xi - rx[j], dyy = yi - ry[j], dzz = zi - rz[j];
-               const double r2 = dx * dx + dyy * dyy + dzz * dzz;
+               const real_t dx = xi - rx[j], dyy = yi - ry[j], dzz = zi - rz[j];
+               const real_t r2 = dx * dx + dyy * dyy + dzz * dzz;
                if (r2 <= P.rc2 && j != i)
                {
-                  const double ir2 = 1.0 / r2;
-                  const double r6 = (P.s6 * ir2) * (ir2 * ir2);
-                  u += r6 * (r6 - 1.0) - P.eShift;
-                  const double fr = -4.0 * P.eps * r6 * ir2 * (12.0 * r6 - 6.0);
+                  const real_t ir2 = R(1.0) / r2;
+                  const real_t r6 = (P.s6 * ir2) * (ir2 * ir2);
+                  u += r6 * (r6 - R(1.0)) - P.eShift;
+                  const real_t fr = -R(4.0) * P.eps * r6 * ir2 * (R(12.0) * r6 - R(6.0));
                   ax -= dx * fr; ay -= dyy * fr; az -= dzz * fr;
                }
             }
          }
       }
       fx[i] = ax; fy[i] = ay; fz[i] = az;
-      e[i] = (0.5 * u) * (4.0 * P.eps);
+      e[i] = (R(0.5) * u) * (R(4.0) * P.eps);
    }
 }
 
@@ -64,8 +64,8 @@ int comdForceLJ(ComdDev* d)
    P.s6 = s * s * s * s * s * s;
    P.eps = d->ljEps;
    P.rc2 = d->cutoff * d->cutoff;
-   const double rc6 = P.s6 / (P.rc2 * P.rc2 * P.rc2);
-   P.eShift = 1.0 * rc6 * (rc6 - 1.0);                 // POT_SHIFT 1.0, ljForce.c:83,173-174
+   const real_t rc6 = P.s6 / (P.rc2 * P.rc2 * P.rc2);
+   P.eShift = R(1.0) * rc6 * (rc6 - R(1.0));                 // POT_SHIFT 1.0, ljForce.c:83,173-174
    d->eValid = 1;
    if (d->useNL || d->optForceVariant == 1)
    {

@@ -54,17 +54,17 @@ static_assert(sizeof(TileHdr) <= FT_HDR, "TileHdr");
 struct PairParams
 {
    // LJ
-   double s6, eps, eShift;
+   real_t s6, eps, eShift;
    // both
-   double rc2;
+   real_t rc2;
    // EAM
    DevTable tPhi, tRho, tF;
-   const double2* tPR;                // interleaved {phi,rho} (same grid), entry 0; valid [-1, n+1]
-   const double2* tW0; const double2* tW1;   // shifted copies of tPR for 256-bit window loads (comd_dev.cuh), or NULL
-   const double2* tDR;                // pass 3: {g1, g2-g1} of rho per interval
+   const real2* tPR;                // interleaved {phi,rho} (same grid), entry 0; valid [-1, n+1]
+   const real2* tW0; const real2* tW1;   // shifted copies of tPR for 256-bit window loads (comd_dev.cuh), or NULL
+   const real2* tDR;                // pass 3: {g1, g2-g1} of rho per interval
    // list path (force_nl.cuh): 32-byte records, one sector per lookup
-   const double4* rvPhi; const double4* rvRho; const double4* r3;
-   double n3ScaleRho;                 // fixed-point scale of the rhobar accumulators (force_n3.cuh)
+   const real4* rvPhi; const real4* rvRho; const real4* r3;
+   real_t n3ScaleRho;                 // fixed-point scale of the rhobar accumulators (force_n3.cuh)
 };
 
 // ---- PTX helpers: mbarrier + 1-D bulk copy (TMA engine, UBLKCP in SASS) -----------------
@@ -92,25 +92,25 @@ __device__ __forceinline__ void bulkG2S(void* dst, const void* src, unsigned byt
 }
 
 // one 256-bit read-only load (LDG.E.256 on sm_100a): two adjacent double2, 32-byte aligned
-__device__ __forceinline__ void ldg256(const double2* p, double2& a, double2& b)
+__device__ __forceinline__ void ldg256(const real2* p, real2& a, real2& b)
 {
    asm volatile("ld.global.nc.v4.f64 {%0, %1, %2, %3}, [%4];" : "=d"(a.x), "=d"(a.y), "=d"(b.x), "=d"(b.y) : "l"(p));
 }
 
 // interpolate() of eam.c:557-579 on four already-loaded stencil values
-__device__ __forceinline__ void interpValue(double tm, double t0, double t1, double t, double& f)
+__device__ __forceinline__ void interpValue(real_t tm, real_t t0, real_t t1, real_t t, real_t& f)
 {
-   const double g1 = t1 - tm;
-   f = t0 + 0.5 * t * (g1 + t * (t1 + tm - 2.0 * t0));
+   const real_t g1 = t1 - tm;
+   f = t0 + R(0.5) * t * (g1 + t * (t1 + tm - R(2.0) * t0));
 }
-__device__ __forceinline__ void interpDeriv(double tm, double t0, double t1, double t2, double t, double invDx, double& df)
+__device__ __forceinline__ void interpDeriv(real_t tm, real_t t0, real_t t1, real_t t2, real_t t, real_t invDx, real_t& df)
 {
-   const double g1 = t1 - tm;
-   const double g2 = t2 - t0;
-   df = 0.5 * (g1 + t * (g2 - g1)) * invDx;
+   const real_t g1 = t1 - tm;
+   const real_t g2 = t2 - t0;
+   df = R(0.5) * (g1 + t * (g2 - g1)) * invDx;
 }
 // index + fraction with the reference's one-sided clamps (eam.c:561-571)
-__device__ __forceinline__ int tableIndex(const DevTable& T, double r, double& t)
+__device__ __forceinline__ int tableIndex(const DevTable& T, real_t r, real_t& t)
 {
    if (r < T.x0) r = T.x0;
    r = (r - T.x0) * T.invDx;
@@ -119,12 +119,12 @@ __device__ __forceinline__ int tableIndex(const DevTable& T, double r, double& t
    t = r - floor(r);
    return ii;
 }
-__device__ __forceinline__ void tableLookupFull(const DevTable& T, double r, double& f, double& df)
+__device__ __forceinline__ void tableLookupFull(const DevTable& T, real_t r, real_t& f, real_t& df)
 {
-   double t;
+   real_t t;
    const int ii = tableIndex(T, r, t);
-   const double* __restrict__ v = T.v + ii;
-   const double tm = __ldg(v - 1), t0 = __ldg(v), t1 = __ldg(v + 1), t2 = __ldg(v + 2);
+   const real_t* __restrict__ v = T.v + ii;
+   const real_t tm = __ldg(v - 1), t0 = __ldg(v), t1 = __ldg(v + 1), t2 = __ldg(v + 2);
    interpValue(tm, t0, t1, t, f);
    interpDeriv(tm, t0, t1, t2, t, T.invDx, df);
 }
@@ -132,28 +132,28 @@ __device__ __forceinline__ void tableLookupFull(const DevTable& T, double r, dou
 // ---- one surviving pair, FP64 ---------------------------------------------------------
 // acc layout: [0..2] force, [3] energy part, [4] rhobar (EAM pass 1)
 template <int KIND>
-__device__ __forceinline__ void pairEval(const PairParams& P, double dx, double dy, double dz, double r2,
-                                         double dfi, double dfj, double* acc)
+__device__ __forceinline__ void pairEval(const PairParams& P, real_t dx, real_t dy, real_t dz, real_t r2,
+                                         real_t dfi, real_t dfj, real_t* acc)
 {
    if (KIND == PK_LJ)
    {  // ljForce.c:207-233
-      const double ir2 = 1.0 / r2;
-      const double r6 = (P.s6 * ir2) * (ir2 * ir2);
-      acc[3] += r6 * (r6 - 1.0) - P.eShift;
-      const double fr = -4.0 * P.eps * r6 * ir2 * (12.0 * r6 - 6.0);
+      const real_t ir2 = R(1.0) / r2;
+      const real_t r6 = (P.s6 * ir2) * (ir2 * ir2);
+      acc[3] += r6 * (r6 - R(1.0)) - P.eShift;
+      const real_t fr = -R(4.0) * P.eps * r6 * ir2 * (R(12.0) * r6 - R(6.0));
       acc[0] -= dx * fr; acc[1] -= dy * fr; acc[2] -= dz * fr;
    }
    else if (KIND == PK_EAM1)
    {  // eam.c:311-345
-      const double rinv = rsqrt(r2);
-      const double r = r2 * rinv;
-      double phi, dphi, rho;
+      const real_t rinv = rsqrt(r2);
+      const real_t r = r2 * rinv;
+      real_t phi, dphi, rho;
       if (P.tW0)
       {
-         double t;
+         real_t t;
          const int ii = tableIndex(P.tPhi, r, t);
-         const double2* v = ((ii & 1) ? P.tW1 : P.tW0) + (ii & ~1);          // entries ii-1 .. ii+2, 32-byte aligned
-         double2 vm, v0, v1, v2;
+         const real2* v = ((ii & 1) ? P.tW1 : P.tW0) + (ii & ~1);          // entries ii-1 .. ii+2, 32-byte aligned
+         real2 vm, v0, v1, v2;
          ldg256(v, vm, v0); ldg256(v + 2, v1, v2);
          interpValue(vm.x, v0.x, v1.x, t, phi);
          interpDeriv(vm.x, v0.x, v1.x, v2.x, t, P.tPhi.invDx, dphi);
@@ -161,43 +161,43 @@ __device__ __forceinline__ void pairEval(const PairParams& P, double dx, double 
       }
       else if (P.tPR)
       {
-         double t;
+         real_t t;
          const int ii = tableIndex(P.tPhi, r, t);
-         const double2* __restrict__ v = P.tPR + ii;
-         const double2 vm = __ldg(v - 1), v0 = __ldg(v), v1 = __ldg(v + 1), v2 = __ldg(v + 2);
+         const real2* __restrict__ v = P.tPR + ii;
+         const real2 vm = __ldg(v - 1), v0 = __ldg(v), v1 = __ldg(v + 1), v2 = __ldg(v + 2);
          interpValue(vm.x, v0.x, v1.x, t, phi);
          interpDeriv(vm.x, v0.x, v1.x, v2.x, t, P.tPhi.invDx, dphi);
          interpValue(vm.y, v0.y, v1.y, t, rho);
       }
       else
       {
-         double drho;
+         real_t drho;
          tableLookupFull(P.tPhi, r, phi, dphi);
          tableLookupFull(P.tRho, r, rho, drho);
       }
-      const double s = dphi * rinv;
+      const real_t s = dphi * rinv;
       acc[0] -= s * dx; acc[1] -= s * dy; acc[2] -= s * dz;
-      acc[3] += 0.5 * phi;
+      acc[3] += R(0.5) * phi;
       acc[4] += rho;
    }
    else
    {  // eam.c:390-409
-      const double rinv = rsqrt(r2);
-      const double r = r2 * rinv;
-      double t, drho;
+      const real_t rinv = rsqrt(r2);
+      const real_t r = r2 * rinv;
+      real_t t, drho;
       const int ii = tableIndex(P.tRho, r, t);
       if (P.tDR)
       {
-         const double2 gq = __ldg(P.tDR + ii);
-         drho = 0.5 * (gq.x + t * gq.y) * P.tRho.invDx;
+         const real2 gq = __ldg(P.tDR + ii);
+         drho = R(0.5) * (gq.x + t * gq.y) * P.tRho.invDx;
       }
       else
       {
-         const double* __restrict__ v = P.tRho.v + ii;
-         const double tm = __ldg(v - 1), t0 = __ldg(v), t1 = __ldg(v + 1), t2 = __ldg(v + 2);
+         const real_t* __restrict__ v = P.tRho.v + ii;
+         const real_t tm = __ldg(v - 1), t0 = __ldg(v), t1 = __ldg(v + 1), t2 = __ldg(v + 2);
          interpDeriv(tm, t0, t1, t2, t, P.tRho.invDx, drho);
       }
-      const double s = (dfi + dfj) * drho * rinv;
+      const real_t s = (dfi + dfj) * drho * rinv;
       acc[0] -= s * dx; acc[1] -= s * dy; acc[2] -= s * dz;
    }
 }
@@ -219,9 +219,9 @@ __host__ __device__ inline size_t tileSmemBytes(int sMax)
 // ---- PROCESS: compact the 8 lane queues of every atom, then one pair per lane per round ----
 template <int KIND>
 __device__ __forceinline__ void processQueues(const PairParams& P, unsigned short* myQ, unsigned short* myD, int& qn,
-                                              int gl, int si, double xi, double yi, double zi, double dfi,
-                                              const double* sx, const double* sy, const double* sz, const double* sdf,
-                                              double* acc)
+                                              int gl, int si, real_t xi, real_t yi, real_t zi, real_t dfi,
+                                              const real_t* sx, const real_t* sy, const real_t* sz, const real_t* sdf,
+                                              real_t* acc)
 {
    const unsigned full = 0xffffffffu;
    int incl = qn;
@@ -238,10 +238,10 @@ __device__ __forceinline__ void processQueues(const PairParams& P, unsigned shor
       if (k < total)
       {
          const int j = myD[k];
-         const double dx = xi - sx[j], dy = yi - sy[j], dz = zi - sz[j];
-         const double r2 = dx * dx + dy * dy + dz * dz;
+         const real_t dx = xi - sx[j], dy = yi - sy[j], dz = zi - sz[j];
+         const real_t r2 = dx * dx + dy * dy + dz * dz;
          const bool in = (KIND == PK_EAM3) ? (r2 < P.rc2) : (r2 <= P.rc2);     // eam.c:317 vs :397
-         if (in && j != si) pairEval<KIND>(P, dx, dy, dz, r2, dfi, KIND == PK_EAM3 ? sdf[j] : 0.0, acc);
+         if (in && j != si) pairEval<KIND>(P, dx, dy, dz, r2, dfi, KIND == PK_EAM3 ? sdf[j] : R(0.0), acc);
       }
    }
    __syncwarp();
@@ -251,21 +251,21 @@ __device__ __forceinline__ void processQueues(const PairParams& P, unsigned shor
 template <int KIND>
 __global__ void __launch_bounds__(FT_THREADS, 2)
 k_force_tile(DevGeom g, TileCfg cfg, PairParams P,
-             const double* __restrict__ rx, const double* __restrict__ ry, const double* __restrict__ rz,
+             const real_t* __restrict__ rx, const real_t* __restrict__ ry, const real_t* __restrict__ rz,
              const float4* __restrict__ rf, const int* __restrict__ cell, const int* __restrict__ cellStart,
-             const double* __restrict__ dfIn,
-             double* __restrict__ fx, double* __restrict__ fy, double* __restrict__ fz, double* __restrict__ e,
-             double* __restrict__ rhobar, double* __restrict__ dfOut, int* __restrict__ cnt)
+             const real_t* __restrict__ dfIn,
+             real_t* __restrict__ fx, real_t* __restrict__ fy, real_t* __restrict__ fz, real_t* __restrict__ e,
+             real_t* __restrict__ rhobar, real_t* __restrict__ dfOut, int* __restrict__ cnt)
 {
    extern __shared__ __align__(128) unsigned char smem[];
    constexpr int NACC = PairTraits<KIND>::NACC;
    const unsigned full = 0xffffffffu;
    TileHdr& H = *reinterpret_cast<TileHdr*>(smem);
    const int sMax = cfg.sMax;
-   double* sx = reinterpret_cast<double*>(smem + FT_HDR);
-   double* sy = sx + sMax;
-   double* sz = sy + sMax;
-   double* sdf = sz + sMax;
+   real_t* sx = reinterpret_cast<real_t*>(smem + FT_HDR);
+   real_t* sy = sx + sMax;
+   real_t* sz = sy + sMax;
+   real_t* sdf = sz + sMax;
    unsigned char* q = reinterpret_cast<unsigned char*>(KIND == PK_EAM3 ? sdf + sMax : sdf);
    float4* sf = reinterpret_cast<float4*>(q); q += (size_t)sMax * 16;
    unsigned short* qLane = reinterpret_cast<unsigned short*>(q); q += FT_WARPS * FT_QCAP * 32 * 2;
@@ -342,7 +342,7 @@ k_force_tile(DevGeom g, TileCfg cfg, PairParams P,
       const int si = sI0 + il;
       int cxl = 0;
       float xif = 0.f, yif = 0.f, zif = 0.f;
-      double xi = 0.0, yi = 0.0, zi = 0.0, dfi = 0.0;
+      real_t xi = R(0.0), yi = R(0.0), zi = R(0.0), dfi = R(0.0);
       if (act)
       {
          cxl = cell[iBeg + il] - cellBase;
@@ -351,7 +351,7 @@ k_force_tile(DevGeom g, TileCfg cfg, PairParams P,
          xi = sx[si]; yi = sy[si]; zi = sz[si];
          if (KIND == PK_EAM3) dfi = sdf[si];
       }
-      double acc[5] = { 0.0, 0.0, 0.0, 0.0, 0.0 };
+      real_t acc[5] = { R(0.0), R(0.0), R(0.0), R(0.0), R(0.0) };
       int qn = 0;
       #pragma unroll 1
       for (int r = 0; r < 9; ++r)
@@ -392,11 +392,11 @@ k_force_tile(DevGeom g, TileCfg cfg, PairParams P,
          if (KIND == PK_LJ)
          {
             fx[i] = acc[0]; fy[i] = acc[1]; fz[i] = acc[2];
-            e[i] = (0.5 * acc[3]) * (4.0 * P.eps);            // ljForce.c:256-261
+            e[i] = (R(0.5) * acc[3]) * (R(4.0) * P.eps);            // ljForce.c:256-261
          }
          else if (KIND == PK_EAM1)
          {
-            double fe, dfe;
+            real_t fe, dfe;
             tableLookupFull(P.tF, acc[4], fe, dfe);            // eam.c:352-371 (pass 2 fused)
             fx[i] = acc[0]; fy[i] = acc[1]; fz[i] = acc[2];
             e[i] = acc[3] + fe;
@@ -414,7 +414,7 @@ k_force_tile(DevGeom g, TileCfg cfg, PairParams P,
 // ---- host launcher ----------------------------------------------------------------------
 #include <cmath>
 template <int KIND>
-static int launchForceTile(ComdDev* d, PairParams P, const double* dfIn)
+static int launchForceTile(ComdDev* d, PairParams P, const real_t* dfIn)
 {
    const DevGeom& g = d->g;
    int txT = d->optTileTx;
@@ -427,7 +427,7 @@ static int launchForceTile(ComdDev* d, PairParams P, const double* dfIn)
    int sMax; size_t bytes;
    for (;;)
    {  // staging capacity: the 9 rows at 1.25x the mean density + slack; two CTAs per SM if possible
-      sMax = (int)(9.0 * (txT + 2) * perCell * 1.25) + 9 * 2 + 96;
+      sMax = (int)(R(9.0) * (txT + 2) * perCell * R(1.25)) + 9 * 2 + 96;
       sMax = (sMax + 1) & ~1;
       bytes = tileSmemBytes<KIND>(sMax);
       if (bytes <= 113 * 1024 || txT == 1) break;

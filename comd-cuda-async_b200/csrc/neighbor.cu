@@ -37,10 +37,10 @@ __device__ __forceinline__ int nlSlot(int pos, int G) { return G == 8 ? ((pos & 
 #define N3_FLAG     0x80000000u
 #define N3_ROWSHIFT 26
 __global__ void __launch_bounds__(256)
-k_nl_build(DevGeom g, double rc2, double rl2, const double4* __restrict__ rq,
+k_nl_build(DevGeom g, real_t rc2, real_t rl2, const real4* __restrict__ rq,
            const int* __restrict__ cell, const unsigned char* __restrict__ cellType, const int* __restrict__ cellStart,
            int* __restrict__ cnt, int* __restrict__ list, int* __restrict__ count, int stride, long rows,
-           double* __restrict__ lx, double* __restrict__ ly, double* __restrict__ lz, unsigned long long* __restrict__ stat,
+           real_t* __restrict__ lx, real_t* __restrict__ ly, real_t* __restrict__ lz, unsigned long long* __restrict__ stat,
            int bx, int by, int bz, int G)
 {
    __shared__ int farBuf[8][4][NL_FARCAP];
@@ -58,7 +58,7 @@ k_nl_build(DevGeom g, double rc2, double rl2, const double4* __restrict__ rq,
       bool act = false;
       if (i < n) { c = cell[i]; act = (cellType[c] & CT_LOCAL) != 0 && i < rows; }
       if (!__any_sync(full, act)) continue;
-      double4 pi = make_double4(0.0, 0.0, 0.0, 0.0);
+      real4 pi = make_real4(R(0.0), R(0.0), R(0.0), R(0.0));
       const int i0 = act ? i : 0;                      // a lane without a candidate re-reads its own atom
       if (act) pi = rq[i];
       // block membership of the 27 stencil cells relative to the atom's own cell (N3)
@@ -95,7 +95,7 @@ k_nl_build(DevGeom g, double rc2, double rl2, const double4* __restrict__ rq,
          // the (ballot-serialised) bookkeeping, so a trip exposes one memory latency instead of four
          for (int base = 0; base < maxlen; base += NL_U * NL_G)
          {
-            double4 pj[NL_U];
+            real4 pj[NL_U];
             bool ok[NL_U], both[NL_U];
             #pragma unroll
             for (int u = 0; u < NL_U; ++u)
@@ -115,8 +115,8 @@ k_nl_build(DevGeom g, double rc2, double rl2, const double4* __restrict__ rq,
             for (int u = 0; u < NL_U; ++u)
             {
                const int j = jb + base + u * NL_G + gl;
-               const double dx = pi.x - pj[u].x, dy = pi.y - pj[u].y, dz = pi.z - pj[u].z;
-               const double r2 = dx * dx + dy * dy + dz * dz;
+               const real_t dx = pi.x - pj[u].x, dy = pi.y - pj[u].y, dz = pi.z - pj[u].z;
+               const real_t r2 = dx * dx + dy * dy + dz * dz;
                const bool near = ok[u] && r2 <= rc2;
                const bool far = ok[u] && !near && r2 <= rl2;
                const unsigned below = (1u << gl) - 1u, grp = (1u << NL_G) - 1u;
@@ -154,8 +154,8 @@ k_nl_build(DevGeom g, double rc2, double rl2, const double4* __restrict__ rq,
 
 // ---- rebuild criterion: any local atom moved more than skin/2 since the last build --------
 __global__ void __launch_bounds__(256)
-k_nl_check(double half2, const double* __restrict__ rx, const double* __restrict__ ry, const double* __restrict__ rz,
-           const double* __restrict__ lx, const double* __restrict__ ly, const double* __restrict__ lz,
+k_nl_check(real_t half2, const real_t* __restrict__ rx, const real_t* __restrict__ ry, const real_t* __restrict__ rz,
+           const real_t* __restrict__ lx, const real_t* __restrict__ ly, const real_t* __restrict__ lz,
            const int* __restrict__ cell, const unsigned char* __restrict__ cellType, int* __restrict__ cnt)
 {
    const int n = cnt[C_NATOMS];
@@ -163,7 +163,7 @@ k_nl_check(double half2, const double* __restrict__ rx, const double* __restrict
    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
    {
       if (!(cellType[cell[i]] & CT_LOCAL)) continue;
-      const double dx = lx[i] - rx[i], dy = ly[i] - ry[i], dz = lz[i] - rz[i];
+      const real_t dx = lx[i] - rx[i], dy = ly[i] - ry[i], dz = lz[i] - rz[i];
       hit |= dx * dx + dy * dy + dz * dz > half2;
    }
    if (__any_sync(0xffffffffu, hit) && (threadIdx.x & 31) == 0) cnt[C_NLREBUILD] = 1;   // every writer stores the same value
@@ -181,9 +181,9 @@ k_nl_check(double half2, const double* __restrict__ rx, const double* __restrict
 // timestep.c:328-351; results are the same, the lists here simply never contain an emigrant.)
 __global__ void __launch_bounds__(256)
 k_nl_refresh_pack(DevGeom g, int axis, const int* __restrict__ runTab, int runStride,
-                  const double* __restrict__ rx, const double* __restrict__ ry, const double* __restrict__ rz,
-                  double* __restrict__ bufM, double* __restrict__ bufP, long msgCap, int* __restrict__ cnt,
-                  double shMx, double shMy, double shMz, double shPx, double shPy, double shPz)
+                  const real_t* __restrict__ rx, const real_t* __restrict__ ry, const real_t* __restrict__ rz,
+                  real_t* __restrict__ bufM, real_t* __restrict__ bufP, long msgCap, int* __restrict__ cnt,
+                  real_t shMx, real_t shMy, real_t shMz, real_t shPx, real_t shPy, real_t shPz)
 {
    const int d = blockIdx.y, face = 2 * axis + d;
    const FpFace F = fpFace(g, face, 0);
@@ -191,8 +191,8 @@ k_nl_refresh_pack(DevGeom g, int axis, const int* __restrict__ runTab, int runSt
    const int* runOff = runStart + runStride;
    const int total = runOff[F.nRuns];
    if (total > msgCap) { if (threadIdx.x == 0 && blockIdx.x == 0) atomicOr(&cnt[C_ERR], ERRB_CAPACITY); return; }
-   double* out = d ? bufP : bufM;
-   const double sx = d ? shPx : shMx, sy = d ? shPy : shMy, sz = d ? shPz : shMz;
+   real_t* out = d ? bufP : bufM;
+   const real_t sx = d ? shPx : shMx, sy = d ? shPy : shMy, sz = d ? shPz : shMz;
    for (int m = blockIdx.x * blockDim.x + threadIdx.x; m < total; m += gridDim.x * blockDim.x)
    {
       const int k = fpLocate(runOff, F.nRuns, m);
@@ -204,9 +204,9 @@ k_nl_refresh_pack(DevGeom g, int axis, const int* __restrict__ runTab, int runSt
 }
 __global__ void __launch_bounds__(256)
 k_nl_refresh_unpack(DevGeom g, int axis, const int* __restrict__ runTab, int runStride,
-                    double* __restrict__ rx, double* __restrict__ ry, double* __restrict__ rz,
-                    const double* __restrict__ bufFromM, const double* __restrict__ bufFromP,
-                    const int* __restrict__ nFromM, const int* __restrict__ nFromP, int* __restrict__ cnt, double4* __restrict__ rq)
+                    real_t* __restrict__ rx, real_t* __restrict__ ry, real_t* __restrict__ rz,
+                    const real_t* __restrict__ bufFromM, const real_t* __restrict__ bufFromP,
+                    const int* __restrict__ nFromM, const int* __restrict__ nFromP, int* __restrict__ cnt, real4* __restrict__ rq)
 {
    const int d = blockIdx.y, face = 2 * axis + d;
    const FpFace F = fpFace(g, face, 1);
@@ -215,14 +215,14 @@ k_nl_refresh_unpack(DevGeom g, int axis, const int* __restrict__ runTab, int run
    const int total = runOff[F.nRuns];
    const int got = d ? *nFromP : *nFromM;
    if (got != total) { if (threadIdx.x == 0 && blockIdx.x == 0) atomicOr(&cnt[C_ERR], ERRB_FPMISMATCH); return; }
-   const double* in = d ? bufFromP : bufFromM;
+   const real_t* in = d ? bufFromP : bufFromM;
    for (int m = blockIdx.x * blockDim.x + threadIdx.x; m < total; m += gridDim.x * blockDim.x)
    {
       const int k = fpLocate(runOff, F.nRuns, m);
       const int i = runStart[k] + (m - runOff[k]);                  // a halo cell by construction: never a local atom
-      const double x = in[3 * (long)m + 0], y = in[3 * (long)m + 1], z = in[3 * (long)m + 2];
+      const real_t x = in[3 * (long)m + 0], y = in[3 * (long)m + 1], z = in[3 * (long)m + 2];
       rx[i] = x; ry[i] = y; rz[i] = z;
-      rq[i] = make_double4(x, y, z, 0.0);
+      rq[i] = make_real4(x, y, z, R(0.0));
    }
 }
 
@@ -236,7 +236,7 @@ static int nlAllocate(ComdDev* d)
    const int nLocal = d->hCnt[C_NLOCAL] > 0 ? d->hCnt[C_NLOCAL] : d->approxAtoms;
    const double rl = d->cutoff + d->skin;
    const double expect = 4.0 / 3.0 * 3.14159265358979323846 * rl * rl * rl * (double)nLocal / vol;
-   int stride = (int)(expect * 1.35) + 16;
+   int stride = (int)(expect * R(1.35)) + 16;
    stride = (stride + 31) / 32 * 32;                      // whole chunks (nlSlot)
    const long rows = d->cap;
    // Keep the first allocation: the row stride is sized once from the mean density (a row overflow is reported,
@@ -250,7 +250,7 @@ static int nlAllocate(ComdDev* d)
    CUDA_TRY(cudaMemset(d->nlCount, 0, rows * sizeof(int)));
    CUDA_TRY(cudaMalloc(&d->nlCountHit, rows * sizeof(int)));
    CUDA_TRY(cudaMemset(d->nlCountHit, 0, rows * sizeof(int)));
-   for (int k = 0; k < 3; ++k) CUDA_TRY(cudaMalloc(&d->nlLastR[k], rows * sizeof(double)));
+   for (int k = 0; k < 3; ++k) CUDA_TRY(cudaMalloc(&d->nlLastR[k], rows * sizeof(real_t)));
    d->nlStride = stride; d->nlRows = rows;
    return COMD_OK;
 }
@@ -348,7 +348,7 @@ int comdNeighborRefreshOrRebuild(ComdDev* d, int* didRefresh)
 
 extern "C" int comd_dev_set_neighbor_list(ComdDev* d, int useNeighborList, double skinDistance)
 {
-   if (!d || skinDistance < 0.0) { comdSetError("comd_dev_set_neighbor_list: bad argument"); return COMD_E_ARG; }
+   if (!d || skinDistance < R(0.0)) { comdSetError("comd_dev_set_neighbor_list: bad argument"); return COMD_E_ARG; }
    d->useNL = useNeighborList ? 1 : 0;
    d->skin = skinDistance;
    d->nlValid = 0; d->runLayoutValid = 0;
