@@ -556,8 +556,8 @@ extern "C" int comd_dev_create(ComdDev** out, int deviceId, const ComdGeometry* 
    d->approxAtoms = 0;
    d->mass = R(1.0);
    d->optForceVariant = 1;
-   d->optNlN3 = 1;
-   if (const char* ev = getenv("COMD_NL_N3")) d->optNlN3 = atoi(ev) != 0;
+   d->optNlN3 = -1;
+   if (const char* ev = getenv("COMD_NL_N3")) d->optNlN3 = atoi(ev) < 0 ? -1 : atoi(ev) != 0;
    d->optTileTx = 8;
    if (const char* ev = getenv("COMD_FORCE_VARIANT")) d->optForceVariant = atoi(ev);
    if (const char* ev = getenv("COMD_TILE_TX")) d->optTileTx = atoi(ev);
@@ -1043,7 +1043,7 @@ extern "C" int comd_dev_set_option(ComdDev* d, const char* key, long value)
    if (!strcmp(key, "force_variant")) { if (value < 0 || value > 1) { comdSetError("force_variant: 0 or 1"); return COMD_E_ARG; } d->optForceVariant = (int)value; return COMD_OK; }
    if (!strcmp(key, "nl_chunks_per_cta")) { if (value < 0 || value > 64) { comdSetError("nl_chunks_per_cta: 0..64"); return COMD_E_ARG; } d->optNlChunksPerCta = (int)value; return COMD_OK; }
    if (!strcmp(key, "nl_lanes")) { if (value != 4 && value != 8) { comdSetError("nl_lanes: 4 or 8"); return COMD_E_ARG; } d->optNlLanes = (int)value; d->nlValid = 0; return COMD_OK; }
-   if (!strcmp(key, "nl_n3")) { d->optNlN3 = value != 0; d->nlValid = 0; return COMD_OK; }
+   if (!strcmp(key, "nl_n3")) { d->optNlN3 = value < 0 ? -1 : value != 0; d->nlValid = 0; return COMD_OK; }
    if (!strcmp(key, "overlap")) { d->optOverlap = value != 0; return COMD_OK; }
    if (!strcmp(key, "e2e_speculate")) { d->e2eSpecArmed = value != 0; return COMD_OK; }
    if (!strcmp(key, "overlap_sms")) { if (value < 0 || value > 148) { comdSetError("overlap_sms: 0..148"); return COMD_E_ARG; } d->optOverlapSms = (int)value; return COMD_OK; }
@@ -1058,7 +1058,7 @@ extern "C" int comd_dev_set_option(ComdDev* d, const char* key, long value)
    if (!strcmp(key, "nl_block")) { const int bx = (int)(value / 10000), by = (int)(value / 100 % 100), bz = (int)(value % 100);
       if (value != 0 && (bx < 1 || by < 1 || bz < 1 || by * bz > 32)) { comdSetError("nl_block: bx*10000 + by*100 + bz with by*bz <= 32, or 0 for auto"); return COMD_E_ARG; }
       d->optNlBlock[0] = bx; d->optNlBlock[1] = by; d->optNlBlock[2] = bz;
-      if (d->optNlN3) d->nlValid = 0;              // in-block pairs are stored once: the list is tied to the block shape
+      if (comdNlN3(d)) d->nlValid = 0;              // in-block pairs are stored once: the list is tied to the block shape
       return COMD_OK; }
    if (!strcmp(key, "tile_tx")) { if (value < 1 || value > 16) { comdSetError("tile_tx: 1..16"); return COMD_E_ARG; } d->optTileTx = (int)value; return COMD_OK; }
    comdSetError("comd_dev_set_option: unknown key '%s'", key);

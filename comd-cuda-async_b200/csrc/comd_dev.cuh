@@ -158,7 +158,7 @@ struct ComdDev
    int useNL; double skin;
    int *nlList; int *nlCount; int nlStride; int nlMax; real_t* nlLastR[3]; int nlBuilds; int nlValid;
    long nlRows;                 // rows allocated in nlList
-   int optNlN3;                          // 1 (default): pairs inside a work block are evaluated once for both atoms (force_n3.cuh)
+   int optNlN3;                          // pairs inside a work block evaluated once for both atoms (force_n3.cuh): 1 yes, 0 no, -1 (default) EAM yes / LJ no
    int optNlLanes, nlLanes;              // lanes per atom of the once-per-pair kernels (option nl_lanes: 4 default, 8) / of the current list
    int nlN3Shape[3];                     // block shape the current list was built for (0 = full list)
    int optNlChunksPerCta;                // target work chunks per CTA of the list force kernels (0 = default 32)
@@ -272,6 +272,9 @@ static inline int gridFor(long n, int block, int maxBlocks = 148 * 16)
    if (b > maxBlocks) b = maxBlocks;
    return (int)b;
 }
+
+// once-per-pair list kernels for this potential?  LJ pair terms are cheaper than the scatter, so "auto" keeps its full list
+static inline bool comdNlN3(const ComdDev* d) { return d->optNlN3 < 0 ? d->potKind == 2 : d->optNlN3 != 0; }
 
 // implemented across the translation units
 int comdForceLJ(ComdDev* d);

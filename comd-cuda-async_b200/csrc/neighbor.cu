@@ -271,7 +271,7 @@ int comdNeighborBuildIfNeeded(ComdDev* d)
    const int n = d->approxAtoms > 0 ? d->approxAtoms : (int)d->cap;
    // N3: the list is tied to the work-block shape of the force kernels (in-block pairs are stored once)
    const NlBlocks B = nlBlocksFor(d);
-   const bool n3 = d->optNlN3 != 0;
+   const bool n3 = comdNlN3(d);
    if (n3 && d->cap > (1L << N3_ROWSHIFT)) { comdSetError("neighbour list: more than %ld atoms per GPU", 1L << N3_ROWSHIFT); return COMD_E_CAPACITY; }
    d->nlN3Shape[0] = n3 ? B.bx : 0; d->nlN3Shape[1] = n3 ? B.by : 0; d->nlN3Shape[2] = n3 ? B.bz : 0;
    d->nlLanes = n3 && d->optNlLanes != 8 ? 4 : 8;

@@ -68,7 +68,7 @@ static NlBlocks nlBlocksFor(const ComdDev* d)
    static const int shapes[][3] = { {4, 4, 4}, {4, 4, 2}, {4, 2, 2}, {2, 2, 2}, {2, 2, 1}, {2, 1, 1}, {1, 1, 1} };
    const DevGeom& g = d->g;
    NlBlocks B = {};
-   for (int k = d->optNlN3 ? 0 : 1; k < 7; ++k)
+   for (int k = comdNlN3(d) ? 0 : 1; k < 7; ++k)
    {
       B.bx = shapes[k][0]; B.by = shapes[k][1]; B.bz = shapes[k][2];
       if (d->optNlBlock[0] > 0) { B.bx = d->optNlBlock[0]; B.by = d->optNlBlock[1]; B.bz = d->optNlBlock[2]; }

@@ -152,9 +152,10 @@ int  comd_comm_barrier(ComdDev* dev);                               /* barrierPa
  *                        stencil loop (the shape of LJ_Force_thread_atom, gpu_lj_thread_atom.h:31-143)
  *   "tile_tx"            link-cell path: target cells per force tile along x (1..16)
  *   "energy_every_step"  list path: per-atom EAM pair energies at every step of comd_dev_timestep (default 0)
- *   "nl_n3"              list path: 1 (default) pairs inside a work block are stored and evaluated once, for both
+ *   "nl_n3"              list path: 1 = pairs inside a work block are stored and evaluated once, for both
  *                        atoms (half-list form of neighborList.c:123,142 / eam.c:311-345 inside the block, shared-memory
- *                        fixed-point accumulators); 0 = full list, every pair met from both ends.  Invalidates the list.
+ *                        fixed-point accumulators); 0 = full list, every pair met from both ends; -1 (default) = 1 for EAM,
+ *                        0 for LJ (whose pair term is cheaper than the scatter).  Invalidates the list.
  *   "nl_lanes"           once-per-pair kernels: lanes that walk one atom's list row, 4 (default) or 8.  Invalidates the list.
  *   "nl_block"           list path: cells per work block as bx*10000 + by*100 + bz (by*bz <= 32), 0 = auto
  *   "nl_threads"         list path: cap on the CTA size of the force kernels (multiple of 32)
