@@ -489,6 +489,7 @@ def parity_leg(R):
         e = dev.energy()
         nc = dev.neighbor_counters()
         rebin(dev)
+        dev.compute_force()            # the re-bin re-sorts r and p only (as the reference's does); forces on the new owners
         runs.append((gathered_state(R, dev), R.reduce([e[0] + e[1]])[0], own0, nc))
         dev.close()
     sd, ed, own0, nc = runs[0]
