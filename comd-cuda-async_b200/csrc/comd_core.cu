@@ -24,6 +24,7 @@ void comdSetError(const char* fmt, ...)
 }
 extern "C" const char* comd_last_error(void) { return g_err; }
 extern "C" const char* comd_version(void) { return "comd-cuda-async_b200 0.1 (sm_100a)"; }
+extern "C" int comd_precision(void) { return (int)sizeof(real_t); }
 
 // ------------------------------------------------------------------ small kernels
 __global__ void k_set_int(int* p, int v, int n)
@@ -1306,7 +1307,7 @@ k_e2e_equal(EqualArrays Q, const int* __restrict__ ga, const int* __restrict__ g
    {
       bad |= ga[t] != gb[t];
       #pragma unroll
-      for (int k = 0; k < 9; ++k) bad |= __double_as_longlong(Q.a[k][t]) != __double_as_longlong(Q.b[k][t]);
+      for (int k = 0; k < 9; ++k) bad |= realBits(Q.a[k][t]) != realBits(Q.b[k][t]);
    }
    if (bad) *flag = 1;
 }
@@ -1336,7 +1337,7 @@ static bool rangesOverlap(const void* a, const void* b, size_t bytes)
 //  * full: new atoms; re-bin, sort, rebuild.
 static int stepHostImpl(ComdDev* d, int n, double dt, bool inputsOnDevice,
                         const int* gidIn, const real_t* const in[9],
-                        int* nOut, int* gidOut, double* const outPtr[10], double eLocal[2])
+                        int* nOut, int* gidOut, real_t* const outPtr[10], double eLocal[2])
 {
    cudaStream_t s = d->stream;
    const long cap = d->cap;

@@ -26,6 +26,10 @@ typedef float real_t; typedef float2 real2; typedef float4 real4;
 #define COMD_MSG_REALS 8            // AtomMsg on the wire: gid, species, r[3], p[3] = 32 B (haloExchange.h:32-38 with float real_t)
 __device__ __forceinline__ real_t mulRn(real_t a, real_t b) { return __fmul_rn(a, b); }
 __device__ __forceinline__ real_t addRn(real_t a, real_t b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ int realFloorInt(real_t x) { return __float2int_rd(x); }
+__device__ __forceinline__ long long realBits(real_t x) { return (long long)__float_as_int(x); }
+// one 16-byte load of a real4 record (LDG.E.128); P = PTX cache-policy qualifiers
+#define COMD_LDG_REAL4(P, v, p) asm volatile("ld.global" P ".v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p))
 #else
 typedef double real_t; typedef double2 real2; typedef double4 real4;
 #define R(x) x
@@ -35,6 +39,10 @@ typedef double real_t; typedef double2 real2; typedef double4 real4;
 #define COMD_MSG_REALS 7            // AtomMsg on the wire: {gid|species}, r[3], p[3] = 56 B (haloExchange.h:32-38)
 __device__ __forceinline__ real_t mulRn(real_t a, real_t b) { return __dmul_rn(a, b); }
 __device__ __forceinline__ real_t addRn(real_t a, real_t b) { return __dadd_rn(a, b); }
+__device__ __forceinline__ int realFloorInt(real_t x) { return __double2int_rd(x); }
+__device__ __forceinline__ long long realBits(real_t x) { return __double_as_longlong(x); }
+// one 32-byte load of a real4 record (LDG.E.256 on sm_100a); P = PTX cache-policy qualifiers
+#define COMD_LDG_REAL4(P, v, p) asm volatile("ld.global" P ".v4.f64 {%0, %1, %2, %3}, [%4];" : "=d"(v.x), "=d"(v.y), "=d"(v.z), "=d"(v.w) : "l"(p))
 #endif
 // identity of an atom inside a message: FP64 packs {gid, species} into one 8-byte slot, FP32 uses one 4-byte slot each
 __device__ __forceinline__ void msgPutId(real_t* o, int gid, int spec)

@@ -248,7 +248,7 @@ int comdForceEAM(ComdDev* d)
       // leave a factor 4 to the 32-bit high word and let one pair contribute up to 1/4 of the domain
       const double rhoMax = fabs(d->tF.x0) + (d->tF.n + 1) / d->tF.invDx;
       int ex = 0; frexp(rhoMax, &ex);                   // rhoMax < 2^ex
-      Q.n3ScaleRho = ldexp(R(1.0), 53 - ex);
+      Q.n3ScaleRho = ldexp(1.0, 53 - ex);
    }
    if (d->useNL)
    {  // list path: rhobar, F' halo, then every pair force in pass 3 (force_nl.cuh); pair energies on request

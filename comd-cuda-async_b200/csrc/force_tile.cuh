@@ -64,7 +64,7 @@ struct PairParams
    const real2* tDR;                // pass 3: {g1, g2-g1} of rho per interval
    // list path (force_nl.cuh): 32-byte records, one sector per lookup
    const real4* rvPhi; const real4* rvRho; const real4* r3;
-   real_t n3ScaleRho;                 // fixed-point scale of the rhobar accumulators (force_n3.cuh)
+   double n3ScaleRho;                 // fixed-point scale of the rhobar accumulators (force_n3.cuh)
 };
 
 // ---- PTX helpers: mbarrier + 1-D bulk copy (TMA engine, UBLKCP in SASS) -----------------
@@ -94,7 +94,9 @@ __device__ __forceinline__ void bulkG2S(void* dst, const void* src, unsigned byt
 // one 256-bit read-only load (LDG.E.256 on sm_100a): two adjacent double2, 32-byte aligned
 __device__ __forceinline__ void ldg256(const real2* p, real2& a, real2& b)
 {
-   asm volatile("ld.global.nc.v4.f64 {%0, %1, %2, %3}, [%4];" : "=d"(a.x), "=d"(a.y), "=d"(b.x), "=d"(b.y) : "l"(p));
+   real4 v;
+   COMD_LDG_REAL4(".nc", v, p);
+   a = make_real2(v.x, v.y); b = make_real2(v.z, v.w);
 }
 
 // interpolate() of eam.c:557-579 on four already-loaded stencil values
@@ -114,7 +116,7 @@ __device__ __forceinline__ int tableIndex(const DevTable& T, real_t r, real_t& t
 {
    if (r < T.x0) r = T.x0;
    r = (r - T.x0) * T.invDx;
-   int ii = __double2int_rd(r);
+   int ii = realFloorInt(r);
    if (ii > T.n) { ii = T.n; r = T.n / T.invDx; }
    t = r - floor(r);
    return ii;

@@ -30,6 +30,10 @@
 extern "C" {
 #endif
 
+/* Per-atom arrays (r, p, f, U) cross this interface as comd_real, the reference's real_t (mytype.h:11-24):
+ * double in libcomd_b200.so, float in libcomd_b200_f32.so (built with -DCOMD_SINGLE, the reference's
+ * "DOUBLE_PRECISION = OFF").  Scalars, geometry, tables and energy sums stay double in both; the library
+ * rounds tables to comd_real when it uploads them.  comd_precision() tells which one was loaded. */
 #ifdef COMD_SINGLE
 typedef float comd_real;
 #else
@@ -78,6 +82,7 @@ int  comd_dev_create(ComdDev** out, int deviceId, const ComdGeometry* geom, long
 int  comd_dev_destroy(ComdDev* dev);
 const char* comd_last_error(void);
 const char* comd_version(void);
+int  comd_precision(void);                  /* sizeof(comd_real): 8 or 4 */
 
 /* ---- potential + species: the potential block of CopyDataToGpu (gpu_utility.c:432-600) */
 int  comd_dev_set_mass(ComdDev* dev, double massInternalUnits);
@@ -91,13 +96,13 @@ int  comd_dev_set_eam(ComdDev* dev, double cutoff,
  * Download returns LOCAL atoms in device order (cell-major in the reference's own box
  * numbering is NOT implied; key by gid).  Any output pointer may be NULL. */
 int  comd_dev_upload_atoms(ComdDev* dev, int nLocal, const int* gid, const int* species,
-                           const double* rx, const double* ry, const double* rz,
-                           const double* px, const double* py, const double* pz);
+                           const comd_real* rx, const comd_real* ry, const comd_real* rz,
+                           const comd_real* px, const comd_real* py, const comd_real* pz);
 int  comd_dev_download_atoms(ComdDev* dev, int* nLocalOut, int capacity,
                              int* gid, int* species, int* refBox,
-                             double* rx, double* ry, double* rz,
-                             double* px, double* py, double* pz,
-                             double* fx, double* fy, double* fz, double* U);
+                             comd_real* rx, comd_real* ry, comd_real* rz,
+                             comd_real* px, comd_real* py, comd_real* pz,
+                             comd_real* fx, comd_real* fy, comd_real* fz, comd_real* U);
 int  comd_dev_num_local(ComdDev* dev, int* nLocal);        /* sumAtoms input (CoMD.c:442-457) */
 int  comd_dev_num_total(ComdDev* dev, int* nLocalPlusGhost);
 /* per-cell populations in the REFERENCE's box numbering (getBoxFromTuple,
@@ -105,7 +110,7 @@ int  comd_dev_num_total(ComdDev* dev, int* nLocalPlusGhost);
 int  comd_dev_cell_counts(ComdDev* dev, int* nAtomsPerRefBox, int nTotalBoxes);
 /* all atoms incl. ghosts, for the halo parity tests */
 int  comd_dev_download_all(ComdDev* dev, int* nOut, int capacity, int* gid, int* refBox,
-                           double* rx, double* ry, double* rz);
+                           comd_real* rx, comd_real* ry, comd_real* rz);
 
 /* ---- binning + atom halo: updateLinkCellsGpu (gpu_kernels.cu:470), haloExchange of
  * atoms (haloExchange.c:732; pack/unpack gpu_kernels.cu:507-638), buildAtomListGpu
@@ -192,8 +197,8 @@ int  comd_dev_fp64_peak(ComdDev* dev, double* tflops);
 int  comd_host_alloc(void** p, size_t bytes);      /* cudaMallocHost; any rank, any time after comd_dev_create */
 int  comd_host_free(void* p);
 int  comd_dev_step_host(ComdDev* dev, int nLocal, double dt,
-                        const int* gidIn, const double* rIn[3], const double* pIn[3], const double* fIn[3],
-                        int* nOut, int* gidOut, double* rOut[3], double* pOut[3], double* fOut[3], double* UOut,
+                        const int* gidIn, const comd_real* rIn[3], const comd_real* pIn[3], const comd_real* fIn[3],
+                        int* nOut, int* gidOut, comd_real* rOut[3], comd_real* pOut[3], comd_real* fOut[3], comd_real* UOut,
                         double eLocal[2]);
 /* A caller that hands the atoms of one comd_dev_step_host call to the next (same gids, same order, no
  * position further than skin/2 from the neighbour list's snapshot) is served without re-sorting and

@@ -20,6 +20,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ORACLE_SO = os.path.join(HERE, "libcomd_oracle.so")
 REF_DIR = os.path.join(HERE, "_ref")
 REF_SO = os.path.join(REF_DIR, "libcomd_ref.so")
+REF_SO_F32 = os.path.join(REF_DIR, "libcomd_ref_f32.so")   # the reference with real_t = float (DOUBLE_PRECISION=OFF)
 REF_EXE = os.path.join(REF_DIR, "CoMD-ref")
 REF_SRC = "/root/reference"
 
@@ -50,8 +51,8 @@ def build(ref=True):
         subprocess.check_call(["make", "-s", "-C", os.path.join(HERE, "ref_build")])
 
 
-def have_ref():
-    return os.path.exists(REF_SO)
+def have_ref(precision="f64"):
+    return os.path.exists(REF_SO if precision == "f64" else REF_SO_F32)
 
 
 POT_LJ, POT_FUNCFL, POT_SETFL = 0, 1, 2
@@ -219,13 +220,14 @@ class Ref:
     """The reference's own CPU path (one simulation per process: it keeps global state)."""
 
     _lib = None
+    SO = REF_SO
 
     @classmethod
     def lib(cls):
         if cls._lib is None:
-            if not have_ref():
-                raise FileNotFoundError(REF_SO + " missing: run `make -C oracle ref` where /root/reference exists")
-            L = C.CDLL(REF_SO)
+            if not os.path.exists(cls.SO):
+                raise FileNotFoundError(cls.SO + " missing: run `make -C oracle ref` where /root/reference exists")
+            L = C.CDLL(cls.SO)
             L.ref_init.argtypes = [C.c_int, C.POINTER(C.c_char_p)]
             L.ref_set_lj_cutoff_mult.argtypes = [C.c_double]
             L.ref_geometry.argtypes = [_ip, _dp]
@@ -329,3 +331,11 @@ class Ref:
         a, b = C.c_double(), C.c_double()
         L.ref_eam_table(h, which, C.byref(a), C.byref(b), _d(v))
         return dict(n=n, x0=a.value, inv_dx=b.value, padded=v)
+
+
+class Ref32(Ref):
+    """The reference's single-precision build (real_t = float); the wrappers still speak double, so every value
+    that comes back is a float widened exactly."""
+
+    _lib = None
+    SO = REF_SO_F32

@@ -19,9 +19,26 @@ def test_header_and_binding_agree():
 
 
 def test_library_exports_every_symbol():
-    L = ctypes.CDLL(pycomd.LIB_PATH)
-    for name in header_symbols():
-        assert hasattr(L, name), name
+    """Both precision builds (comd_real = double / float) export the whole interface and say which one they are."""
+    for precision, size in (("f64", 8), ("f32", 4)):
+        L = ctypes.CDLL(pycomd.LIB_PATHS[precision])
+        for name in header_symbols():
+            assert hasattr(L, name), (precision, name)
+        assert L.comd_precision() == size
+
+
+def test_f32_geometry_is_the_float_references_arithmetic():
+    """make_geometry(precision="f32") against the link-cell geometry the reference's real_t = float build derives
+    (initLinkCells, linkCells.c:122-182; fixture from libcomd_ref_f32.so, tests/golden/make_golden_f32.py)."""
+    import numpy as np
+    for kind in ("lj", "funcfl", "setfl"):
+        g = np.load(os.path.join(ROOT, "tests", "golden", "f32_%s_n6.npz" % kind))
+        ext = np.float32(6) * np.float32(g["lat"])
+        geo = pycomd.make_geometry([ext] * 3, np.float32(g["cutoff"]), precision="f32")
+        assert list(geo.gridSize) == list(g["cell_grid"])
+        assert [geo.boxSize[a] for a in range(3)] == list(g["cell_box_size"])
+        assert [geo.invBoxSize[a] for a in range(3)] == list(g["cell_inv_box_size"])
+        assert pycomd.n_total_boxes(tuple(geo.gridSize)) == int(g["cell_n_total"])
 
 
 def test_no_device_fails_loudly(gpu_available):
