@@ -509,9 +509,9 @@ extern "C" int comd_dev_create(ComdDev** out, int deviceId, const ComdGeometry* 
    CUDA_TRY(cudaMalloc(&d->cnt, C_COUNT * sizeof(int)));
    CUDA_TRY(cudaMemset(d->cnt, 0, C_COUNT * sizeof(int)));
    CUDA_TRY(cudaMallocHost(&d->hCnt, C_COUNT * sizeof(int)));
-   CUDA_TRY(cudaMalloc(&d->redPartial, 2 * RED_BLOCKS * sizeof(real_t)));
-   CUDA_TRY(cudaMalloc(&d->redOut, 2 * sizeof(real_t)));
-   CUDA_TRY(cudaMallocHost(&d->hRed, 2 * sizeof(real_t)));
+   CUDA_TRY(cudaMalloc(&d->redPartial, 2 * RED_BLOCKS * sizeof(double)));
+   CUDA_TRY(cudaMalloc(&d->redOut, 2 * sizeof(double)));
+   CUDA_TRY(cudaMallocHost(&d->hRed, 2 * sizeof(double)));
    CUDA_TRY(cudaMalloc(&d->rhobar, (cap + COMD_PAD) * sizeof(real_t)));
    CUDA_TRY(cudaMalloc(&d->dfEmbed, (cap + COMD_PAD) * sizeof(real_t)));
    CUDA_TRY(cudaMemset(d->dfEmbed, 0, (cap + COMD_PAD) * sizeof(real_t)));
@@ -988,7 +988,7 @@ extern "C" int comd_dev_energy(ComdDev* d, double eLocal[2])
    k_energy_partial<<<RED_BLOCKS, 256, 0, d->stream>>>(R(0.5) / d->mass, d->A.cell, d->cellType, d->e, d->A.p[0], d->A.p[1], d->A.p[2],
       d->cnt, d->redPartial); LAUNCH_CHECK(d);
    k_energy_final<<<1, 1024, 0, d->stream>>>(d->redPartial, RED_BLOCKS, d->redOut); LAUNCH_CHECK(d);
-   CUDA_TRY(cudaMemcpyAsync(d->hRed, d->redOut, 2 * sizeof(real_t), cudaMemcpyDeviceToHost, d->stream));
+   CUDA_TRY(cudaMemcpyAsync(d->hRed, d->redOut, 2 * sizeof(double), cudaMemcpyDeviceToHost, d->stream));
    int rc = syncCounters(d, "comd_dev_energy");
    eLocal[0] = d->hRed[0]; eLocal[1] = d->hRed[1];
    return rc;

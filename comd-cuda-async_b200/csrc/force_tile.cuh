@@ -206,12 +206,15 @@ __device__ __forceinline__ void pairEval(const PairParams& P, real_t dx, real_t 
 
 template <int KIND> struct PairTraits { static constexpr int NACC = KIND == PK_LJ ? 4 : (KIND == PK_EAM1 ? 5 : 3); };
 
+// elements of a per-atom array in 16 bytes: TMA bulk copies start and end on such boundaries
+#define FT_AL ((int)(16 / sizeof(real_t)))
+
 // shared-memory bytes for a given staging capacity
 template <int KIND>
 __host__ __device__ inline size_t tileSmemBytes(int sMax)
 {
    size_t b = FT_HDR;
-   b += (size_t)sMax * 8 * (KIND == PK_EAM3 ? 4 : 3);      // x,y,z (+F')
+   b += (size_t)sMax * sizeof(real_t) * (KIND == PK_EAM3 ? 4 : 3);      // x,y,z (+F')
    b += (size_t)sMax * 16;                                 // float4 shadow
    b += (size_t)FT_WARPS * FT_QCAP * 32 * 2;               // lane queues
    b += (size_t)FT_WARPS * FT_APW * FT_DCAP * 2;           // dense queues
@@ -291,7 +294,7 @@ k_force_tile(DevGeom g, TileCfg cfg, PairParams P,
    {  // row layout + TMA issue: lane r < 9 owns row r
       int gs = 0, ge = 0;
       if (lane < 9) { gs = H.cs[lane][0]; ge = H.cs[lane][nk - 1]; }
-      const int ga = gs & ~1, cntR = ((ge + 1) & ~1) - ga;        // 16-byte aligned ends for the FP64 arrays
+      const int ga = gs & ~(FT_AL - 1), cntR = ((ge + FT_AL - 1) & ~(FT_AL - 1)) - ga;        // 16-byte aligned ends for the real_t arrays
       int incl = cntR;
       #pragma unroll
       for (int o = 1; o < 16; o <<= 1) { const int u = __shfl_up_sync(full, incl, o); if (lane >= o) incl += u; }
@@ -301,17 +304,17 @@ k_force_tile(DevGeom g, TileCfg cfg, PairParams P,
       if (lane == 0) { H.total = total; H.iBeg = H.cs[4][1]; H.iEnd = H.cs[4][Tx + 1]; }
       if (total <= sMax)
       {
-         constexpr unsigned perAtom = 8u * (KIND == PK_EAM3 ? 4 : 3) + 16u;
+         constexpr unsigned perAtom = (unsigned)sizeof(real_t) * (KIND == PK_EAM3 ? 4 : 3) + 16u;
          if (lane == 0) mbarExpectTx(&H.mbar, (unsigned)total * perAtom);
          __syncwarp();
          if (lane < 9 && cntR > 0)
          {
-            const unsigned nb = (unsigned)cntR * 8u;
+            const unsigned nb = (unsigned)cntR * (unsigned)sizeof(real_t);
             bulkG2S(sx + excl, rx + ga, nb, &H.mbar);
             bulkG2S(sy + excl, ry + ga, nb, &H.mbar);
             bulkG2S(sz + excl, rz + ga, nb, &H.mbar);
             if (KIND == PK_EAM3) bulkG2S(sdf + excl, dfIn + ga, nb, &H.mbar);
-            bulkG2S(sf + excl, rf + ga, nb * 2u, &H.mbar);
+            bulkG2S(sf + excl, rf + ga, (unsigned)cntR * 16u, &H.mbar);
          }
       }
    }
@@ -429,8 +432,8 @@ static int launchForceTile(ComdDev* d, PairParams P, const real_t* dfIn)
    int sMax; size_t bytes;
    for (;;)
    {  // staging capacity: the 9 rows at 1.25x the mean density + slack; two CTAs per SM if possible
-      sMax = (int)(R(9.0) * (txT + 2) * perCell * R(1.25)) + 9 * 2 + 96;
-      sMax = (sMax + 1) & ~1;
+      sMax = (int)(R(9.0) * (txT + 2) * perCell * R(1.25)) + 9 * 2 * (FT_AL - 1) + 96;
+      sMax = (sMax + FT_AL - 1) & ~(FT_AL - 1);
       bytes = tileSmemBytes<KIND>(sMax);
       if (bytes <= 113 * 1024 || txT == 1) break;
       --txT;

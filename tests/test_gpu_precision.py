@@ -4,9 +4,11 @@ itself produced in that precision (tests/golden/make_golden.py, make_golden_f32.
 
 Tolerances.  FP64: the north_star gates (1e-12 step 0, 1e-6 energy at step 100).  FP32: the reference's float
 build and ours sum the same ~70 float terms per atom in different orders, so per-atom results agree to a few
-float ulps of the largest term: 2e-6 of max|F| / max|U| at step 0 (measured 3e-7), 1e-6 for the energy sums, and
-2e-5 for the total energy after 100 steps (two float trajectories; the float reference itself drifts by up to 5e-6
-over those steps).  Cell assignment is bit-exact in both.
+float ulps of the largest term: 2e-6 of max|F| / max|U| at step 0; 3e-6 for the energy sums (the reference adds its
+864 per-atom energies into a float, 1.1e-6 off on Cu01; the device sums in double in both builds); 2e-5 for the total
+energy after 100 steps (two float trajectories; the float reference itself drifts by up to 5e-6 over those steps).
+esum_big: the 32000-atom FP64 sums of the trace fixture, added in a different order (measured 1.3e-12).
+Cell assignment is bit-exact in both.
 """
 import os
 
@@ -20,8 +22,8 @@ from common import GOLDEN_DIR, LJ_EPS, LJ_SIGMA, by_gid, rel_err
 pytestmark = pytest.mark.gpu
 
 KINDS = {"lj": po.POT_LJ, "funcfl": po.POT_FUNCFL, "setfl": po.POT_SETFL}
-TOL = {"f64": dict(step0=1e-12, esum=1e-12, e100=1e-6, paths=1e-12),
-       "f32": dict(step0=2e-6, esum=1e-6, e100=2e-5, paths=4e-6)}
+TOL = {"f64": dict(step0=1e-12, esum=1e-12, esum_big=1e-11, e100=1e-6),
+       "f32": dict(step0=2e-6, esum=3e-6, esum_big=3e-6, e100=2e-5)}
 PATHS = {"link_cell": None, "list_n3": 1, "list_full": 0}
 
 
@@ -124,7 +126,7 @@ def test_energy_after_100_steps_in_that_precision(kind, precision, path):
     e1 = sum(dev.energy())
     tr = g["trace"].sum(1)
     t = TOL[precision]
-    assert abs(e0 - tr[0]) <= t["esum"] * abs(tr[0])
+    assert abs(e0 - tr[0]) <= t["esum_big"] * abs(tr[0])
     assert abs(e1 - tr[-1]) <= t["e100"] * abs(tr[-1])
     assert dev.num_local() == 4 * n ** 3
     dev.close()
@@ -132,7 +134,11 @@ def test_energy_after_100_steps_in_that_precision(kind, precision, path):
 
 @pytest.mark.parametrize("kind", list(KINDS))
 def test_f32_build_stays_within_float_rounding_of_the_f64_build(kind):
-    """Same (float-representable) inputs through both libraries in one process: the two builds share no state."""
+    """Same (float-representable) inputs and the same tables through both libraries in one process (the two builds
+    share no state).  LJ: float rounding of the pair term, <= 1e-5 of max|F|.  EAM: interpolate() (eam.c:573-578)
+    differentiates the table by differencing neighbouring entries; rounded to float (6e-8 relative) and divided by
+    the grid step (5.5e-4 A on Cu01) that is ~1e-4 of the slope -- a property of the reference's float build, which
+    the device reproduces (the step-0 test above holds it to 2e-6 of the float reference)."""
     g = golden(kind, "f32")
     g64 = golden(kind, "f64")
     res = {}
@@ -144,19 +150,20 @@ def test_f32_build_stays_within_float_rounding_of_the_f64_build(kind):
         dev.compute_force()
         res[precision] = by_gid(dev.download())
         dev.close()
-    assert rel_err(res["f32"]["f"].astype(np.float64), res["f64"]["f"]) <= 4e-6
-    assert rel_err(res["f32"]["U"].astype(np.float64), res["f64"]["U"]) <= 4e-6
+    tol = 1e-5 if kind == "lj" else 1e-4
+    assert rel_err(res["f32"]["f"].astype(np.float64), res["f64"]["f"]) <= tol
+    assert rel_err(res["f32"]["U"].astype(np.float64), res["f64"]["U"]) <= tol
 
 
 @pytest.mark.parametrize("kind", ["lj", "setfl"])
 def test_f32_step_host_round_trip(kind):
     g = golden(kind, "f32")
-    dev, _ = device_from(g, kind, "f32", "list_n3")
+    dev, _ = device_from(g, kind, "f32")
     dev.compute_force()
     s0 = by_gid(dev.download())
     dev.timestep(1, 1.0)
     want = by_gid(dev.download())
-    dev2, _ = device_from(g, kind, "f32", "list_n3", atoms=False)
+    dev2, _ = device_from(g, kind, "f32", atoms=False)
     cols = lambda a: [np.ascontiguousarray(a[:, k]) for k in range(3)]
     m, o, e = dev2.step_host(1.0, s0["gid"].astype(np.int32), cols(s0["r"]), cols(s0["p"]), cols(s0["f"]))
     got = by_gid(dict(gid=o["gid"][:m].copy(), r=np.stack([a[:m] for a in o["r"]], 1), p=np.stack([a[:m] for a in o["p"]], 1),
