@@ -8,6 +8,11 @@ keep = ['Kernel Name', 'gpu__time_duration.sum', 'launch__registers_per_thread',
         'sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active', 'sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active',
         'sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active', 'sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active',
         'sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active', 'smsp__inst_executed.sum', 'smsp__thread_inst_executed_per_inst_executed.ratio',
+        'l1tex__throughput.avg.pct_of_peak_sustained_active', 'SM_A.TriageCompute.l1tex__data_pipe_lsu_wavefronts.avg',
+        'SM_A.TriageCompute.l1tex__data_pipe_lsu_wavefronts_mem_lgds.avg', 'SM_A.TriageCompute.l1tex__data_pipe_lsu_wavefronts_mem_shared.avg',
+        'l1tex__data_pipe_lsu_wavefronts_mem_shared_op_atom.sum', 'smsp__inst_executed_op_shared_atom.sum',
+        'l1tex__t_requests_pipe_lsu_mem_global_op_ld.sum', 'l1tex__t_requests_pipe_lsu_mem_local_op_ld.sum',
+        'smsp__warps_eligible.avg.per_cycle_active',
         'dram__bytes_read.sum', 'dram__bytes_write.sum', 'l1tex__t_sector_hit_rate.pct', 'lts__t_sector_hit_rate.pct', 'sm__cycles_active.avg']
 keep += [h for h in hdr if 'issue_stalled' in h and 'per_issue_active' in h]
 for k in keep:
