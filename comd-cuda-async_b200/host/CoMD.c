@@ -46,10 +46,19 @@ static void createDevice(SimFlat* s, int doeam)
    if (doeam)
    {
       EamPotential* e = (EamPotential*)s->pot;
-      ComdTable t[3] = { { e->phi->n, e->phi->x0, e->phi->invDx, e->phi->values },
-                         { e->rho->n, e->rho->x0, e->rho->invDx, e->rho->values },
-                         { e->f->n, e->f->x0, e->f->invDx, e->f->values } };
+      /* ComdTable carries doubles in either precision: a float table widens exactly (the device layer of the
+       * single-precision build rounds back to the same floats) */
+      InterpolationObject* src[3] = { e->phi, e->rho, e->f };
+      ComdTable t[3];
+      double* wide[3];
+      for (int k = 0; k < 3; ++k)
+      {
+         wide[k] = malloc((src[k]->n + 3) * sizeof(double));
+         for (int i = -1; i <= src[k]->n + 1; ++i) wide[k][i + 1] = src[k]->values[i];
+         t[k].n = src[k]->n; t[k].x0 = src[k]->x0; t[k].invDx = src[k]->invDx; t[k].values = wide[k] + 1;
+      }
       DEV_TRY(comd_dev_set_eam(s->dev, e->cutoff, &t[0], &t[1], &t[2]));
+      for (int k = 0; k < 3; ++k) free(wide[k]);
    }
    else
    {

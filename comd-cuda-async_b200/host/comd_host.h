@@ -28,10 +28,17 @@
 #include <stdio.h>
 #include "../../include/comd_b200.h"
 
+/* mytype.h:8-24: one switch for the whole host layer.  -DCOMD_SINGLE builds CoMD-b200-f32 / libcomd_host_f32.so against
+ * libcomd_b200_f32.so (comd_real = float in include/comd_b200.h follows the same macro). */
 #ifdef COMD_SINGLE
-#error "this build is FP64 (COMD_DOUBLE); the -DSINGLE variant is listed under 'next' in DESIGN.md"
-#endif
+typedef float real_t;
+#define FMT1 "%g"
+#define EMT1 "%e"
+#else
 typedef double real_t;
+#define FMT1 "%lg"
+#define EMT1 "%le"
+#endif
 typedef real_t real3[3];
 
 /* ---- constants.h:28-39 ---- */

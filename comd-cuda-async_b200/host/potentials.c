@@ -120,7 +120,7 @@ static FILE* openPot(const char* who, const char* dir, const char* name)
 static void readNumbers(FILE* fp, real_t* buf, int n, const char* who)
 {
    for (int i = 0; i < n; ++i)
-      if (fscanf(fp, "%lg", buf + i) != 1) { fprintf(stderr, "%s: short table (entry %d of %d)\n", who, i, n); exit(-1); }
+      if (fscanf(fp, FMT1, buf + i) != 1) { fprintf(stderr, "%s: short table (entry %d of %d)\n", who, i, n); exit(-1); }
 }
 
 static void readSetfl(EamPotential* pot, const char* dir, const char* name)
@@ -132,7 +132,7 @@ static void readSetfl(EamPotential* pot, const char* dir, const char* name)
    sscanf(line, "%d %63s", &nElems, elem);
    if (nElems != 1) { fprintf(stderr, "eamReadSetfl: CoMD 1.1 does not support alloys and cannot read setfl files with multiple species\n"); exit(-1); }
    strncpy(pot->name, elem, 2); pot->name[2] = 0;
-   int nRho = 0, nR = 0; double dRho = 0, dR = 0, cutoff = 0;
+   int nRho = 0, nR = 0; double dRho = 0, dR = 0, cutoff = 0;      /* doubles in either precision (eam.c:707,834) */
    if (!fgets(line, sizeof line, fp)) line[0] = 0;
    sscanf(line, "%d %le %d %le %le", &nRho, &dRho, &nR, &dR, &cutoff);
    pot->cutoff = cutoff;
@@ -167,7 +167,7 @@ static void readFuncfl(EamPotential* pot, const char* dir, const char* name)
    sscanf(line, "%d %le %le %7s", &atomicNo, &mass, &lat, lattice);
    pot->atomicNo = atomicNo; pot->lat = lat; pot->mass = mass * amuToInternalMass;
    strcpy(pot->latticeType, lattice);
-   int nRho = 0, nR = 0; double dRho = 0, dR = 0, cutoff = 0;
+   int nRho = 0, nR = 0; double dRho = 0, dR = 0, cutoff = 0;      /* doubles in either precision (eam.c:707,834) */
    if (!fgets(line, sizeof line, fp)) line[0] = 0;
    sscanf(line, "%d %le %d %le %le", &nRho, &dRho, &nR, &dR, &cutoff);
    pot->cutoff = cutoff;

@@ -48,10 +48,11 @@ void computeForce(SimFlat* s)
 
 void kineticEnergyGpu(SimFlat* s)
 {
-   double e[2], sum[2];
-   DEV_TRY(comd_dev_energy(s->dev, e));
+   double e[2];
+   DEV_TRY(comd_dev_energy(s->dev, e));                /* device sums are double in either precision */
+   real_t eLocal[2] = { (real_t)e[0], (real_t)e[1] }, sum[2];     /* timestep.c:124-128 reduces real_t */
    startTimer(commReduceTimer);
-   addRealParallel(e, sum, 2);
+   addRealParallel(eLocal, sum, 2);
    stopTimer(commReduceTimer);
    s->ePotential = sum[0];
    s->eKinetic = sum[1];

@@ -51,6 +51,29 @@ def test_driver_trace_matches_reference_executable(tmp_path, flags, method):
         assert abs(ek0 - ek1) <= max(tol, 1e-6 if s0 else 0) * abs(ek1) + 1.5e-12, (s0, ek0, ek1)
 
 
+@pytest.mark.parametrize("flags,method", [([], "thread_atom_nl"), (["-e"], "thread_atom"), (["-e", "-t", "setfl"], "thread_atom_nl")])
+def test_single_precision_driver_trace_matches_the_float_reference(tmp_path, flags, method):
+    """CoMD-b200-f32 (host/ and csrc/ built with -DCOMD_SINGLE, real_t = float end to end, mytype.h:8-24) beside the
+    reference's own float build (oracle/_ref/CoMD-ref-f32, -m cpu_nl).  Tolerances of tests/test_gpu_precision.py:
+    3e-6 on the energy sums at step 0 (the reference adds 6912 per-atom energies into a float), 2e-5 on the total
+    energy over 100 steps of two float trajectories; the kinetic energy alone is a small difference of large sums."""
+    ref32 = REF + "-f32"
+    if not os.path.exists(ref32):
+        pytest.skip("oracle/_ref/CoMD-ref-f32 not built (needs /root/reference at build time)")
+    subprocess.check_call(["make", "-s", "-C", PKG, "host"])
+    n = "12"
+    common = ["-x", n, "-y", n, "-z", n, "-N", "100", "-n", "10", "-d", POTS] + flags
+    ours = trace(run(os.path.join(PKG, "CoMD-b200-f32"), common + ["-m", method], tmp_path))
+    ref = trace(run(ref32, common + ["-m", "cpu_nl"], tmp_path))
+    assert len(ours) == len(ref) == 11
+    for (s0, et0, eu0, ek0, n0), (s1, et1, eu1, ek1, n1) in zip(ours, ref):
+        assert s0 == s1 and n0 == n1 == 4 * int(n) ** 3
+        tol = 3e-6 if s0 == 0 else 2e-5
+        assert abs(et0 - et1) <= tol * abs(et1), (s0, et0, et1)
+        assert abs(eu0 - eu1) <= tol * abs(eu1), (s0, eu0, eu1)
+        assert abs(ek0 - ek1) <= tol * abs(eu1), (s0, ek0, ek1)
+
+
 def test_driver_async_flag_gives_the_same_trace(tmp_path):
     subprocess.check_call(["make", "-s", "-C", PKG, "host"])
     args = ["-x", "10", "-y", "10", "-z", "10", "-N", "30", "-n", "10", "-e", "-d", POTS]

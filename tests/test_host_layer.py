@@ -19,10 +19,10 @@ POTS = os.path.join(ROOT, "pots")
 @pytest.fixture(scope="module")
 def tools():
     subprocess.check_call(["make", "-s", "-C", PKG, "host"])
-    return {k: os.path.join(PKG, k) for k in ("host_dump", "comd-launch", "CoMD-b200")}
+    return {k: os.path.join(PKG, k) for k in ("host_dump", "comd-launch", "CoMD-b200", "host_dump_f32", "CoMD-b200-f32")}
 
 
-def read_dump(path):
+def read_dump(path, real=np.float64):
     with open(path, "rb") as fh:
         raw = fh.read()
     n, n_global, gx, gy, gz, n_boxes = struct.unpack_from("6i", raw, 0)
@@ -30,8 +30,9 @@ def read_dump(path):
     off = 24 + 15 * 8
     gid = np.frombuffer(raw, np.int32, n, off); off += 4 * n
     box = np.frombuffer(raw, np.int32, n, off); off += 4 * n
-    r = np.frombuffer(raw, np.float64, 3 * n, off).reshape(3, n).T; off += 24 * n
-    p = np.frombuffer(raw, np.float64, 3 * n, off).reshape(3, n).T
+    w = np.dtype(real).itemsize
+    r = np.frombuffer(raw, real, 3 * n, off).reshape(3, n).T; off += 3 * w * n
+    p = np.frombuffer(raw, real, 3 * n, off).reshape(3, n).T
     return dict(n=n, n_global=n_global, grid=(gx, gy, gz), n_boxes=n_boxes, cutoff=dh[0], mass=dh[1], lat=dh[2], box_size=dh[3:6],
                 inv_box_size=dh[6:9], local_min=dh[9:12], local_max=dh[12:15], gid=gid, box=box, r=r, p=p)
 
@@ -60,6 +61,34 @@ def test_initial_state_is_bit_identical_to_the_oracle(tools, tmp_path, kind):
     assert np.array_equal(d["r"][h], a["r"][o])                   # lattice + gid-seeded displacement
     assert np.array_equal(d["p"][h], a["p"][o])                   # gid-seeded momenta, COM removal, rescale to T: same sums, same order
     assert np.array_equal(d["box"][h], a["box"][o])               # getBoxFromCoord / getBoxFromTuple
+
+
+@pytest.mark.parametrize("kind", list(KINDS))
+def test_single_precision_host_layer_matches_the_float_reference(tools, tmp_path, kind):
+    """host/ built with -DCOMD_SINGLE (real_t = float, mytype.h:8-24) against what the reference's own float build
+    produced (tests/golden/f32_*.npz, made by make_golden_f32.py from oracle/_ref/libcomd_ref_f32.so): potential
+    constants, lattice + displacements, momenta, the link-cell id of every atom -- bit for bit, all floats."""
+    g = np.load(os.path.join(ROOT, "tests", "golden", "f32_%s_n6.npz" % kind))
+    base = ["-x", "6", "-y", "6", "-z", "6", "-r", "0.1", "-T", "600", "-d", POTS] + FLAGS[kind]
+    out = str(tmp_path / "d32.bin")
+    subprocess.check_call([tools["host_dump_f32"], out] + base, cwd=tmp_path, stdout=subprocess.DEVNULL)
+    d = read_dump(out, np.float32)
+    assert d["n"] == len(g["gid"]) == 864
+    assert d["cutoff"] == float(g["cutoff"]) and d["mass"] == float(g["mass"]) and d["lat"] == float(g["lat"])
+    assert np.float32(d["cutoff"]) == d["cutoff"]                 # the constants live in floats
+    assert tuple(int(x) for x in g["cell_grid"]) == d["grid"] and int(g["cell_n_total"]) == d["n_boxes"]
+    assert np.array_equal(g["cell_inv_box_size"], d["inv_box_size"]) and np.array_equal(g["cell_box_size"], d["box_size"])
+    o = np.argsort(g["gid"]); h = np.argsort(d["gid"])
+    assert np.array_equal(d["gid"][h], g["gid"][o])
+    assert np.array_equal(d["r"][h], g["r"][o])
+    assert np.array_equal(d["box"][h], g["cell_of_atom"][o])      # getBoxFromCoord in float, cells of one cutoff
+    # momenta: float sums (centre of mass, temperature) depend on the traversal order, i.e. on the link cells; the golden
+    # run is the reference's -m cpu_nl (cells of cutoff + skin), so the same method here
+    subprocess.check_call([tools["host_dump_f32"], out, "-m", "thread_atom_nl"] + base, cwd=tmp_path, stdout=subprocess.DEVNULL)
+    d = read_dump(out, np.float32)
+    h = np.argsort(d["gid"])
+    assert np.array_equal(d["r"][h], g["r"][o])
+    assert np.array_equal(d["p"][h], g["p"][o])
 
 
 def test_two_ranks_partition_the_same_lattice(tools, tmp_path):
