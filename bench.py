@@ -69,29 +69,65 @@ def measured_peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    """SM clock + throttle reasons during the timed region (B200_PROFILING.md recipe).  In-process NVML on a thread,
+    two light queries every 200 ms: an `nvidia-smi -lms 100` child polling nine fields stalled the 8-rank step
+    (4.6 against 2.4 ms/step on 8 B200 with and without it, gpurun_out/r2f_bench_n8.json); nvidia-smi is only the
+    fallback where pynvml does not load."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    BITS = {"hw_slowdown": 0x8, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20, "sw_power_cap": 0x4}     # nvml.h nvmlClocksEventReason*
 
     def __init__(self, index):
         self.index = index
         self.proc = None
+        self.nvml = None
         self.lines = []
+        self.samples = []
+        self.stop_flag = threading.Event()
 
     def start(self):
         try:
+            import pynvml
+            pynvml.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = int(vis.split(",")[self.index]) if vis and all(x.strip().isdigit() for x in vis.split(",")) else self.index
+            self.handle = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.smax = float(pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM))
+            self.nvml = pynvml
+            self.th = threading.Thread(target=self._poll, daemon=True)
+            self.th.start()
+            return
+        except Exception:
+            self.nvml = None
+        try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
-                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                                          "-lms", "250"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.th = threading.Thread(target=self._read, daemon=True)
             self.th.start()
         except OSError:
             self.proc = None
+
+    def _poll(self):
+        n = self.nvml
+        while not self.stop_flag.is_set():
+            try:
+                self.samples.append((float(n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM)),
+                                     int(n.nvmlDeviceGetCurrentClocksEventReasons(self.handle))))
+            except Exception:
+                pass
+            self.stop_flag.wait(0.2)
 
     def _read(self):
         for ln in self.proc.stdout:
             self.lines.append(ln.strip())
 
     def stop(self):
+        if self.nvml is not None:
+            self.stop_flag.set()
+            self.th.join(timeout=2)
+            sm = [s[0] for s in self.samples]
+            reasons = sorted(k for k, b in self.BITS.items() if any(s[1] & b for s in self.samples))
+            return dict(sm_mhz=float(np.median(sm)) if sm else None, sm_max_mhz=self.smax, reasons=reasons, samples=len(sm), source="nvml")
         if not self.proc:
             return dict(sm_mhz=None, sm_max_mhz=None, reasons=["nvidia-smi unavailable"])
         self.proc.terminate()
@@ -112,7 +148,7 @@ class ClockSampler:
                 if v.lower().startswith("active"):
                     reasons.add(name)
         return dict(sm_mhz=float(np.median(sm)) if sm else None, sm_max_mhz=max(smax) if smax else None,
-                    reasons=sorted(reasons), samples=len(sm))
+                    reasons=sorted(reasons), samples=len(sm), source="nvidia-smi")
 
 
 def host_cores():
@@ -481,8 +517,12 @@ def parity_leg(R):
     pd = og["p"] + drift
     steps_d = 60
     runs = []
-    for overlap in ((1, 0) if R.world > 1 else (1,)):
-        dev, geom, _ = make_device(R, "funcfl", potential, [n] * 3, 0.1, True, opts=["overlap=%d" % overlap], gid_r_p=(og["gid"], og["r"], pd))
+    # run 0: defaults (sync-free steps; N > 1: exchange overlapped, one-shot interior CTAs + boundary shell on a side stream);
+    # run 1: round 1's step (host waits for the rebuild verdict every step; N > 1: overlapped, persistent interior CTAs on
+    # 140 SMs); run 2 (N > 1): no overlap at all
+    variants = [[], ["nl_speculate=0", "overlap_mode=0"]] + ([["overlap=0"]] if R.world > 1 else [])
+    for vopts in variants:
+        dev, geom, _ = make_device(R, "funcfl", potential, [n] * 3, 0.1, True, opts=vopts, gid_r_p=(og["gid"], og["r"], pd))
         dev.compute_force()
         own0 = gathered_state(R, dev)["owner"]
         dev.timestep(steps_d, 1.0)
@@ -511,9 +551,11 @@ def parity_leg(R):
                     "owner_mismatches": int(np.sum(sd["owner"] != owner_of(sd["r"], gext, R.grid))), "atoms": int(len(sd["gid"]))}
     ok &= rec["drift"]["energy_rel_err"] <= 1e-9 and pos_err <= 1e-8 and f_err <= 1e-6 and rec["drift"]["owner_mismatches"] == 0
     ok &= len(sd["gid"]) == len(og["gid"]) and (R.world == 1 or rec["drift"]["atoms_that_changed_rank"] > 0)
+    same_bits = lambda q: bool(all(np.array_equal(sd[k], q[k]) for k in ("gid", "r", "p", "f", "owner")))
+    rec["sync_free_step_bit_identical_to_synchronised"] = same_bits(runs[1][0]) and runs[1][3] == nc
+    ok &= rec["sync_free_step_bit_identical_to_synchronised"]
     if R.world > 1:
-        s_off = runs[1][0]
-        rec["overlap_on_off_bit_identical"] = bool(all(np.array_equal(sd[k], s_off[k]) for k in ("gid", "r", "p", "f", "owner")))
+        rec["overlap_on_off_bit_identical"] = same_bits(runs[2][0])
         ok &= rec["overlap_on_off_bit_identical"]
     rec["pass"] = bool(ok)
     rec["wall_s"] = round(time.time() - t_begin, 1)
@@ -529,14 +571,18 @@ def timed_steps(R, dev, steps, print_rate, dt=1.0):
     l0 = dev.kernel_stats()["launches"]          # also resets the force-time ring
     dev.timer_start()
     left = steps
+    walls = []                                   # host wall clock per timestep() call (diagnostic: a stalled interval shows here)
     while left > 0:
+        w0 = time.perf_counter()
         dev.timestep(min(left, print_rate), dt)
+        walls.append(round(1e3 * (time.perf_counter() - w0), 3))
         left -= print_rate
     t_local = dev.timer_stop() * 1e-3
     ks = dev.kernel_stats()
     c1 = dev.neighbor_counters()
     t_max = R.reduce([t_local], "max")[0]
-    return t_max, ks["last_force_ms"], ks["launches"] - l0, dict(builds=c1["builds"] - c0["builds"], refreshes=c1["refreshes"] - c0["refreshes"])
+    return t_max, ks["last_force_ms"], ks["launches"] - l0, dict(builds=c1["builds"] - c0["builds"], refreshes=c1["refreshes"] - c0["refreshes"],
+                                                                 host_wall_ms_per_call=walls)
 
 
 def run_workload(R, name, steps, warmup, print_rate, skin, use_nl, every_step_too=False, opts=(), sampler=None):

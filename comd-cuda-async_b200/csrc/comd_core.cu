@@ -486,6 +486,11 @@ extern "C" int comd_dev_create(ComdDev** out, int deviceId, const ComdGeometry* 
       CUDA_TRY(cudaStreamCreateWithPriority(&d->commStream, cudaStreamNonBlocking, hi));
       CUDA_TRY(cudaEventCreateWithFlags(&d->evRefresh, cudaEventDisableTiming)); CUDA_TRY(cudaEventCreateWithFlags(&d->evPass1, cudaEventDisableTiming));
       CUDA_TRY(cudaEventCreateWithFlags(&d->evFp, cudaEventDisableTiming)); CUDA_TRY(cudaEventCreateWithFlags(&d->evStepBegin, cudaEventDisableTiming));
+      CUDA_TRY(cudaStreamCreateWithFlags(&d->sideStream, cudaStreamNonBlocking));
+      CUDA_TRY(cudaEventCreateWithFlags(&d->evSideBegin, cudaEventDisableTiming)); CUDA_TRY(cudaEventCreateWithFlags(&d->evSideDone, cudaEventDisableTiming));
+      d->optOverlapMode = 1;
+      CUDA_TRY(cudaEventCreateWithFlags(&d->evFlag, cudaEventDisableTiming));
+      d->optNlSpeculate = 1;
       d->xs = d->stream; d->optOverlap = 1; d->phStep = -1;
       d->e2eSpecArmed = 0;             // opt-in (option e2e_speculate): it only pays when the caller hands back bit-identical buffers
    }
@@ -607,6 +612,7 @@ extern "C" int comd_dev_destroy(ComdDev* d)
    for (int a = 0; a < 32; ++a) for (int b = 0; b < 8; ++b) if (d->evPh[a][b]) cudaEventDestroy(d->evPh[a][b]);
    cudaEventDestroy(d->evRefresh); cudaEventDestroy(d->evPass1); cudaEventDestroy(d->evFp); cudaEventDestroy(d->evStepBegin);
    cudaStreamDestroy(d->commStream);
+   cudaEventDestroy(d->evFlag); cudaEventDestroy(d->evSideBegin); cudaEventDestroy(d->evSideDone); cudaStreamDestroy(d->sideStream);
    if (d->copyStream)
    {
       cudaStreamDestroy(d->copyStream); cudaStreamDestroy(d->upStream);
@@ -1046,6 +1052,8 @@ extern "C" int comd_dev_set_option(ComdDev* d, const char* key, long value)
    if (!strcmp(key, "nl_lanes")) { if (value != 4 && value != 8) { comdSetError("nl_lanes: 4 or 8"); return COMD_E_ARG; } d->optNlLanes = (int)value; d->nlValid = 0; return COMD_OK; }
    if (!strcmp(key, "nl_n3")) { d->optNlN3 = value < 0 ? -1 : value != 0; d->nlValid = 0; return COMD_OK; }
    if (!strcmp(key, "overlap")) { d->optOverlap = value != 0; return COMD_OK; }
+   if (!strcmp(key, "nl_speculate")) { d->optNlSpeculate = value != 0; return COMD_OK; }
+   if (!strcmp(key, "overlap_mode")) { if (value < 0 || value > 1) { comdSetError("overlap_mode: 0 or 1"); return COMD_E_ARG; } d->optOverlapMode = (int)value; return COMD_OK; }
    if (!strcmp(key, "e2e_speculate")) { d->e2eSpecArmed = value != 0; return COMD_OK; }
    if (!strcmp(key, "overlap_sms")) { if (value < 0 || value > 148) { comdSetError("overlap_sms: 0..148"); return COMD_E_ARG; } d->optOverlapSms = (int)value; return COMD_OK; }
    if (!strcmp(key, "phase_timing"))
@@ -1099,11 +1107,33 @@ extern "C" int comd_dev_timestep(ComdDev* d, int nSteps, double dt)
       PH_MARK(d, 0);
       int rc = launchKickDrift(d, dt, it > 0);    // it > 0: the previous step left its second half-kick to this kernel
       if (rc != COMD_OK) { d->inTimestep = 0; return rc; }
-      rc = comd_dev_redistribute(d);               // marks 1 (decision known) and 2 (ghosts in place / enqueued)
-      if (rc != COMD_OK) { d->inTimestep = 0; return rc; }
+      const int wantE = it == nSteps - 1 || d->optEnergyEveryStep;
+      // List mode with a valid list: the step is enqueued for the common case (no rebuild) without waiting for the
+      // verdict of the displacement check; the host reads the flag once the force kernels are queued, i.e. while the
+      // GPU is busy with them.  Where the reference needed its -a 1 two-stream step to stay ahead of the GPU
+      // (timestep.c:257-265, eam.c:201-257).
+      d->specStep = d->useNL && d->nlValid && d->optNlSpeculate;
+      const int spec = d->specStep;
+      rc = comd_dev_redistribute(d);               // marks 1 (decision known / flag on its way) and 2 (ghosts in place / enqueued)
+      if (rc != COMD_OK) { d->inTimestep = 0; d->specStep = 0; return rc; }
       PH_MARK(d, 2);
-      rc = computeForce(d, it == nSteps - 1 || d->optEnergyEveryStep);     // marks 3, 4
+      rc = computeForce(d, wantE);                 // marks 3, 4
+      d->specStep = 0;
       if (rc != COMD_OK) { d->inTimestep = 0; return rc; }
+      if (spec)
+      {
+         CUDA_TRY(cudaEventSynchronize(d->evFlag));
+         if (d->hCnt[C_NLREBUILD])
+         {  // some atom on some rank moved more than skin/2: the kernels above returned at once.  Now the real thing:
+            // re-bin + atom exchange + sort + list build (redistributeAtomsGpuNL's rebuild branch, timestep.c:296-351)
+            d->nlRefreshes--; d->nForceEv--; d->nlSpecRedone++;
+            d->nlValid = 0; d->refreshInFlight = 0;
+            rc = comd_dev_redistribute(d);
+            if (rc != COMD_OK) { d->inTimestep = 0; return rc; }
+            rc = computeForce(d, wantE);
+            if (rc != COMD_OK) { d->inTimestep = 0; return rc; }
+         }
+      }
       PH_MARK(d, 5);
       if (it == nSteps - 1)
       {

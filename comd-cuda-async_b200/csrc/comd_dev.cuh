@@ -206,6 +206,13 @@ struct ComdDev
    cudaStream_t commStream;      // high priority
    cudaStream_t xs;              // stream the exchange code enqueues on: `stream`, or `commStream` inside an overlapped section
    cudaEvent_t evRefresh, evPass1, evFp, evStepBegin;
+   cudaStream_t sideStream;      // boundary-shell force launches of an overlapped pass (force_n3.cuh)
+   cudaEvent_t evSideBegin, evSideDone;
+   int specStep;                 // inside a speculatively enqueued step (comd_dev_timestep): no host sync on the rebuild flag
+   long nlSpecRedone;            // speculatively enqueued steps that had to be redone behind a rebuild
+   int optNlSpeculate;           // 1 (default): list-mode steps are enqueued without waiting for the rebuild verdict
+   cudaEvent_t evFlag;           // the flag's copy to the host has landed
+   int optOverlapMode;           // 1: one-shot interior CTAs on all SMs + boundary shell on sideStream; 0: round-1 scheme
    int optOverlap;               // 1 (default): overlap where it applies
    int optOverlapSms;            // SMs an overlapped interior launch may fill (0 = default)
    int checkFused;               // the drift kernel already evaluated the list's rebuild criterion for the current positions

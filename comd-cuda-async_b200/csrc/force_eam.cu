@@ -244,6 +244,7 @@ int comdForceEAM(ComdDev* d)
    PairParams Q = {};
    Q.rc2 = rc2; Q.tPhi = d->tPhi; Q.tRho = d->tRho; Q.tF = d->tF; Q.tPR = d->tPR; Q.tW0 = d->tPR ? d->tW[0] : nullptr; Q.tW1 = d->tW[1]; Q.tDR = d->tDR;
    Q.rvPhi = d->rvPhi; Q.rvRho = d->rvRho; Q.r3 = d->r3;
+   Q.skipFlag = d->specStep ? d->cnt + C_NLREBUILD : nullptr;
    {  // rhobar never exceeds the domain of F (beyond it the lookup clamps, eam.c:561-571): 2^53 quanta over that domain
       // leave a factor 4 to the 32-bit high word and let one pair contribute up to 1/4 of the domain
       const double rhoMax = fabs(d->tF.x0) + (d->tF.n + 1) / d->tF.invDx;

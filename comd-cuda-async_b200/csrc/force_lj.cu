@@ -71,6 +71,7 @@ int comdForceLJ(ComdDev* d)
    {
       PairParams Q = {};
       Q.s6 = P.s6; Q.eps = P.eps; Q.eShift = P.eShift; Q.rc2 = P.rc2;
+      Q.skipFlag = d->specStep ? d->cnt + C_NLREBUILD : nullptr;
       if (d->useNL && d->nlN3Shape[0] > 0)
       {  // in-block pairs once (force_n3.cuh); the per-atom energies only when somebody can read them
          d->eValid = d->wantEnergy;

@@ -65,6 +65,7 @@ struct PairParams
    // list path (force_nl.cuh): 32-byte records, one sector per lookup
    const real4* rvPhi; const real4* rvRho; const real4* r3;
    double n3ScaleRho;                 // fixed-point scale of the rhobar accumulators (force_n3.cuh)
+   const int* skipFlag;               // list kernels return at once when *skipFlag != 0 (speculatively enqueued step whose list turned out stale)
 };
 
 // ---- PTX helpers: mbarrier + 1-D bulk copy (TMA engine, UBLKCP in SASS) -----------------

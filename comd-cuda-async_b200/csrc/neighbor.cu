@@ -308,9 +308,19 @@ int comdNeighborRefreshOrRebuild(ComdDev* d, int* didRefresh)
    int rc = comdAllreduceFlagDevice(d, d->cnt + C_NLREBUILD);     // "if one rebuilds, all rebuild"
    if (rc != COMD_OK) return rc;
    CUDA_TRY(cudaMemcpyAsync(d->hCnt + C_NLREBUILD, d->cnt + C_NLREBUILD, sizeof(int), cudaMemcpyDeviceToHost, s));
-   CUDA_TRY(cudaStreamSynchronize(s));
-   PH_MARK(d, 1);
-   if (d->hCnt[C_NLREBUILD]) return COMD_OK;       // caller runs the full re-bin + exchange
+   if (d->specStep)
+   {  // sync-free step (comd_dev_timestep): the host does not wait for the verdict here.  It enqueues the refresh and the
+      // force kernels of the no-rebuild case -- the force kernels read the flag on the device and return at once if it is
+      // set (PairParams::skipFlag) -- and looks at the flag after that, when the GPU has a whole step queued.
+      CUDA_TRY(cudaEventRecord(d->evFlag, s));
+      PH_MARK(d, 1);
+   }
+   else
+   {
+      CUDA_TRY(cudaStreamSynchronize(s));
+      PH_MARK(d, 1);
+      if (d->hCnt[C_NLREBUILD]) return COMD_OK;    // caller runs the full re-bin + exchange
+   }
    // More than one rank: the three exchange phases go to the high-priority exchange stream and the force
    // kernels start on the interior blocks meanwhile (force_nl.cuh); evRefresh marks "ghosts in place".
    const bool overlap = d->nRanks > 1 && d->optOverlap && d->inTimestep;   // only where the force call is known to follow

@@ -11,6 +11,7 @@ struct NlBlocks
    int total;                 // blocks this launch walks
    int phase;                 // 0 all blocks, 1 interior (no atom of the block has a ghost neighbour), 2 the boundary shell
    int chunk, nChunks;        // blocks per work chunk, chunks in this launch
+   int oneShot;               // 1: a CTA works on one chunk and retires (grid = nChunks), so kernels of a higher-priority stream find SM slots
 };
 #define NLB_ALL 0
 #define NLB_INTERIOR 1

@@ -166,7 +166,12 @@ int  comd_comm_barrier(ComdDev* dev);                               /* barrierPa
  *   "nl_threads"         list path: cap on the CTA size of the force kernels (multiple of 32)
  *   "nl_chunks_per_cta"  list path: work chunks per persistent CTA handed out through the global counter (default 32)
  *   "overlap"            list path, N > 1: halo exchange overlapped with the interior blocks (default 1)
- *   "overlap_sms"        SMs an overlapped interior launch may fill (default 140 of 148)
+ *   "nl_speculate"       list path inside comd_dev_timestep: 1 (default) enqueue each step for the no-rebuild case without waiting
+ *                        for the displacement check (the force kernels return at once if the list turns out stale, the
+ *                        host then re-bins and repeats them); 0: wait for the verdict every step (round 1)
+ *   "overlap_mode"       1 (default): interior blocks as one-shot CTAs on all SMs, boundary shell on a side stream that waits
+ *                        for the exchange only; 0: persistent interior CTAs on "overlap_sms" SMs, boundary launch behind them
+ *   "overlap_sms"        overlap_mode 0: SMs an overlapped interior launch may fill (default 140 of 148)
  *   "phase_timing"       per-phase CUDA-event timing of comd_dev_timestep, reported on stderr by comd_dev_destroy
  *   "e2e_speculate"      0 (default): comd_dev_step_host waits for its upload before the step starts.  1: a call that
  *                        follows another one may start from the atoms the device still holds while its inputs are

@@ -461,6 +461,34 @@ def test_neighbor_list_work_block_shape_is_invisible(kind, block, n3):
 
 
 @pytest.mark.parametrize("kind", list(KINDS))
+@pytest.mark.parametrize("n3", [0, 1])
+def test_neighbor_list_sync_free_step_equals_the_synchronised_step(kind, n3):
+    """comd_dev_timestep enqueues a list-mode step for the no-rebuild case without waiting for the displacement check
+    (option nl_speculate, default 1): the force kernels return at once when the flag turns out set, the host re-bins
+    and repeats them.  Same bits, same number of builds and refreshes as the step that waits for the verdict
+    (nl_speculate 0, round 1) -- over a hot run with several rebuilds."""
+    n = 8
+    orc = oracle_sim(KINDS[kind], n, delta=0.05, temperature=1500.0)
+    a = orc.atoms()
+    res = []
+    for spec in (0, 1):
+        dev, _ = device_for(orc, (n, n, n), nl_skin=0.1)
+        dev.set_option("nl_n3", n3)
+        dev.set_option("nl_speculate", spec)
+        dev.upload(a["gid"], a["r"], a["p"])
+        dev.compute_force()
+        for _ in range(5):
+            dev.timestep(10, 1.0)
+        res.append((by_gid(dev.download()), dev.energy(), dev.neighbor_counters()))
+        dev.close()
+    (d0, e0, c0), (d1, e1, c1) = res
+    assert c0 == c1 and c0["builds"] >= 3 and c0["refreshes"] >= 30
+    assert e0 == e1
+    for k in ("r", "p", "f", "U"):
+        assert np.array_equal(d0[k], d1[k]), k
+
+
+@pytest.mark.parametrize("kind", list(KINDS))
 def test_neighbor_list_full_list_kernels_still_match(kind):
     """nl_n3 0 keeps round 1's full-list kernels (every pair met from both ends, no shared-memory accumulators) and
     nl_lanes 8 the eight-lanes-per-row form of the once-per-pair kernels: same parity gate, and the same trajectory
