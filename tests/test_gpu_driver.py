@@ -54,9 +54,12 @@ def test_driver_trace_matches_reference_executable(tmp_path, flags, method):
 @pytest.mark.parametrize("flags,method", [([], "thread_atom_nl"), (["-e"], "thread_atom"), (["-e", "-t", "setfl"], "thread_atom_nl")])
 def test_single_precision_driver_trace_matches_the_float_reference(tmp_path, flags, method):
     """CoMD-b200-f32 (host/ and csrc/ built with -DCOMD_SINGLE, real_t = float end to end, mytype.h:8-24) beside the
-    reference's own float build (oracle/_ref/CoMD-ref-f32, -m cpu_nl).  Tolerances of tests/test_gpu_precision.py:
-    3e-6 on the energy sums at step 0 (the reference adds 6912 per-atom energies into a float), 2e-5 on the total
-    energy over 100 steps of two float trajectories; the kinetic energy alone is a small difference of large sums."""
+    reference's own float build (oracle/_ref/CoMD-ref-f32, -m cpu_nl) and beside its double build.
+    The float reference adds every pair's energy into ONE float accumulator (ljForce.c:222, eam.c:343,369): on 6912 atoms
+    its printed energies sit 5e-5 (LJ) to 1.1e-3 (Cu_u6) away from its own double build and wander by 3e-4 along the
+    run (measured here, CoMD-ref vs CoMD-ref-f32) -- so 2e-3 is what a comparison WITH it can resolve.  This build sums per
+    atom in float and over atoms in double, which lands on the double reference: 2e-5 on the total and potential energy
+    over 100 steps (tests/test_gpu_precision.py states the per-atom float tolerances)."""
     ref32 = REF + "-f32"
     if not os.path.exists(ref32):
         pytest.skip("oracle/_ref/CoMD-ref-f32 not built (needs /root/reference at build time)")
@@ -64,14 +67,14 @@ def test_single_precision_driver_trace_matches_the_float_reference(tmp_path, fla
     n = "12"
     common = ["-x", n, "-y", n, "-z", n, "-N", "100", "-n", "10", "-d", POTS] + flags
     ours = trace(run(os.path.join(PKG, "CoMD-b200-f32"), common + ["-m", method], tmp_path))
-    ref = trace(run(ref32, common + ["-m", "cpu_nl"], tmp_path))
-    assert len(ours) == len(ref) == 11
-    for (s0, et0, eu0, ek0, n0), (s1, et1, eu1, ek1, n1) in zip(ours, ref):
-        assert s0 == s1 and n0 == n1 == 4 * int(n) ** 3
-        tol = 3e-6 if s0 == 0 else 2e-5
-        assert abs(et0 - et1) <= tol * abs(et1), (s0, et0, et1)
-        assert abs(eu0 - eu1) <= tol * abs(eu1), (s0, eu0, eu1)
-        assert abs(ek0 - ek1) <= tol * abs(eu1), (s0, ek0, ek1)
+    for exe, tol in ((ref32, 2e-3), (REF, 2e-5)):
+        ref = trace(run(exe, common + ["-m", "cpu_nl"], tmp_path))
+        assert len(ours) == len(ref) == 11
+        for (s0, et0, eu0, ek0, n0), (s1, et1, eu1, ek1, n1) in zip(ours, ref):
+            assert s0 == s1 and n0 == n1 == 4 * int(n) ** 3
+            assert abs(et0 - et1) <= tol * abs(et1), (exe, s0, et0, et1)
+            assert abs(eu0 - eu1) <= tol * abs(eu1), (exe, s0, eu0, eu1)
+            assert abs(ek0 - ek1) <= tol * abs(eu1), (exe, s0, ek0, ek1)
 
 
 def test_driver_async_flag_gives_the_same_trace(tmp_path):
