@@ -643,7 +643,7 @@ def main():
 
     # ---- leg 2: warm-up, then EXACTLY K timed steps
     M = run_workload(R, args.workload, args.steps, args.warmup, args.print_rate, args.skin, args.neighbor_list, every_step_too=True,
-                     sampler=ClockSampler(R.local_rank) if rank == 0 else None)
+                     sampler=ClockSampler(R.local_rank) if rank == 0 and not os.environ.get("COMD_BENCH_NO_SAMPLER") else None)
     clocks = M["clocks"]
     dev, geom, n_local, n_global = M["dev"], M["geom"], M["n_local"], M["n_global"]
     fp64_peak = dev.fp64_peak()

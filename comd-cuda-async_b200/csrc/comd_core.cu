@@ -612,6 +612,7 @@ extern "C" int comd_dev_destroy(ComdDev* d)
    for (int a = 0; a < 32; ++a) for (int b = 0; b < 8; ++b) if (d->evPh[a][b]) cudaEventDestroy(d->evPh[a][b]);
    cudaEventDestroy(d->evRefresh); cudaEventDestroy(d->evPass1); cudaEventDestroy(d->evFp); cudaEventDestroy(d->evStepBegin);
    cudaStreamDestroy(d->commStream);
+   for (int ph = 0; ph < 3; ++ph) if (d->nlOrder[ph]) cudaFree(d->nlOrder[ph]);
    cudaEventDestroy(d->evFlag); cudaEventDestroy(d->evSideBegin); cudaEventDestroy(d->evSideDone); cudaStreamDestroy(d->sideStream);
    if (d->copyStream)
    {
@@ -1052,6 +1053,7 @@ extern "C" int comd_dev_set_option(ComdDev* d, const char* key, long value)
    if (!strcmp(key, "nl_lanes")) { if (value != 4 && value != 8) { comdSetError("nl_lanes: 4 or 8"); return COMD_E_ARG; } d->optNlLanes = (int)value; d->nlValid = 0; return COMD_OK; }
    if (!strcmp(key, "nl_n3")) { d->optNlN3 = value < 0 ? -1 : value != 0; d->nlValid = 0; return COMD_OK; }
    if (!strcmp(key, "overlap")) { d->optOverlap = value != 0; return COMD_OK; }
+   if (!strcmp(key, "nl_hilbert")) { d->optNlHilbert = value != 0; return COMD_OK; }
    if (!strcmp(key, "nl_speculate")) { d->optNlSpeculate = value != 0; return COMD_OK; }
    if (!strcmp(key, "overlap_mode")) { if (value < 0 || value > 1) { comdSetError("overlap_mode: 0 or 1"); return COMD_E_ARG; } d->optOverlapMode = (int)value; return COMD_OK; }
    if (!strcmp(key, "e2e_speculate")) { d->e2eSpecArmed = value != 0; return COMD_OK; }

@@ -212,6 +212,8 @@ struct ComdDev
    long nlSpecRedone;            // speculatively enqueued steps that had to be redone behind a rebuild
    int optNlSpeculate;           // 1 (default): list-mode steps are enqueued without waiting for the rebuild verdict
    cudaEvent_t evFlag;           // the flag's copy to the host has landed
+   int optNlHilbert;             // work blocks of the list kernels handed out along a Hilbert curve (CoMD's -H)
+   int* nlOrder[3]; int nlOrderShape[6];   // order tables per phase set (all / interior / boundary), nl_blocks.cuh
    int optOverlapMode;           // 1: one-shot interior CTAs on all SMs + boundary shell on sideStream; 0: round-1 scheme
    int optOverlap;               // 1 (default): overlap where it applies
    int optOverlapSms;            // SMs an overlapped interior launch may fill (0 = default)

@@ -385,3 +385,8 @@ extern "C" int comd_dev_neighbor_counters(ComdDev* d, long* nBuilds, long* nRefr
    if (nRefreshes) *nRefreshes = d->nlRefreshes;
    return COMD_OK;
 }
+
+extern "C" unsigned long long comd_hilbert_key(unsigned x, unsigned y, unsigned z, int bits)
+{
+   return bits >= 1 && bits <= 20 ? nlHilbertKey(x, y, z, bits) : 0ull;
+}

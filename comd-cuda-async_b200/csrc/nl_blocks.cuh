@@ -12,6 +12,7 @@ struct NlBlocks
    int phase;                 // 0 all blocks, 1 interior (no atom of the block has a ghost neighbour), 2 the boundary shell
    int chunk, nChunks;        // blocks per work chunk, chunks in this launch
    int oneShot;               // 1: a CTA works on one chunk and retires (grid = nChunks), so kernels of a higher-priority stream find SM slots
+   const int* order;          // traversal order of the launch's set: order[q] = linear block id (x fastest), or NULL for the index order
 };
 #define NLB_ALL 0
 #define NLB_INTERIOR 1
@@ -24,8 +25,18 @@ __host__ __device__ inline int nlInteriorCount(const NlBlocks& B)
    return (B.nbx > 2 && B.nby > 2 && B.nbz > 2) ? (B.nbx - 2) * (B.nby - 2) * (B.nbz - 2) : 0;
 }
 // q-th block of the launch's set -> block coordinates
-__device__ __forceinline__ void nlBlockCoord(const NlBlocks& B, int q, int& ix, int& iy, int& iz)
+__host__ __device__ __forceinline__ void nlBlockCoord(const NlBlocks& B, int q, int& ix, int& iy, int& iz)
 {
+   if (B.order)
+   {  // space-filling-curve traversal (option nl_hilbert, CoMD's -H): the table lists the set's blocks along the curve
+#ifdef __CUDA_ARCH__
+      const int id = __ldg(B.order + q);
+#else
+      const int id = B.order[q];
+#endif
+      ix = id % B.nbx; iy = (id / B.nbx) % B.nby; iz = id / (B.nbx * B.nby);
+      return;
+   }
    if (B.phase == NLB_INTERIOR)
    {
       const int mx = B.nbx - 2, my = B.nby - 2;
@@ -78,4 +89,75 @@ static NlBlocks nlBlocksFor(const ComdDev* d)
       if (d->optNlBlock[0] > 0 || B.total >= 148 * 8) break;
    }
    return B;
+}
+
+// ---- Hilbert traversal of the work blocks (CoMD's -H / --hilbert, linkCells.c:28-63,151-174) -----------------------
+// The reference renumbers its link cells along a 3-D Hilbert curve so that consecutive thread blocks work on cells
+// that are neighbours in space (only for power-of-two grids).  Here the unit of scheduling is the work block, so the
+// curve orders the blocks: chunks of consecutive blocks are handed to the SMs in curve order, and the blocks in
+// flight at any time share their halo cells in L2.  Any grid size: the key is computed in the enclosing power-of-two
+// cube (Skilling's transpose algorithm, "Programming the Hilbert curve", AIP Conf. Proc. 707, 2004) and the blocks of
+// the launch's set are sorted by it.  Results do not depend on the order (per-atom sums are formed inside a block).
+#include <algorithm>
+#include <vector>
+static inline unsigned long long nlHilbertKey(unsigned x, unsigned y, unsigned z, int bits)
+{
+   unsigned X[3] = { x, y, z };
+   const unsigned M = 1u << (bits - 1);
+   for (unsigned Q = M; Q > 1; Q >>= 1)                 // inverse undo of the excess work
+   {
+      const unsigned P = Q - 1;
+      for (int i = 0; i < 3; ++i)
+      {
+         if (X[i] & Q) X[0] ^= P;
+         else { const unsigned t = (X[0] ^ X[i]) & P; X[0] ^= t; X[i] ^= t; }
+      }
+   }
+   for (int i = 1; i < 3; ++i) X[i] ^= X[i - 1];        // Gray encode
+   unsigned t = 0;
+   for (unsigned Q = M; Q > 1; Q >>= 1) if (X[2] & Q) t ^= Q - 1;
+   for (int i = 0; i < 3; ++i) X[i] ^= t;
+   unsigned long long key = 0;                          // interleave the transposed bits, most significant first
+   for (int b = bits - 1; b >= 0; --b)
+      for (int i = 0; i < 3; ++i) key = (key << 1) | ((X[i] >> b) & 1u);
+   return key;
+}
+
+// order table of one phase set (device memory, cached in the handle until the block shape or the grid changes)
+static int nlBlockOrder(ComdDev* d, NlBlocks& B, int phase, cudaStream_t s)
+{
+   B.order = nullptr;
+   if (!d->optNlHilbert) return COMD_OK;
+   const int shape[6] = { B.bx, B.by, B.bz, B.nbx, B.nby, B.nbz };
+   bool same = true;
+   for (int k = 0; k < 6; ++k) same = same && d->nlOrderShape[k] == shape[k];
+   if (!same)
+   {
+      for (int ph = 0; ph < 3; ++ph) { if (d->nlOrder[ph]) cudaFree(d->nlOrder[ph]); d->nlOrder[ph] = nullptr; }
+      for (int k = 0; k < 6; ++k) d->nlOrderShape[k] = shape[k];
+   }
+   if (!d->nlOrder[phase])
+   {
+      NlBlocks T = B; T.order = nullptr; T.phase = phase;
+      const int all = B.nbx * B.nby * B.nbz, interior = nlInteriorCount(B);
+      const int n = phase == NLB_ALL ? all : (phase == NLB_INTERIOR ? interior : all - interior);
+      if (n <= 0) return COMD_OK;
+      int bits = 1;
+      while ((1 << bits) < std::max(B.nbx, std::max(B.nby, B.nbz))) ++bits;
+      std::vector<std::pair<unsigned long long, int>> keyed(n);
+      for (int q = 0; q < n; ++q)
+      {
+         int ix, iy, iz;
+         nlBlockCoord(T, q, ix, iy, iz);
+         keyed[q] = { nlHilbertKey((unsigned)ix, (unsigned)iy, (unsigned)iz, bits), ix + B.nbx * (iy + B.nby * iz) };
+      }
+      std::sort(keyed.begin(), keyed.end());
+      std::vector<int> ids(n);
+      for (int q = 0; q < n; ++q) ids[q] = keyed[q].second;
+      CUDA_TRY(cudaMalloc(&d->nlOrder[phase], n * sizeof(int)));
+      CUDA_TRY(cudaMemcpyAsync(d->nlOrder[phase], ids.data(), n * sizeof(int), cudaMemcpyHostToDevice, s));
+      CUDA_TRY(cudaStreamSynchronize(s));            // ids goes out of scope; once per shape
+   }
+   B.order = d->nlOrder[phase];
+   return COMD_OK;
 }

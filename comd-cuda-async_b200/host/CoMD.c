@@ -67,6 +67,7 @@ static void createDevice(SimFlat* s, int doeam)
    }
    const int useNL = s->method == THREAD_ATOM_NL || s->method == WARP_ATOM_NL;
    DEV_TRY(comd_dev_set_neighbor_list(s->dev, useNL, s->skinDistance));
+   if (s->useHilbert) DEV_TRY(comd_dev_set_option(s->dev, "nl_hilbert", 1));    /* -H: Hilbert traversal of the work blocks */
    if (getNRanks() > 1)
    {
       unsigned char id[COMD_COMM_ID_BYTES];
@@ -87,6 +88,7 @@ SimFlat* initSimulation(Command cmd)
    sim->ljInterpolation = cmd.ljInterpolation;
    sim->spline = cmd.spline;
    sim->usePairlist = cmd.usePairlist;
+   sim->useHilbert = cmd.doHilbert;
    if (sim->gpuProfile) sim->nSteps = 0;         /* profile mode: one force call, no steps (CoMD.c:215-218) */
 
    if (!strcmp(cmd.method, "thread_atom")) sim->method = THREAD_ATOM;

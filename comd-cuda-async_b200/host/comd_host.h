@@ -67,6 +67,7 @@ typedef struct LinkCellSt
 {
    int gridSize[3];
    int nLocalBoxes, nHaloBoxes, nTotalBoxes;
+   int useHilbert;              /* recorded for the device layer; box numbering stays getBoxFromTuple's */
    real3 localMin, localMax, boxSize, invBoxSize;
    int* nAtoms;                 /* nTotalBoxes; refreshed by sumAtoms() from the device */
 } LinkCell;
@@ -169,6 +170,7 @@ typedef struct SimFlatSt
    int method;
    int gpuAsync, gpuProfile;
    int ljInterpolation, spline, usePairlist;   /* accepted, recorded, not acted on (DESIGN.md "out of scope") */
+   int useHilbert;              /* -H: the device hands its work blocks to the SMs along a Hilbert curve (list path) */
    real_t skinDistance;
    int hostAtomsStale;          /* device state is newer than sim->atoms */
 } SimFlat;

@@ -43,8 +43,8 @@ int processorNum(Domain* dom, int dix, int diy, int diz)
 
 LinkCell* initLinkCells(const Domain* dom, real_t cutoff, int useHilbert)
 {
-   (void)useHilbert;   /* the device orders cells itself (padded x-fastest grid); -H is accepted and ignored */
    LinkCell* lc = calloc(1, sizeof *lc);
+   lc->useHilbert = useHilbert;   /* -H: acted on by the device layer (option nl_hilbert), for any grid size -- the reference needs powers of two (linkCells.c:151-155) */
    for (int a = 0; a < 3; ++a)
    {
       lc->localMin[a] = dom->localMin[a];

@@ -2,7 +2,8 @@
  * initSimulation does up to (not including) the device, and dump it for tests/test_host_layer.py.
  *   host_dump OUT.bin <CoMD options>      multi-rank: start it under comd-launch, one file per rank
  * Layout: int32 nLocal, nGlobal, grid[3], nTotalBoxes; double cutoff, mass, lat, boxSize[3], invBoxSize[3],
- *         localMin[3], localMax[3]; then gid[n] (int32), box[n] (int32), r[3][n], p[3][n] (float64).
+ *         localMin[3], localMax[3]; then gid[n] (int32), box[n] (int32), r[3][n], p[3][n] (real_t).
+ *         With --doeam the three tables follow, phi, rho, F: int32 n; double x0, invDx; real_t values[-1 .. n+1].
  */
 #include "comd_host.h"
 #include <stdlib.h>
@@ -48,6 +49,18 @@ int main(int argc, char** argv)
    }
    for (int k = 0; k < 3; ++k) fwrite(a->r[k], sizeof(real_t), a->nLocal, fp);
    for (int k = 0; k < 3; ++k) fwrite(a->p[k], sizeof(real_t), a->nLocal, fp);
+   if (cmd.doeam)
+   {  /* what eamReadFuncfl / eamReadSetfl + initInterpolationObject left in the potential (host/potentials.c) */
+      const EamPotential* e = (const EamPotential*)sim->pot;
+      const InterpolationObject* tab[3] = { e->phi, e->rho, e->f };
+      for (int k = 0; k < 3; ++k)
+      {
+         const double xd[2] = { tab[k]->x0, tab[k]->invDx };
+         fwrite(&tab[k]->n, sizeof(int), 1, fp);
+         fwrite(xd, sizeof xd, 1, fp);
+         fwrite(tab[k]->values - 1, sizeof(real_t), tab[k]->n + 3, fp);
+      }
+   }
    fclose(fp);
    if (printRank()) printf("host_dump: %d atoms (%d global), eKinetic/atom %.15g\n", a->nLocal, a->nGlobal, sim->eKinetic / a->nGlobal);
    destroyParallel();

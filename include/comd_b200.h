@@ -166,6 +166,8 @@ int  comd_comm_barrier(ComdDev* dev);                               /* barrierPa
  *   "nl_threads"         list path: cap on the CTA size of the force kernels (multiple of 32)
  *   "nl_chunks_per_cta"  list path: work chunks per persistent CTA handed out through the global counter (default 32)
  *   "overlap"            list path, N > 1: halo exchange overlapped with the interior blocks (default 1)
+ *   "nl_hilbert"         list path: work blocks handed to the SMs along a 3-D Hilbert curve instead of x-fastest index order
+ *                        (CoMD's -H / --hilbert, linkCells.c:28-63,151-174; any grid size; results unchanged; default 0)
  *   "nl_speculate"       list path inside comd_dev_timestep: 1 (default) enqueue each step for the no-rebuild case without waiting
  *                        for the displacement check (the force kernels return at once if the list turns out stale, the
  *                        host then re-bins and repeats them); 0: wait for the verdict every step (round 1)
@@ -194,6 +196,8 @@ int  comd_dev_timer_stop(ComdDev* dev, double* ms);
 /* FP64 FMA-pipe peak of this GPU (DFMA microbenchmark, TFLOP/s): the roofline denominator
  * for the force kernels; the driver's MEASURED_PEAKS.json has no FP64 entry. */
 int  comd_dev_fp64_peak(ComdDev* dev, double* tflops);
+/* position of work block (x, y, z) on the 3-D Hilbert curve of order `bits` (the key option "nl_hilbert" sorts by; needs no device) */
+unsigned long long comd_hilbert_key(unsigned x, unsigned y, unsigned z, int bits);
 /* End-to-end step through HOST buffers (bench.py `e2e`): one full timestep() whose inputs
  * (gid, r, p, f at time t; SoA, any order, all local to this rank) start in host memory and
  * whose results (gid, r, p, f, U at t+dt, in device order, *nOut of them) end there.

@@ -71,3 +71,20 @@ def test_every_option_key_is_documented_in_the_header():
     header = open(os.path.join(ROOT, "include", "comd_b200.h")).read()
     missing = sorted(k for k in keys if '"%s"' % k not in header)
     assert not missing, missing
+
+
+def test_hilbert_key_walks_the_cube_through_face_neighbours():
+    """The key option nl_hilbert sorts the work blocks by (CoMD's -H, linkCells.c:28-63): a bijection of the 2^b cube onto
+    0 .. 8^b - 1 whose consecutive cells share a face -- the property that makes consecutive work chunks neighbours in space."""
+    L = pycomd.lib()
+    for bits in (1, 2, 3, 4):
+        n = 1 << bits
+        cells = {}
+        for x in range(n):
+            for y in range(n):
+                for z in range(n):
+                    cells[L.comd_hilbert_key(x, y, z, bits)] = (x, y, z)
+        assert sorted(cells) == list(range(n ** 3))
+        path = [cells[k] for k in range(n ** 3)]
+        for a, b in zip(path, path[1:]):
+            assert sum(abs(p - q) for p, q in zip(a, b)) == 1, (bits, a, b)

@@ -462,6 +462,31 @@ def test_neighbor_list_work_block_shape_is_invisible(kind, block, n3):
 
 @pytest.mark.parametrize("kind", list(KINDS))
 @pytest.mark.parametrize("n3", [0, 1])
+def test_neighbor_list_hilbert_traversal_of_work_blocks_is_invisible(kind, n3):
+    """Option nl_hilbert (CoMD's -H, linkCells.c:28-63,151-174): the work blocks are handed to the SMs along a 3-D
+    Hilbert curve, on a grid that is NOT a power of two (the reference would refuse it).  A scheduling choice only:
+    every bit of the trajectory stays."""
+    n = 11
+    orc = oracle_sim(KINDS[kind], n, delta=0.06, temperature=900.0)
+    a = orc.atoms()
+    res = []
+    for hil in (0, 1):
+        dev, _ = device_for(orc, (n, n, n), nl_skin=0.1)
+        dev.set_option("nl_n3", n3)
+        dev.set_option("nl_block", 10201)              # small blocks: a long curve (several hundred blocks)
+        dev.set_option("nl_hilbert", hil)
+        dev.upload(a["gid"], a["r"], a["p"])
+        dev.compute_force()
+        dev.timestep(12, 1.0)
+        res.append((by_gid(dev.download()), dev.energy()))
+        dev.close()
+    assert res[0][1] == res[1][1]
+    for k in ("r", "p", "f", "U"):
+        assert np.array_equal(res[0][0][k], res[1][0][k]), k
+
+
+@pytest.mark.parametrize("kind", list(KINDS))
+@pytest.mark.parametrize("n3", [0, 1])
 def test_neighbor_list_sync_free_step_equals_the_synchronised_step(kind, n3):
     """comd_dev_timestep enqueues a list-mode step for the no-rebuild case without waiting for the displacement check
     (option nl_speculate, default 1): the force kernels return at once when the flag turns out set, the host re-bins

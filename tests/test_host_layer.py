@@ -32,9 +32,14 @@ def read_dump(path, real=np.float64):
     box = np.frombuffer(raw, np.int32, n, off); off += 4 * n
     w = np.dtype(real).itemsize
     r = np.frombuffer(raw, real, 3 * n, off).reshape(3, n).T; off += 3 * w * n
-    p = np.frombuffer(raw, real, 3 * n, off).reshape(3, n).T
+    p = np.frombuffer(raw, real, 3 * n, off).reshape(3, n).T; off += 3 * w * n
+    tables = []
+    while off < len(raw):                                         # --doeam: phi, rho, F as the host layer holds them
+        tn = struct.unpack_from("i", raw, off)[0]; off += 4
+        x0, inv_dx = struct.unpack_from("2d", raw, off); off += 16
+        tables.append(dict(n=tn, x0=x0, inv_dx=inv_dx, padded=np.frombuffer(raw, real, tn + 3, off))); off += w * (tn + 3)
     return dict(n=n, n_global=n_global, grid=(gx, gy, gz), n_boxes=n_boxes, cutoff=dh[0], mass=dh[1], lat=dh[2], box_size=dh[3:6],
-                inv_box_size=dh[6:9], local_min=dh[9:12], local_max=dh[12:15], gid=gid, box=box, r=r, p=p)
+                inv_box_size=dh[6:9], local_min=dh[9:12], local_max=dh[12:15], gid=gid, box=box, r=r, p=p, tables=tables)
 
 
 FLAGS = {"lj": [], "funcfl": ["-e"], "setfl": ["-e", "-t", "setfl"]}
@@ -89,6 +94,28 @@ def test_single_precision_host_layer_matches_the_float_reference(tools, tmp_path
     h = np.argsort(d["gid"])
     assert np.array_equal(d["r"][h], g["r"][o])
     assert np.array_equal(d["p"][h], g["p"][o])
+
+
+@pytest.mark.parametrize("kind", ["funcfl", "setfl"])
+def test_potential_readers_give_the_reference_tables_entry_for_entry(tools, tmp_path, kind):
+    """eamReadFuncfl / eamReadSetfl + initInterpolationObject (eam.c:680-872,496-519) as restated in host/potentials.c (C)
+    and pycomd/potentials.py (test plumbing): n, x0, 1/dx and every padded entry of phi, rho and F equal the oracle's,
+    and -- where oracle/_ref is built -- the tables the reference's own code leaves in its EamPotential."""
+    import pycomd.potentials as P
+    out = str(tmp_path / "t.bin")
+    subprocess.check_call([tools["host_dump"], out, "-x", "4", "-y", "4", "-z", "4", "-d", POTS] + FLAGS[kind], cwd=tmp_path, stdout=subprocess.DEVNULL)
+    host = read_dump(out)["tables"]
+    assert len(host) == 3
+    py = P.load(kind)
+    orc = po.Oracle(pot=KINDS[kind], nx=4, ny=4, nz=4, initial_force=False)
+    ref = po.Ref(["-e", "-x", 4, "-y", 4, "-z", 4] + (["-t", "setfl"] if kind == "setfl" else [])) if po.have_ref() else None
+    for which, name in enumerate(("phi", "rho", "f")):
+        want = [orc.table(which)] + ([ref.table(which)] if ref else [])
+        for w in want:
+            for got in (host[which], py[name]):
+                assert got["n"] == w["n"] and got["x0"] == w["x0"] and got["inv_dx"] == w["inv_dx"], (name, got["n"], w["n"])
+                assert np.array_equal(np.asarray(got["padded"]), w["padded"]), name
+    assert py["cutoff"] == orc.potential()["cutoff"] and py["mass"] == orc.potential()["mass"] and py["lat"] == orc.potential()["lat"]
 
 
 def test_two_ranks_partition_the_same_lattice(tools, tmp_path):

@@ -4,11 +4,13 @@ set -u
 N=${1:-2}
 mkdir -p gpurun_out
 T=r2k
-run() { python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port $1 bench.py --gpus $N "${@:2}"; }
+run() { timeout 1200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port $1 bench.py --gpus $N "${@:2}"; }
 port=29520
-for o in "nl_speculate=0,overlap_mode=0" "nl_speculate=0" "overlap_mode=0" ""; do
+IFS=";" read -ra VARIANTS <<< "${AB:-nl_speculate=0,overlap_mode=0;nl_speculate=0;overlap_mode=0;}"
+[ "${AB:-x}" != "${AB%;}" ] && VARIANTS+=("")
+for o in "${VARIANTS[@]}"; do
   port=$((port+1))
-  COMD_OPTS=$o timeout 600 run $port --no-cpu-baseline --no-verify --no-secondary --e2e-steps 1 2>/dev/null | grep '^{' > gpurun_out/${T}_ab_n${N}.json
+  COMD_OPTS=$o run $port --no-cpu-baseline --no-verify --no-secondary --e2e-steps 1 2>/dev/null | grep '^{' > gpurun_out/${T}_ab_n${N}.json
   python - <<P
 import json
 j=json.load(open('gpurun_out/${T}_ab_n${N}.json'))
@@ -16,7 +18,7 @@ print('[N=$N $o] ms/step %.3f force %.3f (every-step window %.3f ms/step) clocks
 print('   wall per 10-step call', j['config']['list_in_timed_window']['host_wall_ms_per_call'])
 P
 done 2>&1 | tee gpurun_out/${T}_ab_n${N}.txt
-( time timeout 1200 run 29540 ) > gpurun_out/${T}_bench_n$N.log 2>&1
+( time run 29540 ) > gpurun_out/${T}_bench_n$N.log 2>&1
 grep '^{' gpurun_out/${T}_bench_n$N.log > gpurun_out/${T}_bench_n$N.json
 python - <<P
 import json
