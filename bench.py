@@ -594,6 +594,11 @@ def run_workload(R, name, steps, warmup, print_rate, skin, use_nl, every_step_to
     n_global = 4 * n_cells[0] * n_cells[1] * n_cells[2]
     dev.compute_force()
     e0 = dev.energy()
+    if use_nl:
+        # first-use costs belong to the warm-up: with the list marked stale, the first warm-up step takes the rebuild branch
+        # INSIDE timestep() (re-bin, atom exchange, list build, uncached F' halo on the exchange stream) -- at N = 8 its first
+        # occurrence cost 13 ms more than any later one (NCCL's lazy set-up of those message sizes, gpurun_out/r2k_ab_n8.txt)
+        dev.set_neighbor_list(True, skin * potential["cutoff"])
     dev.timestep(warmup, 1.0)
     res = dict(name=name, pot=pot, label=label, scaling=scaling, n_global=n_global, n_local=n_local, geom=geom, dev=dev, e0=e0)
     if sampler is not None:                      # clocks + throttle reasons DURING the timed region only

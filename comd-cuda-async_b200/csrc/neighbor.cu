@@ -87,7 +87,20 @@ k_nl_build(DevGeom g, real_t rc2, real_t rl2, const real4* __restrict__ rq,
             {
                const int y = cy + (r % 3) - 1, z = cz + (r / 3) - 1;
                rowSame = y >= 0 && y < g.n[1] && z >= 0 && z < g.n[2] && y / by == cy / by && z / bz == cz / bz;
-               if (rowSame) { b1 = cellStart[rc]; b2 = cellStart[rc + 1]; tag = N3_FLAG | (unsigned)((y % by) + by * (z % bz)) << N3_ROWSHIFT; }
+               if (rowSame)
+               {
+                  b1 = cellStart[rc]; b2 = cellStart[rc + 1]; tag = N3_FLAG | (unsigned)((y % by) + by * (z % bz)) << N3_ROWSHIFT;
+                  // Candidates that would only be skipped (same block, lower index: the pair lives on the other row) are
+                  // cut out of the sweep where they form one end of the run: a lower stencil row of the same block keeps
+                  // just its out-of-block cell, the atom's own row starts behind the atom when its x-1 cell is in the block.
+                  if (r < 4)
+                  {
+                     if (xSame == 7) je = jb;
+                     else if (xSame == 3) jb = b2;
+                     else if (xSame == 6) je = b1;
+                  }
+                  else if (r == 4 && (xSame & 1)) jb = i + 1;
+               }
             }
          }
          const int maxlen = __reduce_max_sync(full, je - jb);

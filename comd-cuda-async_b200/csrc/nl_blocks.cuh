@@ -127,8 +127,12 @@ static inline unsigned long long nlHilbertKey(unsigned x, unsigned y, unsigned z
 static int nlBlockOrder(ComdDev* d, NlBlocks& B, int phase, cudaStream_t s)
 {
    B.order = nullptr;
-   if (!d->optNlHilbert) return COMD_OK;
-   const int shape[6] = { B.bx, B.by, B.bz, B.nbx, B.nby, B.nbz };
+   // Without -H: index order, except where a launch gives every CTA slot only a few blocks (small per-GPU domains): there the
+   // set is walked largest block first, so the ragged blocks at the high faces (3/4, 9/16, 27/64 of a full one on a
+   // 47-cell axis) fill the tail of the launch (longest-processing-time-first).
+   const bool lpt = !d->optNlHilbert && B.total < 148 * 2 * 16 && (d->g.n[0] % B.bx || d->g.n[1] % B.by || d->g.n[2] % B.bz);
+   if (!d->optNlHilbert && !lpt) return COMD_OK;
+   const int shape[6] = { B.bx, B.by, B.bz, B.nbx, B.nby, d->optNlHilbert ? B.nbz : -B.nbz };
    bool same = true;
    for (int k = 0; k < 6; ++k) same = same && d->nlOrderShape[k] == shape[k];
    if (!same)
@@ -149,7 +153,14 @@ static int nlBlockOrder(ComdDev* d, NlBlocks& B, int phase, cudaStream_t s)
       {
          int ix, iy, iz;
          nlBlockCoord(T, q, ix, iy, iz);
-         keyed[q] = { nlHilbertKey((unsigned)ix, (unsigned)iy, (unsigned)iz, bits), ix + B.nbx * (iy + B.nby * iz) };
+         unsigned long long key = 0;
+         if (d->optNlHilbert) key = nlHilbertKey((unsigned)ix, (unsigned)iy, (unsigned)iz, bits);
+         else
+         {  // cells of the block, descending; index order among equals
+            const int cx = std::min(B.bx, d->g.n[0] - ix * B.bx), cy = std::min(B.by, d->g.n[1] - iy * B.by), cz = std::min(B.bz, d->g.n[2] - iz * B.bz);
+            key = ((unsigned long long)(B.bx * B.by * B.bz - cx * cy * cz) << 32) | (unsigned)q;
+         }
+         keyed[q] = { key, ix + B.nbx * (iy + B.nby * iz) };
       }
       std::sort(keyed.begin(), keyed.end());
       std::vector<int> ids(n);
