@@ -374,7 +374,7 @@ def owner_of(r, gext, grid):
     return own
 
 
-def make_device(R, pot, potential, n_cells, skin_rel, use_nl, opts=(), gid_r_p=None, seed=1234):
+def make_device(R, pot, potential, n_cells, skin_rel, use_nl, opts=(), gid_r_p=None, seed=1234, precision="f64"):
     """One ComdDev for this rank's brick of an n_cells FCC lattice; atoms generated in place (or taken from the
     caller: global arrays, this rank keeps what it owns)."""
     import pycomd
@@ -382,7 +382,7 @@ def make_device(R, pot, potential, n_cells, skin_rel, use_nl, opts=(), gid_r_p=N
     lat = potential["lat"]
     gext = [n_cells[a] * lat for a in range(3)]
     skin = skin_rel * potential["cutoff"] if use_nl else 0.0
-    geom = pycomd.make_geometry(gext, potential["cutoff"] + skin, R.grid, R.coord)
+    geom = pycomd.make_geometry(gext, potential["cutoff"] + skin, R.grid, R.coord, precision=precision)
     lmin = [geom.localMin[a] for a in range(3)]; lmax = [geom.localMax[a] for a in range(3)]
     if gid_r_p is None:
         gid, r = P.fcc_block(n_cells, lat, lmin, lmax)
@@ -396,7 +396,7 @@ def make_device(R, pot, potential, n_cells, skin_rel, use_nl, opts=(), gid_r_p=N
     for a in range(3):
         ghost_frac *= (geom.gridSize[a] + 2.0) / geom.gridSize[a]
     cap = int(n_local * (2.0 * ghost_frac - 1.0) * 1.10) + 65536     # old ghosts + new ghosts coexist in the pool while redistributing
-    dev = pycomd.Device(geom, cap, device_id=R.local_rank)
+    dev = pycomd.Device(geom, cap, device_id=R.local_rank, precision=precision)
     dev.set_mass(potential["mass"])
     if pot == "lj":
         dev.set_lj(potential["sigma"], potential["epsilon"], potential["cutoff"])
@@ -585,12 +585,12 @@ def timed_steps(R, dev, steps, print_rate, dt=1.0):
                                                                  host_wall_ms_per_call=walls)
 
 
-def run_workload(R, name, steps, warmup, print_rate, skin, use_nl, every_step_too=False, opts=(), sampler=None):
+def run_workload(R, name, steps, warmup, print_rate, skin, use_nl, every_step_too=False, opts=(), sampler=None, precision="f64"):
     from pycomd import potentials as P
     pot, ncell, scaling, label = WORKLOADS[name]
     n_cells = [ncell * (R.grid[a] if scaling == "weak" else 1) for a in range(3)]
     potential = P.load(pot)
-    dev, geom, n_local = make_device(R, pot, potential, n_cells, skin, use_nl, opts=opts)
+    dev, geom, n_local = make_device(R, pot, potential, n_cells, skin, use_nl, opts=opts, precision=precision)
     n_global = 4 * n_cells[0] * n_cells[1] * n_cells[2]
     dev.compute_force()
     e0 = dev.energy()
@@ -621,6 +621,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="eam_strong", choices=sorted(WORKLOADS))
+    ap.add_argument("--dtype", default="f64", choices=["f64", "f32"], help="precision build of the library: f64 (libcomd_b200.so, the headline) or f32 "
+                    "(libcomd_b200_f32.so, the reference's -DSINGLE / DOUBLE_PRECISION=OFF build, mytype.h:8-24)")
     ap.add_argument("--e2e-steps", type=int, default=4)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-verify", action="store_true", help="skip the parity leg (A/B tuning runs only)")
@@ -647,11 +649,12 @@ def main():
     parity = None if args.no_verify else parity_leg(R)
 
     # ---- leg 2: warm-up, then EXACTLY K timed steps
-    M = run_workload(R, args.workload, args.steps, args.warmup, args.print_rate, args.skin, args.neighbor_list, every_step_too=True,
+    M = run_workload(R, args.workload, args.steps, args.warmup, args.print_rate, args.skin, args.neighbor_list, every_step_too=True, precision=args.dtype,
                      sampler=ClockSampler(R.local_rank) if rank == 0 and not os.environ.get("COMD_BENCH_NO_SAMPLER") else None)
     clocks = M["clocks"]
     dev, geom, n_local, n_global = M["dev"], M["geom"], M["n_local"], M["n_global"]
-    fp64_peak = dev.fp64_peak()
+    fp64_peak = dev.fp64_peak() if args.dtype == "f64" else dev.fp32_peak()      # the FMA pipe the build computes on
+    fp32_peak = dev.fp32_peak()
     t_max, t_every = M["t"], M["t_every"]
     n_after = dev.num_local()
 
@@ -668,6 +671,7 @@ def main():
     def pin(a):
         pa, v = pycomd.pinned_like(np.ascontiguousarray(a)); _pins.append(pa); return v
     hg, hr, hp, hf = pin(d0["gid"]), [pin(c) for c in cols(d0["r"])], [pin(c) for c in cols(d0["p"])], [pin(c) for c in cols(d0["f"])]
+    wb = np.dtype(dev.real).itemsize                # bytes per comd_real
     def chain(k, o, m):
         t0 = time.perf_counter()
         for _ in range(k):
@@ -688,8 +692,8 @@ def main():
         _, o, m = chain(1, o, m)
         t_spec, o, m = chain(args.e2e_steps, o, m)
         dev.set_option("e2e_speculate", 0)
-    h2d = n_local * (4 + 9 * 8)
-    d2h = n_local * (4 + 10 * 8) + 16              # local atoms only (compacted on the device): gid + r,p,f,U, and the two energies
+    h2d = n_local * (4 + 9 * wb)
+    d2h = n_local * (4 + 10 * wb) + 16              # local atoms only (compacted on the device): gid + r,p,f,U, and the two energies
     dev.close()
     for pa in _pins:
         pa.free()
@@ -709,8 +713,19 @@ def main():
         for key, wl, nl in (("lj_weak_C4", "lj_weak", 1), ("eam_60_C3_list", "eam_60", 1), ("eam_60_C3_linkcell", "eam_60", 0)):
             if wl == args.workload and nl == args.neighbor_list:
                 continue
-            S = run_workload(R, wl, ssteps, 3, args.print_rate, args.skin, nl)
+            S = run_workload(R, wl, ssteps, 3, args.print_rate, args.skin, nl, precision=args.dtype)
             secondary[key] = line(S, nl)
+            S["dev"].close()
+        if args.dtype == "f64":
+            # the headline workload through the single-precision build (-DCOMD_SINGLE): beside the FP64 line, never instead of it
+            S = run_workload(R, args.workload, ssteps, 3, args.print_rate, args.skin, args.neighbor_list, precision="f32")
+            ln = line(S, args.neighbor_list)
+            fl = FORCE_FLOP_PER_ATOM[S["pot"]] * S["n_local"] / (S["force_ms"] * 1e-3) * 1e-12 if S["force_ms"] > 0 else None
+            del ln["force_frac_fp64"]
+            ln.update(dtype="f32", library="libcomd_b200_f32.so", force_frac_fp32=fl / fp32_peak if fl else None, fp32_peak_tflops=fp32_peak,
+                      peak_source="FFMA microbenchmark run in this process (comd_dev_fp32_peak)",
+                      tolerance="tests/test_gpu_precision.py: 2e-6 of max|F|, max|U| at step 0 against the reference's own float build")
+            secondary[args.workload + "_f32"] = ln
             S["dev"].close()
 
     if rank != 0:
@@ -723,14 +738,15 @@ def main():
     achieved_tf = flops_force / (fms * 1e-3) * 1e-12 if fms > 0 else None
     achieved_every = flops_force / (fms_every * 1e-3) * 1e-12 if fms_every > 0 else None
     hbm_gbs = value / world * HBM_B_PER_ATOM_STEP[pot] * 1e-9
-    n3 = os.environ.get("COMD_NL_N3", "1") != "0" and "nl_n3=0" not in os.environ.get("COMD_OPTS", "")
+    # option nl_n3 "auto" (the default): once-per-pair kernels for EAM, full-list kernels for LJ
+    n3 = pot != "lj" and "nl_n3=0" not in os.environ.get("COMD_OPTS", "") or "nl_n3=1" in os.environ.get("COMD_OPTS", "")
     kern = ("k_force_n3" if n3 else "k_force_nl") if args.neighbor_list else "k_force_tile"
     dram = NCU_DRAM.get("%s_%s" % (pot, kern))
     e_sched = "pair energies evaluated only where they are read: 1 step in %d (the last of each timestep() call)" % args.print_rate if pot != "lj" or n3 else "every step"
     out = {
         "metric": "atom-steps/s", "value": value, "unit": "atom-steps/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * t_max / args.steps, "higher_is_better": True, "scaling": scaling, "vs_baseline": None,
-        "dtype": "f64", "data": "synthetic FCC Cu lattice (a=3.615 A), numpy-seeded Maxwell-Boltzmann momenta at 600 K, dt=1 fs",
+        "dtype": args.dtype, "data": "synthetic FCC Cu lattice (a=3.615 A), numpy-seeded Maxwell-Boltzmann momenta at 600 K, dt=1 fs",
         "config": {"workload": label, "atoms": n_global, "atoms_per_gpu": n_local, "proc_grid": "%dx%dx%d" % R.grid,
                    "cells_per_gpu": "%dx%dx%d" % tuple(geom.gridSize[:]), "parallelism": "3-D spatial domain decomposition, 1 rank/GPU",
                    "force_path": ("neighbour list (skin %g*cutoff, rebuilt when an atom moved > skin/2)%s" % (args.skin, "; pairs inside a work block evaluated once for both atoms" if n3 else "")) if args.neighbor_list else "link cells (re-binned every step)",
@@ -738,13 +754,13 @@ def main():
                    "list_in_timed_window": M["list"], "list_in_every_step_window": M["list_every"],
                    "l2": "working set %.0f MB per GPU > 126 MB L2 (no flush needed)" % (n_local * 200e-6) if n_local * 200 > 126e6
                          else "working set fits L2: small-config line, not the headline"},
-        "roofline": {"bound": "fp64", "kernel": "force (%s)" % (("%s<LJ>" % kern if pot == "lj" else "%s<RHO> + F' halo + %s<EAMF|EAMFE>" % (kern, kern))),
+        "roofline": {"bound": "fp64" if args.dtype == "f64" else "fp32", "kernel": "force (%s)" % (("%s<LJ>" % kern if pot == "lj" else "%s<RHO> + F' halo + %s<EAMF|EAMFE>" % (kern, kern))),
                      "achieved": achieved_tf, "peak": fp64_peak, "unit": "TFLOP/s",
                      "frac": (achieved_tf / fp64_peak) if achieved_tf else None,
                      "energy_schedule": e_sched,
                      "frac_energies_every_step": (achieved_every / fp64_peak) if achieved_every else None,
                      "force_ms_per_step_energies_every_step": fms_every,
-                     "peak_source": "DFMA microbenchmark run in this process (comd_dev_fp64_peak); MEASURED_PEAKS.json has no FP64 entry",
+                     "peak_source": ("DFMA microbenchmark run in this process (comd_dev_fp64_peak)" if args.dtype == "f64" else "FFMA microbenchmark run in this process (comd_dev_fp32_peak)") + "; MEASURED_PEAKS.json has no FP64/FP32 FMA entry",
                      "algorithmic_flop_per_atom": FORCE_FLOP_PER_ATOM[pot], "force_ms_per_step": fms,
                      "step_frac_fp64": value / world * FLOP_PER_ATOM_STEP[pot] * 1e-12 / fp64_peak,
                      "step_frac_fp64_energies_every_step": value_every / world * FLOP_PER_ATOM_STEP[pot] * 1e-12 / fp64_peak,

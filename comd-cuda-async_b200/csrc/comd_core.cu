@@ -1620,7 +1620,24 @@ k_dfma_peak(double* out, int iters, double a, double b)
    if (s == 12345.678) out[0] = s;        // never true; keeps the chain alive
 }
 
-extern "C" int comd_dev_fp64_peak(ComdDev* d, double* tflops)
+__global__ void __launch_bounds__(256)
+k_ffma_peak(double* out, int iters, float a, float b)
+{
+   float x0 = threadIdx.x * 1e-3f, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5, x6 = x0 + 6, x7 = x0 + 7;
+   for (int i = 0; i < iters; ++i)
+   {
+      x0 = fmaf(x0, a, b); x1 = fmaf(x1, a, b); x2 = fmaf(x2, a, b); x3 = fmaf(x3, a, b);
+      x4 = fmaf(x4, a, b); x5 = fmaf(x5, a, b); x6 = fmaf(x6, a, b); x7 = fmaf(x7, a, b);
+   }
+   const float s = x0 + x1 + x2 + x3 + x4 + x5 + x6 + x7;
+   if (s == 12345.678f) out[0] = s;
+}
+
+static int fmaPeak(ComdDev* d, double* tflops, bool single);
+extern "C" int comd_dev_fp64_peak(ComdDev* d, double* tflops) { return fmaPeak(d, tflops, false); }
+extern "C" int comd_dev_fp32_peak(ComdDev* d, double* tflops) { return fmaPeak(d, tflops, true); }
+
+static int fmaPeak(ComdDev* d, double* tflops, bool single)
 {
    if (!d || !tflops) return COMD_E_ARG;
    CUDA_TRY(cudaSetDevice(d->device));
@@ -1631,7 +1648,9 @@ extern "C" int comd_dev_fp64_peak(ComdDev* d, double* tflops)
    for (int rep = 0; rep < 6; ++rep)
    {
       CUDA_TRY(cudaEventRecord(a, d->stream));
-      k_dfma_peak<<<blocks, threads, 0, d->stream>>>(d->redOut, iters, 0.999999, 1e-9); LAUNCH_CHECK(d);
+      if (single) k_ffma_peak<<<blocks, threads, 0, d->stream>>>(d->redOut, iters, 0.999999f, 1e-9f);
+      else k_dfma_peak<<<blocks, threads, 0, d->stream>>>(d->redOut, iters, 0.999999, 1e-9);
+      LAUNCH_CHECK(d);
       CUDA_TRY(cudaEventRecord(b, d->stream));
       CUDA_TRY(cudaEventSynchronize(b));
       float ms = 0.f;

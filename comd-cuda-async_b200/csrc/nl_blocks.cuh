@@ -73,8 +73,10 @@ __host__ __device__ __forceinline__ void nlBlockCoord(const NlBlocks& B, int q, 
 }
 
 // cells per work block: the largest shape that still gives every SM several blocks.  4x4x4 with the once-per-pair
-// kernels (76 % of the pairs of a copper crystal are inside such a block), 4x4x2 with the full-list kernels (the
-// gathered positions of block + halo, ~90 KB, stay in L1).
+// kernels (76 % of the pairs of a copper crystal are inside such a block) where that leaves at least 8 blocks per CTA slot
+// (2 x 148 slots): C5 on one GPU 12.45 against 12.85 ms/step with 4x4x2, but on eight GPUs (47^3 cells each, 5.8 blocks per
+// slot) 1.84 against 1.74 -- the tail of the launch outweighs the pairs saved (profiles/r2_v3_block_shape_n8.txt,
+// r2_v3_block_lanes_ab.txt).  4x4x2 with the full-list kernels (the gathered positions of block + halo, ~90 KB, stay in L1).
 static NlBlocks nlBlocksFor(const ComdDev* d)
 {
    static const int shapes[][3] = { {4, 4, 4}, {4, 4, 2}, {4, 2, 2}, {2, 2, 2}, {2, 2, 1}, {2, 1, 1}, {1, 1, 1} };
@@ -86,7 +88,7 @@ static NlBlocks nlBlocksFor(const ComdDev* d)
       if (d->optNlBlock[0] > 0) { B.bx = d->optNlBlock[0]; B.by = d->optNlBlock[1]; B.bz = d->optNlBlock[2]; }
       B.nbx = (g.n[0] + B.bx - 1) / B.bx; B.nby = (g.n[1] + B.by - 1) / B.by; B.nbz = (g.n[2] + B.bz - 1) / B.bz;
       B.total = B.nbx * B.nby * B.nbz;
-      if (d->optNlBlock[0] > 0 || B.total >= 148 * 8) break;
+      if (d->optNlBlock[0] > 0 || B.total >= (k == 0 ? 148 * 16 : 148 * 8)) break;
    }
    return B;
 }

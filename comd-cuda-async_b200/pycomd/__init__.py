@@ -52,7 +52,7 @@ ABI_SYMBOLS = [
     "comd_comm_allreduce_sum", "comd_comm_allreduce_sum_int", "comd_comm_barrier", "comd_dev_sync",
     "comd_dev_kernel_stats", "comd_dev_step_host", "comd_dev_fp64_peak", "comd_dev_timer_start", "comd_dev_timer_stop",
     "comd_dev_set_option", "comd_host_alloc", "comd_host_free", "comd_dev_step_host_stats", "comd_dev_neighbor_counters", "comd_dev_halo_bytes", "comd_precision",
-    "comd_hilbert_key",
+    "comd_hilbert_key", "comd_dev_fp32_peak",
 ]
 
 _libs = {}
@@ -101,6 +101,7 @@ def lib(precision="f64"):
         L.comd_dev_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_long]
         L.comd_dev_kernel_stats.argtypes = [C.c_void_p, _dp, C.POINTER(C.c_long)]
         L.comd_dev_fp64_peak.argtypes = [C.c_void_p, _dp]
+        L.comd_dev_fp32_peak.argtypes = [C.c_void_p, _dp]
         L.comd_hilbert_key.argtypes = [C.c_uint, C.c_uint, C.c_uint, C.c_int]; L.comd_hilbert_key.restype = C.c_ulonglong
         L.comd_dev_timer_start.argtypes = [C.c_void_p]
         L.comd_dev_timer_stop.argtypes = [C.c_void_p, _dp]
@@ -332,6 +333,11 @@ class Device:
     def fp64_peak(self):
         t = C.c_double()
         self._chk(self.L.comd_dev_fp64_peak(self.h, C.byref(t)))
+        return t.value
+
+    def fp32_peak(self):
+        t = C.c_double()
+        self._chk(self.L.comd_dev_fp32_peak(self.h, C.byref(t)))
         return t.value
 
     def step_host(self, dt, gid, r, p, f):

@@ -196,6 +196,7 @@ int  comd_dev_timer_stop(ComdDev* dev, double* ms);
 /* FP64 FMA-pipe peak of this GPU (DFMA microbenchmark, TFLOP/s): the roofline denominator
  * for the force kernels; the driver's MEASURED_PEAKS.json has no FP64 entry. */
 int  comd_dev_fp64_peak(ComdDev* dev, double* tflops);
+int  comd_dev_fp32_peak(ComdDev* dev, double* tflops);    /* FFMA twin: the roofline denominator of the -DCOMD_SINGLE build */
 /* position of work block (x, y, z) on the 3-D Hilbert curve of order `bits` (the key option "nl_hilbert" sorts by; needs no device) */
 unsigned long long comd_hilbert_key(unsigned x, unsigned y, unsigned z, int bits);
 /* End-to-end step through HOST buffers (bench.py `e2e`): one full timestep() whose inputs

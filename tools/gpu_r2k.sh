@@ -7,7 +7,7 @@ T=r2k
 run() { timeout 1200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port $1 bench.py --gpus $N "${@:2}"; }
 port=29520
 IFS=";" read -ra VARIANTS <<< "${AB:-nl_speculate=0,overlap_mode=0;nl_speculate=0;overlap_mode=0;}"
-[ "${AB:-x}" != "${AB%;}" ] && VARIANTS+=("")
+AB=${AB:-;}; [ "$AB" != "${AB%;}" ] && VARIANTS+=("")
 for o in "${VARIANTS[@]}"; do
   port=$((port+1))
   COMD_OPTS=$o run $port --no-cpu-baseline --no-verify --no-secondary --e2e-steps 1 2>/dev/null | grep '^{' > gpurun_out/${T}_ab_n${N}.json
