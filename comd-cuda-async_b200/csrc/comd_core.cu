@@ -491,6 +491,7 @@ extern "C" int comd_dev_create(ComdDev** out, int deviceId, const ComdGeometry* 
       d->optOverlapMode = 1;
       CUDA_TRY(cudaEventCreateWithFlags(&d->evFlag, cudaEventDisableTiming));
       d->optNlSpeculate = 1;
+      d->optGraph = -1;
       d->xs = d->stream; d->optOverlap = 1; d->phStep = -1;
       d->e2eSpecArmed = 0;             // opt-in (option e2e_speculate): it only pays when the caller hands back bit-identical buffers
    }
@@ -612,6 +613,7 @@ extern "C" int comd_dev_destroy(ComdDev* d)
    for (int a = 0; a < 32; ++a) for (int b = 0; b < 8; ++b) if (d->evPh[a][b]) cudaEventDestroy(d->evPh[a][b]);
    cudaEventDestroy(d->evRefresh); cudaEventDestroy(d->evPass1); cudaEventDestroy(d->evFp); cudaEventDestroy(d->evStepBegin);
    cudaStreamDestroy(d->commStream);
+   if (d->stepGraph) cudaGraphExecDestroy(d->stepGraph);
    for (int ph = 0; ph < 3; ++ph) if (d->nlOrder[ph]) cudaFree(d->nlOrder[ph]);
    cudaEventDestroy(d->evFlag); cudaEventDestroy(d->evSideBegin); cudaEventDestroy(d->evSideDone); cudaStreamDestroy(d->sideStream);
    if (d->copyStream)
@@ -1011,13 +1013,12 @@ static int computeForce(ComdDev* d, int wantEnergy)
    if (d->posDirty && !d->useNL && d->optForceVariant == 1) { int rc = comdRefreshShadow(d); if (rc != COMD_OK) return rc; }
    NVTX_RANGE("computeForce");
    const int slot = d->nForceEv % 128;
-   CUDA_TRY(cudaEventRecord(d->evForce[2 * slot], d->stream));
+   if (!d->capturing) CUDA_TRY(cudaEventRecord(d->evForce[2 * slot], d->stream));     // (a replayed graph step carries no force timing)
    d->wantEnergy = wantEnergy;
    int rc = d->potKind == 1 ? comdForceLJ(d) : comdForceEAM(d);      // both set d->eValid
    if (rc != COMD_OK) return rc;
    if (d->potKind == 1 || !d->useNL) { PH_MARK(d, 3); PH_MARK(d, 4); }
-   CUDA_TRY(cudaEventRecord(d->evForce[2 * slot + 1], d->stream));
-   d->nForceEv++;
+   if (!d->capturing) { CUDA_TRY(cudaEventRecord(d->evForce[2 * slot + 1], d->stream)); d->nForceEv++; }
    return COMD_OK;
 }
 
@@ -1053,6 +1054,7 @@ extern "C" int comd_dev_set_option(ComdDev* d, const char* key, long value)
    if (!strcmp(key, "nl_lanes")) { if (value != 4 && value != 8) { comdSetError("nl_lanes: 4 or 8"); return COMD_E_ARG; } d->optNlLanes = (int)value; d->nlValid = 0; return COMD_OK; }
    if (!strcmp(key, "nl_n3")) { d->optNlN3 = value < 0 ? -1 : value != 0; d->nlValid = 0; return COMD_OK; }
    if (!strcmp(key, "overlap")) { d->optOverlap = value != 0; return COMD_OK; }
+   if (!strcmp(key, "graph_step")) { d->optGraph = value < 0 ? -1 : value != 0; return COMD_OK; }
    if (!strcmp(key, "nl_hilbert")) { d->optNlHilbert = value != 0; return COMD_OK; }
    if (!strcmp(key, "nl_speculate")) { d->optNlSpeculate = value != 0; return COMD_OK; }
    if (!strcmp(key, "overlap_mode")) { if (value < 0 || value > 1) { comdSetError("overlap_mode: 0 or 1"); return COMD_E_ARG; } d->optOverlapMode = (int)value; return COMD_OK; }
@@ -1077,7 +1079,7 @@ extern "C" int comd_dev_set_option(ComdDev* d, const char* key, long value)
 }
 
 // first half of a step: p += dt/2 f ; r += dt p/m (timestep.c:62-68), gather copy refreshed
-static int launchKickDrift(ComdDev* d, double dt, bool two = false)
+static int launchKickDrift(ComdDev* d, double dt, bool two)
 {
    NVTX_RANGE("kick + drift");
    const bool check = d->useNL && d->nlValid;
@@ -1097,6 +1099,65 @@ static int launchKickDrift(ComdDev* d, double dt, bool two = false)
    return COMD_OK;
 }
 
+// ---- CUDA-graph replay of the steady-state step (list path) -----------------------------------------------------
+// Between two list builds every step without energies enqueues the same kernels with the same arguments: fused
+// kick + kick + drift + displacement check, flag reduction and copy, ghost refresh, pass 1, F' halo, pass 3.  That
+// sequence is captured once per list build (stream capture of the very code the eager step runs) and replayed with one
+// cudaGraphLaunch; a later build updates the executable graph in place (same topology, new pointers and grids).  The
+// sync-free protocol is unchanged: the flag's copy is followed by an external event record, the host looks at it after
+// the launch, a stale list makes the captured force kernels return at once and the step is redone eagerly behind the
+// rebuild.  Where the host enqueue time of a step exceeds its GPU time (small systems) this is the difference between a
+// launch-bound and a GPU-bound step; large systems run eagerly (the host is a step ahead anyway) and keep the per-step
+// force timing events.  Reference precedent: the -a 1 step that never returns to the host (timestep.c:257-265).
+static bool graphWanted(const ComdDev* d)
+{
+   if (d->optGraph == 0 || d->optPhaseTiming) return false;
+   if (d->optGraph < 0 && (d->nRanks > 1 || d->approxAtoms > 400000)) return false;
+   if (d->nRanks > 1 && (d->fpCntValid & 7) != 7) return false;       // first exchange after a build still sizes its messages through the host
+   return true;
+}
+
+
+static int captureStepGraph(ComdDev* d, double dt)
+{
+   const long launches0 = d->nLaunches, refreshes0 = d->nlRefreshes;
+   const int posDirty0 = d->posDirty, checkFused0 = d->checkFused, refresh0 = d->refreshInFlight, eValid0 = d->eValid, wantE0 = d->wantEnergy;
+   CUDA_TRY(cudaStreamBeginCapture(d->stream, cudaStreamCaptureModeThreadLocal));
+   d->capturing = 1; d->specStep = 1;
+   int rc = launchKickDrift(d, dt, true);
+   if (rc == COMD_OK) rc = comd_dev_redistribute(d);
+   if (rc == COMD_OK) rc = computeForce(d, 0);
+   d->capturing = 0; d->specStep = 0;
+   cudaGraph_t g = nullptr;
+   const cudaError_t ce = cudaStreamEndCapture(d->stream, &g);
+   d->stepGraphLaunches = d->nLaunches - launches0; d->stepGraphRefreshes = d->nlRefreshes - refreshes0;
+   d->nLaunches = launches0; d->nlRefreshes = refreshes0;              // nothing ran yet: the replays count
+   d->posDirty = posDirty0; d->checkFused = checkFused0; d->refreshInFlight = refresh0; d->eValid = eValid0; d->wantEnergy = wantE0;
+   if (rc != COMD_OK || ce != cudaSuccess || !g)
+   {
+      if (g) cudaGraphDestroy(g);
+      cudaGetLastError();
+      if (rc == COMD_OK) { comdSetError("step graph: capture failed (%s)", cudaGetErrorString(ce)); rc = COMD_E_CUDA; }
+      return rc;
+   }
+   bool ok = false;
+   if (d->stepGraph)
+   {
+      cudaGraphExecUpdateResultInfo info;
+      ok = cudaGraphExecUpdate(d->stepGraph, g, &info) == cudaSuccess;
+      if (!ok) { cudaGetLastError(); cudaGraphExecDestroy(d->stepGraph); d->stepGraph = nullptr; }
+   }
+   if (!ok)
+   {
+      const cudaError_t ie = cudaGraphInstantiate(&d->stepGraph, g, 0);
+      if (ie != cudaSuccess) { cudaGraphDestroy(g); d->stepGraph = nullptr; comdSetError("step graph: instantiate failed (%s)", cudaGetErrorString(ie)); return COMD_E_CUDA; }
+   }
+   cudaGraphDestroy(g);
+   d->stepGraphGen = d->nlBuilds; d->stepGraphDt = dt;
+   d->stepGraphOpts = d->optOverlap * 2 + d->optOverlapMode;
+   return COMD_OK;
+}
+
 extern "C" int comd_dev_timestep(ComdDev* d, int nSteps, double dt)
 {
    if (!d || nSteps < 0) return COMD_E_ARG;
@@ -1107,28 +1168,51 @@ extern "C" int comd_dev_timestep(ComdDev* d, int nSteps, double dt)
    {
       d->phStep = it; d->inTimestep = 1;
       PH_MARK(d, 0);
-      int rc = launchKickDrift(d, dt, it > 0);    // it > 0: the previous step left its second half-kick to this kernel
-      if (rc != COMD_OK) { d->inTimestep = 0; return rc; }
       const int wantE = it == nSteps - 1 || d->optEnergyEveryStep;
-      // List mode with a valid list: the step is enqueued for the common case (no rebuild) without waiting for the
-      // verdict of the displacement check; the host reads the flag once the force kernels are queued, i.e. while the
-      // GPU is busy with them.  Where the reference needed its -a 1 two-stream step to stay ahead of the GPU
-      // (timestep.c:257-265, eam.c:201-257).
-      d->specStep = d->useNL && d->nlValid && d->optNlSpeculate;
-      const int spec = d->specStep;
-      rc = comd_dev_redistribute(d);               // marks 1 (decision known / flag on its way) and 2 (ghosts in place / enqueued)
-      if (rc != COMD_OK) { d->inTimestep = 0; d->specStep = 0; return rc; }
-      PH_MARK(d, 2);
-      rc = computeForce(d, wantE);                 // marks 3, 4
-      d->specStep = 0;
-      if (rc != COMD_OK) { d->inTimestep = 0; return rc; }
+      int rc = COMD_OK;
+      int spec = 0;
+      bool replay = false;
+      if (it > 0 && !wantE && d->useNL && d->nlValid && d->optNlSpeculate && graphWanted(d))
+      {  // steady-state step: one graph launch (captured once per list build)
+         if (!d->stepGraph || d->stepGraphGen != d->nlBuilds || d->stepGraphDt != dt || d->stepGraphOpts != d->optOverlap * 2 + d->optOverlapMode)
+         {
+            rc = captureStepGraph(d, dt);
+            if (rc != COMD_OK) { d->optGraph = 0; cudaGetLastError(); }       // fall back to eager enqueueing for good
+         }
+         replay = rc == COMD_OK;
+      }
+      if (replay)
+      {
+         CUDA_TRY(cudaGraphLaunch(d->stepGraph, d->stream));
+         d->nLaunches += d->stepGraphLaunches; d->nlRefreshes += d->stepGraphRefreshes; d->nGraphSteps++;
+         d->posDirty = 1; d->checkFused = 0; d->refreshInFlight = 0; d->eValid = 0; d->wantEnergy = 0;
+         spec = 1;
+      }
+      else
+      {
+         rc = launchKickDrift(d, dt, it > 0);     // it > 0: the previous step left its second half-kick to this kernel
+         if (rc != COMD_OK) { d->inTimestep = 0; return rc; }
+         // List mode with a valid list: the step is enqueued for the common case (no rebuild) without waiting for the
+         // verdict of the displacement check; the host reads the flag once the force kernels are queued, i.e. while the
+         // GPU is busy with them.  Where the reference needed its -a 1 two-stream step to stay ahead of the GPU
+         // (timestep.c:257-265, eam.c:201-257).
+         d->specStep = d->useNL && d->nlValid && d->optNlSpeculate;
+         spec = d->specStep;
+         rc = comd_dev_redistribute(d);            // marks 1 (decision known / flag on its way) and 2 (ghosts in place / enqueued)
+         if (rc != COMD_OK) { d->inTimestep = 0; d->specStep = 0; return rc; }
+         PH_MARK(d, 2);
+         rc = computeForce(d, wantE);              // marks 3, 4
+         d->specStep = 0;
+         if (rc != COMD_OK) { d->inTimestep = 0; return rc; }
+      }
       if (spec)
       {
          CUDA_TRY(cudaEventSynchronize(d->evFlag));
          if (d->hCnt[C_NLREBUILD])
          {  // some atom on some rank moved more than skin/2: the kernels above returned at once.  Now the real thing:
             // re-bin + atom exchange + sort + list build (redistributeAtomsGpuNL's rebuild branch, timestep.c:296-351)
-            d->nlRefreshes--; d->nForceEv--; d->nlSpecRedone++;
+            d->nlRefreshes--; d->nlSpecRedone++;
+            if (!replay) d->nForceEv--;            // (a replayed step carries no timing events)
             d->nlValid = 0; d->refreshInFlight = 0;
             rc = comd_dev_redistribute(d);
             if (rc != COMD_OK) { d->inTimestep = 0; return rc; }
@@ -1160,6 +1244,14 @@ extern "C" int comd_dev_timestep(ComdDev* d, int nSteps, double dt)
       }
       cudaGetLastError();
    }
+   return COMD_OK;
+}
+
+extern "C" int comd_dev_step_stats(ComdDev* d, long* nGraphSteps, long* nRedoneSteps)
+{
+   if (!d) return COMD_E_ARG;
+   if (nGraphSteps) *nGraphSteps = d->nGraphSteps;
+   if (nRedoneSteps) *nRedoneSteps = d->nlSpecRedone;
    return COMD_OK;
 }
 
@@ -1495,7 +1587,7 @@ static int stepHostImpl(ComdDev* d, int n, double dt, bool inputsOnDevice,
    // positions and gids are final after the drift + redistribute and cross PCIe (copy stream) while the
    // force kernels run; momenta, forces and energies follow after the second kick.
    d->inTimestep = 1;
-   int rc = launchKickDrift(d, dt);
+   int rc = launchKickDrift(d, dt, false);
    if (rc == COMD_OK) rc = comd_dev_redistribute(d);
    if (rc != COMD_OK) { d->inTimestep = 0; return rc; }
    const real_t* cin[10] = { d->A.r[0], d->A.r[1], d->A.r[2], d->A.p[0], d->A.p[1], d->A.p[2], d->f[0], d->f[1], d->f[2], d->e };

@@ -212,6 +212,11 @@ struct ComdDev
    long nlSpecRedone;            // speculatively enqueued steps that had to be redone behind a rebuild
    int optNlSpeculate;           // 1 (default): list-mode steps are enqueued without waiting for the rebuild verdict
    cudaEvent_t evFlag;           // the flag's copy to the host has landed
+   // CUDA-graph replay of the steady-state list-mode step (comd_dev_timestep): captured once per list build
+   cudaGraphExec_t stepGraph; long stepGraphGen; double stepGraphDt; int stepGraphOpts;
+   long stepGraphLaunches, stepGraphRefreshes, nGraphSteps;
+   int capturing;                // the compute stream is in capture mode: no host-visible event records, no timing ring
+   int optGraph;                 // -1 auto (small systems on one rank), 0 off, 1 on
    int optNlHilbert;             // work blocks of the list kernels handed out along a Hilbert curve (CoMD's -H)
    int* nlOrder[3]; int nlOrderShape[6];   // order tables per phase set (all / interior / boundary), nl_blocks.cuh
    int optOverlapMode;           // 1: one-shot interior CTAs on all SMs + boundary shell on sideStream; 0: round-1 scheme

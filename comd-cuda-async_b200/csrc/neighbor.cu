@@ -325,7 +325,8 @@ int comdNeighborRefreshOrRebuild(ComdDev* d, int* didRefresh)
    {  // sync-free step (comd_dev_timestep): the host does not wait for the verdict here.  It enqueues the refresh and the
       // force kernels of the no-rebuild case -- the force kernels read the flag on the device and return at once if it is
       // set (PairParams::skipFlag) -- and looks at the flag after that, when the GPU has a whole step queued.
-      CUDA_TRY(cudaEventRecord(d->evFlag, s));
+      // (inside a graph capture the record must be an external one to stay visible to cudaEventSynchronize)
+      CUDA_TRY(cudaEventRecordWithFlags(d->evFlag, s, d->capturing ? cudaEventRecordExternal : cudaEventRecordDefault));
       PH_MARK(d, 1);
    }
    else

@@ -52,7 +52,7 @@ ABI_SYMBOLS = [
     "comd_comm_allreduce_sum", "comd_comm_allreduce_sum_int", "comd_comm_barrier", "comd_dev_sync",
     "comd_dev_kernel_stats", "comd_dev_step_host", "comd_dev_fp64_peak", "comd_dev_timer_start", "comd_dev_timer_stop",
     "comd_dev_set_option", "comd_host_alloc", "comd_host_free", "comd_dev_step_host_stats", "comd_dev_neighbor_counters", "comd_dev_halo_bytes", "comd_precision",
-    "comd_hilbert_key", "comd_dev_fp32_peak",
+    "comd_hilbert_key", "comd_dev_fp32_peak", "comd_dev_step_stats",
 ]
 
 _libs = {}
@@ -334,6 +334,11 @@ class Device:
         t = C.c_double()
         self._chk(self.L.comd_dev_fp64_peak(self.h, C.byref(t)))
         return t.value
+
+    def step_stats(self):
+        a = C.c_long(); b = C.c_long()
+        self._chk(self.L.comd_dev_step_stats(self.h, C.byref(a), C.byref(b)))
+        return dict(graph_steps=a.value, redone_steps=b.value)
 
     def fp32_peak(self):
         t = C.c_double()

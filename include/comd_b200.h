@@ -166,6 +166,9 @@ int  comd_comm_barrier(ComdDev* dev);                               /* barrierPa
  *   "nl_threads"         list path: cap on the CTA size of the force kernels (multiple of 32)
  *   "nl_chunks_per_cta"  list path: work chunks per persistent CTA handed out through the global counter (default 32)
  *   "overlap"            list path, N > 1: halo exchange overlapped with the interior blocks (default 1)
+ *   "graph_step"         list path inside comd_dev_timestep: steps between two list builds that need no energies are replayed
+ *                        from a CUDA graph captured once per build (one launch per step).  -1 (default): on one rank with up
+ *                        to 400 000 atoms, where a step is launch-bound; 0 off; 1 on wherever the step qualifies
  *   "nl_hilbert"         list path: work blocks handed to the SMs along a 3-D Hilbert curve instead of x-fastest index order
  *                        (CoMD's -H / --hilbert, linkCells.c:28-63,151-174; any grid size; results unchanged; default 0)
  *   "nl_speculate"       list path inside comd_dev_timestep: 1 (default) enqueue each step for the no-rebuild case without waiting
@@ -195,6 +198,9 @@ int  comd_dev_timer_start(ComdDev* dev);
 int  comd_dev_timer_stop(ComdDev* dev, double* ms);
 /* FP64 FMA-pipe peak of this GPU (DFMA microbenchmark, TFLOP/s): the roofline denominator
  * for the force kernels; the driver's MEASURED_PEAKS.json has no FP64 entry. */
+/* steps of comd_dev_timestep replayed from the CUDA graph (option "graph_step"), and speculatively enqueued steps that were
+ * repeated behind a list rebuild (option "nl_speculate") */
+int  comd_dev_step_stats(ComdDev* dev, long* nGraphSteps, long* nRedoneSteps);
 int  comd_dev_fp64_peak(ComdDev* dev, double* tflops);
 int  comd_dev_fp32_peak(ComdDev* dev, double* tflops);    /* FFMA twin: the roofline denominator of the -DCOMD_SINGLE build */
 /* position of work block (x, y, z) on the 3-D Hilbert curve of order `bits` (the key option "nl_hilbert" sorts by; needs no device) */

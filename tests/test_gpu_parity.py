@@ -514,6 +514,35 @@ def test_neighbor_list_sync_free_step_equals_the_synchronised_step(kind, n3):
 
 
 @pytest.mark.parametrize("kind", list(KINDS))
+@pytest.mark.parametrize("n3", [0, 1])
+def test_neighbor_list_graph_replayed_steps_equal_eager_steps(kind, n3):
+    """Option graph_step: the steps between two list builds that need no energies are replayed from a CUDA graph captured
+    once per build (kick + kick + drift + check, flag, ghost refresh, force kernels -- one launch).  Same bits as the
+    eagerly enqueued steps over a hot run with several rebuilds; the rebuild steps themselves are redone eagerly."""
+    n = 8
+    orc = oracle_sim(KINDS[kind], n, delta=0.05, temperature=1500.0)
+    a = orc.atoms()
+    res = []
+    for graph in (0, 1):
+        dev, _ = device_for(orc, (n, n, n), nl_skin=0.1)
+        dev.set_option("nl_n3", n3)
+        dev.set_option("graph_step", graph)
+        dev.upload(a["gid"], a["r"], a["p"])
+        dev.compute_force()
+        for _ in range(5):
+            dev.timestep(10, 1.0)
+        res.append((by_gid(dev.download()), dev.energy(), dev.neighbor_counters(), dev.step_stats(), dev.kernel_stats()["launches"]))
+        dev.close()
+    (d0, e0, c0, s0, l0), (d1, e1, c1, s1, l1) = res
+    assert s0["graph_steps"] == 0 and s1["graph_steps"] >= 25          # 8 of the 10 steps of a call qualify, minus the rebuild steps
+    assert c0 == c1 and c0["builds"] >= 3 and s0["redone_steps"] == s1["redone_steps"] == c0["builds"] - 1
+    assert l0 == l1                                                     # the replays are counted kernel by kernel
+    assert e0 == e1
+    for k in ("r", "p", "f", "U"):
+        assert np.array_equal(d0[k], d1[k]), k
+
+
+@pytest.mark.parametrize("kind", list(KINDS))
 def test_neighbor_list_full_list_kernels_still_match(kind):
     """nl_n3 0 keeps round 1's full-list kernels (every pair met from both ends, no shared-memory accumulators) and
     nl_lanes 8 the eight-lanes-per-row form of the once-per-pair kernels: same parity gate, and the same trajectory
