@@ -520,7 +520,8 @@ def parity_leg(R):
     # run 0: defaults (sync-free steps; N > 1: exchange overlapped, one-shot interior CTAs + boundary shell on a side stream);
     # run 1: round 1's step (host waits for the rebuild verdict every step; N > 1: overlapped, persistent interior CTAs on
     # 140 SMs); run 2 (N > 1): no overlap at all
-    variants = [[], ["nl_speculate=0", "overlap_mode=0"]] + ([["overlap=0"]] if R.world > 1 else [])
+    # run 3 (N > 1): steady-state steps replayed from a CUDA graph (on one rank that is run 0's default at this size)
+    variants = [[], ["nl_speculate=0", "overlap_mode=0"]] + ([["overlap=0"], ["graph_step=1"]] if R.world > 1 else [])
     for vopts in variants:
         dev, geom, _ = make_device(R, "funcfl", potential, [n] * 3, 0.1, True, opts=vopts, gid_r_p=(og["gid"], og["r"], pd))
         dev.compute_force()
@@ -530,9 +531,9 @@ def parity_leg(R):
         nc = dev.neighbor_counters()
         rebin(dev)
         dev.compute_force()            # the re-bin re-sorts r and p only (as the reference's does); forces on the new owners
-        runs.append((gathered_state(R, dev), R.reduce([e[0] + e[1]])[0], own0, nc))
+        runs.append((gathered_state(R, dev), R.reduce([e[0] + e[1]])[0], own0, nc, dev.step_stats()))
         dev.close()
-    sd, ed, own0, nc = runs[0]
+    sd, ed, own0, nc, st0 = runs[0]
     if R.rank == 0:
         orc2 = po.Oracle(pot=po.POT_FUNCFL, nx=n, ny=n, nz=n, delta=0.1, temperature=600.0)
         orc2.set_atoms(og["gid"], og["r"], pd)
@@ -554,9 +555,12 @@ def parity_leg(R):
     same_bits = lambda q: bool(all(np.array_equal(sd[k], q[k]) for k in ("gid", "r", "p", "f", "owner")))
     rec["sync_free_step_bit_identical_to_synchronised"] = same_bits(runs[1][0]) and runs[1][3] == nc
     ok &= rec["sync_free_step_bit_identical_to_synchronised"]
+    rec["drift"]["steps_replayed_from_cuda_graph"] = st0["graph_steps"]
     if R.world > 1:
         rec["overlap_on_off_bit_identical"] = same_bits(runs[2][0])
-        ok &= rec["overlap_on_off_bit_identical"]
+        rec["graph_step_bit_identical"] = same_bits(runs[3][0]) and runs[3][3] == nc
+        rec["graph_step_replays"] = runs[3][4]["graph_steps"]
+        ok &= rec["overlap_on_off_bit_identical"] and rec["graph_step_bit_identical"]
     rec["pass"] = bool(ok)
     rec["wall_s"] = round(time.time() - t_begin, 1)
     return rec
