@@ -17,7 +17,14 @@ struct cudaDeviceProp { char name[256]; int multiProcessorCount; size_t totalGlo
 typedef struct cudaDeviceProp cudaDeviceProp;
 static inline cudaError_t cudaMalloc(void** p, size_t n) { *p = calloc(1, n ? n : 1); return 0; }
 static inline cudaError_t cudaMallocHost(void** p, size_t n) { *p = calloc(1, n ? n : 1); return 0; }
+#ifdef REF_BIND_B200
+/* CoMD-ref-b200 runs the reference's GPU set-up and tear-down (AllocateGpu / DestroyGpu): DestroyGpu hands cudaFree pointers it
+ * never allocated (spline coefficients of an unused option, gpu_utility.c:330-334) -- an error code from the real runtime, a crash
+ * from free().  The process ends right after, so nothing is released here. */
+static inline cudaError_t cudaFree(void* p) { (void)p; return 0; }
+#else
 static inline cudaError_t cudaFree(void* p) { free(p); return 0; }
+#endif
 static inline cudaError_t cudaFreeHost(void* p) { free(p); return 0; }
 static inline cudaError_t cudaMemcpy(void* d, const void* s, size_t n, int k) { (void)k; memmove(d, s, n); return 0; }
 static inline cudaError_t cudaMemcpyAsync(void* d, const void* s, size_t n, int k, cudaStream_t st) { (void)k; (void)st; memmove(d, s, n); return 0; }

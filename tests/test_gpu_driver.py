@@ -77,6 +77,28 @@ def test_single_precision_driver_trace_matches_the_float_reference(tmp_path, fla
             assert abs(ek0 - ek1) <= tol * abs(eu1), (exe, s0, ek0, ek1)
 
 
+@pytest.mark.parametrize("flags,method", [([], "thread_atom"), (["-e"], "thread_atom"), (["-e"], "thread_atom_nl"), (["-e", "-t", "setfl"], "warp_atom_nl")])
+def test_reference_host_code_drives_the_library_through_its_own_control_flow(tmp_path, flags, method):
+    """The drop-in proof of INTEGRATION.md section 2: oracle/_ref/CoMD-ref-b200 = the reference's UNMODIFIED host C (main,
+    initSimulation, timestep, redistributeAtomsGpu[NL], eamForceGpu / ljForce, kineticEnergyGpu, command line, print-out)
+    with its device entry points bound to libcomd_b200.so by oracle/ref_build/ref_bind_b200.c.  Run with the reference's GPU
+    methods, its trace must be the trace of the reference's CPU path (-m cpu_nl): same gates as CoMD-b200 above."""
+    bound = REF + "-b200"
+    if not os.path.exists(bound) or not os.path.exists(REF):
+        pytest.skip("oracle/_ref/CoMD-ref-b200 not built (needs /root/reference at build time)")
+    n = "12"
+    common = ["-x", n, "-y", n, "-z", n, "-N", "100", "-n", "10", "-d", POTS] + flags
+    ours = trace(run(bound, common + ["-m", method], tmp_path))
+    ref = trace(run(REF, common + ["-m", "cpu_nl"], tmp_path))
+    assert len(ours) == len(ref) == 11
+    for (s0, et0, eu0, ek0, n0), (s1, et1, eu1, ek1, n1) in zip(ours, ref):
+        assert s0 == s1 and n0 == n1 == 4 * int(n) ** 3
+        tol = 2e-12 if s0 == 0 else 1e-6
+        assert abs(et0 - et1) <= tol * abs(et1) + 1.5e-12, (s0, et0, et1)
+        assert abs(eu0 - eu1) <= tol * abs(eu1) + 1.5e-12, (s0, eu0, eu1)
+        assert abs(ek0 - ek1) <= max(tol, 1e-6 if s0 else 0) * abs(ek1) + 1.5e-12, (s0, ek0, ek1)
+
+
 def test_driver_async_flag_gives_the_same_trace(tmp_path):
     subprocess.check_call(["make", "-s", "-C", PKG, "host"])
     args = ["-x", "10", "-y", "10", "-z", "10", "-N", "30", "-n", "10", "-e", "-d", POTS]

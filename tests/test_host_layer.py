@@ -118,6 +118,27 @@ def test_potential_readers_give_the_reference_tables_entry_for_entry(tools, tmp_
     assert py["cutoff"] == orc.potential()["cutoff"] and py["mass"] == orc.potential()["mass"] and py["lat"] == orc.potential()["lat"]
 
 
+def test_reference_host_code_links_against_the_c_abi(tmp_path, gpu_available):
+    """INTEGRATION.md section 2 as a build: the reference's own host C (compiled unmodified from /root/reference by
+    oracle/ref_build/Makefile) with its device entry points bound to libcomd_b200.so through oracle/ref_build/ref_bind_b200.c.
+    Here (no GPU needed): it links, its undefined symbols are the C ABI's, and without a device it stops at comd_dev_create
+    with the library's message -- no CPU fallback behind the reference's GPU methods.  tests/test_gpu_driver.py runs it."""
+    exe = os.path.join(ROOT, "oracle", "_ref", "CoMD-ref-b200")
+    if os.path.isdir("/root/reference/src-mpi"):
+        subprocess.check_call(["make", "-s", "-C", PKG, "libcomd_b200.so"])
+        subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "oracle", "ref_build"), "../_ref/CoMD-ref-b200"])
+    if not os.path.exists(exe):
+        pytest.skip("oracle/_ref/CoMD-ref-b200 not built (needs /root/reference at build time)")
+    und = subprocess.run(["nm", "-D", "--undefined-only", exe], capture_output=True, text=True, check=True).stdout
+    for sym in ("comd_dev_create", "comd_dev_upload_atoms", "comd_dev_redistribute", "comd_dev_compute_force", "comd_dev_energy",
+                "comd_dev_advance_velocity", "comd_dev_advance_position", "comd_dev_set_eam", "comd_dev_set_lj"):
+        assert sym in und, sym
+    if not gpu_available:
+        res = subprocess.run([exe, "-e", "-x", "6", "-y", "6", "-z", "6", "-N", "10", "-n", "5", "-d", POTS, "-m", "thread_atom"],
+                             cwd=tmp_path, capture_output=True, text=True)
+        assert "no CUDA device" in res.stderr and "comd_dev_create" in res.stderr
+
+
 def test_two_ranks_partition_the_same_lattice(tools, tmp_path):
     out = str(tmp_path / "d.bin")
     subprocess.check_call([tools["comd-launch"], "-n", "2", tools["host_dump"], out, "-x", "10", "-y", "6", "-z", "6", "-i", "2", "-r", "0.03",
