@@ -628,6 +628,7 @@ extern "C" int comd_dev_destroy(ComdDev* d)
 
 extern "C" int comd_dev_set_mass(ComdDev* d, double m)
 {
+   if (d) d->stepGraphGen = -1;                     // the captured kick + drift kernel carries 1/m
    if (!d || !(m > R(0.0))) { comdSetError("comd_dev_set_mass: bad argument"); return COMD_E_ARG; }
    d->e2ePristine = 0;
    d->mass = m;
@@ -1049,6 +1050,7 @@ int comdRefreshShadow(ComdDev* d)
 extern "C" int comd_dev_set_option(ComdDev* d, const char* key, long value)
 {
    if (!d || !key) return COMD_E_ARG;
+   d->stepGraphGen = -1;                            // a captured step holds launch shapes and arguments: capture again
    if (!strcmp(key, "force_variant")) { if (value < 0 || value > 1) { comdSetError("force_variant: 0 or 1"); return COMD_E_ARG; } d->optForceVariant = (int)value; return COMD_OK; }
    if (!strcmp(key, "nl_chunks_per_cta")) { if (value < 0 || value > 64) { comdSetError("nl_chunks_per_cta: 0..64"); return COMD_E_ARG; } d->optNlChunksPerCta = (int)value; return COMD_OK; }
    if (!strcmp(key, "nl_lanes")) { if (value != 4 && value != 8) { comdSetError("nl_lanes: 4 or 8"); return COMD_E_ARG; } d->optNlLanes = (int)value; d->nlValid = 0; return COMD_OK; }
