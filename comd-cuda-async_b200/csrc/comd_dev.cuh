@@ -218,7 +218,7 @@ struct ComdDev
    int capturing;                // the compute stream is in capture mode: no host-visible event records, no timing ring
    int optGraph;                 // -1 auto (small systems on one rank), 0 off, 1 on
    int optNlHilbert;             // work blocks of the list kernels handed out along a Hilbert curve (CoMD's -H)
-   int* nlOrder[3]; int nlOrderShape[6];   // order tables per phase set (all / interior / boundary), nl_blocks.cuh
+   int* nlOrder[3]; int nlOrderSig[3][7];   // order tables per phase set (all / interior / boundary) and what each was built for, nl_blocks.cuh
    int optOverlapMode;           // 1: one-shot interior CTAs on all SMs + boundary shell on sideStream; 0: round-1 scheme
    int optOverlap;               // 1 (default): overlap where it applies
    int optOverlapSms;            // SMs an overlapped interior launch may fill (0 = default)

@@ -24,19 +24,16 @@ __host__ __device__ inline int nlInteriorCount(const NlBlocks& B)
 {
    return (B.nbx > 2 && B.nby > 2 && B.nbz > 2) ? (B.nbx - 2) * (B.nby - 2) * (B.nbz - 2) : 0;
 }
-// q-th block of the launch's set -> block coordinates
-__host__ __device__ __forceinline__ void nlBlockCoord(const NlBlocks& B, int q, int& ix, int& iy, int& iz)
+// q-th block of the launch's set -> block coordinates.  On the device every set but "all blocks in index order" comes with
+// an order table (nlBlockOrder below: interior / boundary split, Hilbert traversal, largest-first), so the kernels carry one
+// table read instead of the case analysis; the host enumerates the sets with nlBlockCoordOfSet.
+__device__ __forceinline__ void nlBlockCoord(const NlBlocks& B, int q, int& ix, int& iy, int& iz)
 {
-   if (B.order)
-   {  // space-filling-curve traversal (option nl_hilbert, CoMD's -H): the table lists the set's blocks along the curve
-#ifdef __CUDA_ARCH__
-      const int id = __ldg(B.order + q);
-#else
-      const int id = B.order[q];
-#endif
-      ix = id % B.nbx; iy = (id / B.nbx) % B.nby; iz = id / (B.nbx * B.nby);
-      return;
-   }
+   const int id = B.order ? __ldg(B.order + q) : q;
+   ix = id % B.nbx; iy = (id / B.nbx) % B.nby; iz = id / (B.nbx * B.nby);
+}
+static inline void nlBlockCoordOfSet(const NlBlocks& B, int q, int& ix, int& iy, int& iz)
+{
    if (B.phase == NLB_INTERIOR)
    {
       const int mx = B.nbx - 2, my = B.nby - 2;
@@ -133,14 +130,16 @@ static int nlBlockOrder(ComdDev* d, NlBlocks& B, int phase, cudaStream_t s)
    // set is walked largest block first, so the ragged blocks at the high faces (3/4, 9/16, 27/64 of a full one on a
    // 47-cell axis) fill the tail of the launch (longest-processing-time-first).
    const bool lpt = !d->optNlHilbert && B.total < 148 * 2 * 16 && (d->g.n[0] % B.bx || d->g.n[1] % B.by || d->g.n[2] % B.bz);
-   if (!d->optNlHilbert && !lpt) return COMD_OK;
-   const int shape[6] = { B.bx, B.by, B.bz, B.nbx, B.nby, d->optNlHilbert ? B.nbz : -B.nbz };
+   const bool split = phase != NLB_ALL && nlInteriorCount(B) > 0;        // the interior / boundary sets are not index ranges
+   if (!d->optNlHilbert && !lpt && !split) return COMD_OK;
+   // one cached table per set, valid while the block shape, the grid and the kind of order stay the same
+   const int sig[7] = { B.bx, B.by, B.bz, B.nbx, B.nby, B.nbz, d->optNlHilbert ? 2 : (lpt ? 1 : 0) };
    bool same = true;
-   for (int k = 0; k < 6; ++k) same = same && d->nlOrderShape[k] == shape[k];
+   for (int k = 0; k < 7; ++k) same = same && d->nlOrderSig[phase][k] == sig[k];
    if (!same)
    {
-      for (int ph = 0; ph < 3; ++ph) { if (d->nlOrder[ph]) cudaFree(d->nlOrder[ph]); d->nlOrder[ph] = nullptr; }
-      for (int k = 0; k < 6; ++k) d->nlOrderShape[k] = shape[k];
+      if (d->nlOrder[phase]) { cudaFree(d->nlOrder[phase]); d->nlOrder[phase] = nullptr; }
+      for (int k = 0; k < 7; ++k) d->nlOrderSig[phase][k] = sig[k];
    }
    if (!d->nlOrder[phase])
    {
@@ -154,10 +153,10 @@ static int nlBlockOrder(ComdDev* d, NlBlocks& B, int phase, cudaStream_t s)
       for (int q = 0; q < n; ++q)
       {
          int ix, iy, iz;
-         nlBlockCoord(T, q, ix, iy, iz);
-         unsigned long long key = 0;
+         nlBlockCoordOfSet(T, q, ix, iy, iz);
+         unsigned long long key = (unsigned long long)q;          // the set in its own order
          if (d->optNlHilbert) key = nlHilbertKey((unsigned)ix, (unsigned)iy, (unsigned)iz, bits);
-         else
+         else if (lpt)
          {  // cells of the block, descending; index order among equals
             const int cx = std::min(B.bx, d->g.n[0] - ix * B.bx), cy = std::min(B.by, d->g.n[1] - iy * B.by), cz = std::min(B.bz, d->g.n[2] - iz * B.bz);
             key = ((unsigned long long)(B.bx * B.by * B.bz - cx * cy * cz) << 32) | (unsigned)q;
