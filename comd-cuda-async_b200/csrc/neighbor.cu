@@ -36,12 +36,16 @@ __device__ __forceinline__ int nlSlot(int pos, int G) { return G == 8 ? ((pos & 
 // a ghost, stay on both rows as before.
 #define N3_FLAG     0x80000000u
 #define N3_ROWSHIFT 26
+// N3: once-per-pair rule on (bx > 0); G: lanes per row of the force kernel that will walk the list (slot transposition).
+// Template parameters, so that the full-list build (LJ's default) carries none of the block arithmetic: 7.96 -> see
+// profiles/r2_experiments.md.
+template <bool N3, int G>
 __global__ void __launch_bounds__(256)
 k_nl_build(DevGeom g, real_t rc2, real_t rl2, const real4* __restrict__ rq,
            const int* __restrict__ cell, const unsigned char* __restrict__ cellType, const int* __restrict__ cellStart,
            int* __restrict__ cnt, int* __restrict__ list, int* __restrict__ count, int stride, long rows,
            real_t* __restrict__ lx, real_t* __restrict__ ly, real_t* __restrict__ lz, unsigned long long* __restrict__ stat,
-           int bx, int by, int bz, int G)
+           int bx, int by, int bz)
 {
    __shared__ int farBuf[8][4][NL_FARCAP];
    const unsigned full = 0xffffffffu;
@@ -62,10 +66,11 @@ k_nl_build(DevGeom g, real_t rc2, real_t rl2, const real4* __restrict__ rq,
       const int i0 = act ? i : 0;                      // a lane without a candidate re-reads its own atom
       if (act) pi = rq[i];
       // block membership of the 27 stencil cells relative to the atom's own cell (N3)
-      int cx = 0, cy = 0, cz = 0, xSame = 0;
-      if (bx > 0 && act)
+      int cx = 0, cy = 0, cz = 0, xSame = 0, ry = 0, rz = 0;      // ry, rz: the cell's (y, z) position inside its work block
+      if (N3 && act)
       {
          cx = c % g.P[0] - 1; cy = (c / g.P[0]) % g.P[1] - 1; cz = c / rowZ - 1;
+         ry = cy % by; rz = cz % bz;
          for (int dxc = -1; dxc <= 1; ++dxc)
          {
             const int x = cx + dxc;
@@ -77,19 +82,26 @@ k_nl_build(DevGeom g, real_t rc2, real_t rl2, const real4* __restrict__ rq,
       #pragma unroll 1
       for (int r = 0; r < 9; ++r)
       {
-         int jb = 0, je = 0, b1 = 0, b2 = 0;
+         int jb = 0, je = 0;
+         int sameLo = 0; unsigned sameLen = 0;           // [sameLo, sameLo + sameLen): the candidates of this row that share the atom's work block
          unsigned tag = 0; bool rowSame = false;
          if (act)
          {
-            const int rc = c + ((r % 3) - 1) * rowY + ((r / 3) - 1) * rowZ;
+            const int dyr = (r % 3) - 1, dzr = (r / 3) - 1;
+            const int rc = c + dyr * rowY + dzr * rowZ;
             jb = cellStart[rc - 1]; je = cellStart[rc + 2];
-            if (bx > 0)
+            if (N3)
             {
-               const int y = cy + (r % 3) - 1, z = cz + (r / 3) - 1;
-               rowSame = y >= 0 && y < g.n[1] && z >= 0 && z < g.n[2] && y / by == cy / by && z / bz == cz / bz;
+               // same block in y and z: the neighbour row stays inside the domain and inside the block (no division per row)
+               rowSame = (unsigned)(cy + dyr) < (unsigned)g.n[1] && (unsigned)(cz + dzr) < (unsigned)g.n[2]
+                      && (unsigned)(ry + dyr) < (unsigned)by && (unsigned)(rz + dzr) < (unsigned)bz;
                if (rowSame)
                {
-                  b1 = cellStart[rc]; b2 = cellStart[rc + 1]; tag = N3_FLAG | (unsigned)((y % by) + by * (z % bz)) << N3_ROWSHIFT;
+                  const int b1 = cellStart[rc], b2 = cellStart[rc + 1];
+                  tag = N3_FLAG | (unsigned)((ry + dyr) + by * (rz + dzr)) << N3_ROWSHIFT;
+                  // the in-block cells of a row are adjacent (the atom's own x cell is always one of them): one index range
+                  sameLo = (xSame & 1) ? jb : ((xSame & 2) ? b1 : b2);
+                  sameLen = (unsigned)(((xSame & 4) ? je : ((xSame & 2) ? b2 : b1)) - sameLo);
                   // Candidates that would only be skipped (same block, lower index: the pair lives on the other row) are
                   // cut out of the sweep where they form one end of the run: a lower stencil row of the same block keeps
                   // just its out-of-block cell, the atom's own row starts behind the atom when its x-1 cell is in the block.
@@ -115,13 +127,8 @@ k_nl_build(DevGeom g, real_t rc2, real_t rl2, const real4* __restrict__ rq,
             {
                const int j = jb + base + u * NL_G + gl;
                ok[u] = j < je && j != i;
-               both[u] = false;
-               if (rowSame && ok[u])
-               {  // same block iff the candidate's x cell is (row and block in y,z already are)
-                  const int xs = j < b1 ? 1 : (j < b2 ? 2 : 4);
-                  both[u] = (xSame & xs) != 0;
-                  if (both[u] && j < i) ok[u] = false;             // stored on row j
-               }
+               both[u] = N3 && (unsigned)(j - sameLo) < sameLen;   // same block iff the candidate's x cell is (row and block in y, z already are)
+               if (both[u] && j < i) ok[u] = false;                // stored on row j
                pj[u] = rq[ok[u] ? j : i0];
             }
             #pragma unroll
@@ -288,9 +295,11 @@ int comdNeighborBuildIfNeeded(ComdDev* d)
    if (n3 && d->cap > (1L << N3_ROWSHIFT)) { comdSetError("neighbour list: more than %ld atoms per GPU", 1L << N3_ROWSHIFT); return COMD_E_CAPACITY; }
    d->nlN3Shape[0] = n3 ? B.bx : 0; d->nlN3Shape[1] = n3 ? B.by : 0; d->nlN3Shape[2] = n3 ? B.bz : 0;
    d->nlLanes = n3 && d->optNlLanes != 8 ? 4 : 8;
-   k_nl_build<<<gridFor((n + 3) / 4, 8, 148 * 8), 256, 0, s>>>(d->g, d->cutoff * d->cutoff, rl * rl, d->A.rq, d->A.cell, d->cellType,
-      d->cellStart, d->cnt, d->nlList, d->nlCount, d->nlStride, d->nlRows, d->nlLastR[0], d->nlLastR[1], d->nlLastR[2], d->nlStat,
-      d->nlN3Shape[0], d->nlN3Shape[1], d->nlN3Shape[2], d->nlLanes);
+#define NL_BUILD(N3F, GG) k_nl_build<N3F, GG><<<gridFor((n + 3) / 4, 8, 148 * 8), 256, 0, s>>>(d->g, d->cutoff * d->cutoff, rl * rl, d->A.rq, d->A.cell, d->cellType, \
+      d->cellStart, d->cnt, d->nlList, d->nlCount, d->nlStride, d->nlRows, d->nlLastR[0], d->nlLastR[1], d->nlLastR[2], d->nlStat, \
+      d->nlN3Shape[0], d->nlN3Shape[1], d->nlN3Shape[2])
+   if (!n3) NL_BUILD(false, 8); else if (d->nlLanes == 4) NL_BUILD(true, 4); else NL_BUILD(true, 8);
+#undef NL_BUILD
    LAUNCH_CHECK(d);
    d->nlValid = 1;
    d->nlBuilds++;
