@@ -1,5 +1,5 @@
 #!/bin/bash
-# compute-sanitizer over the small smoke problem (EAM Cu_u6 6^3, both force paths, 5 steps each): memcheck for
+# compute-sanitizer over a small problem (EAM Cu_u6 6^3, all three force paths): memcheck for
 # out-of-bounds / misaligned accesses, racecheck for shared-memory hazards (the block-wide quad counter, the row table and
 # the fixed-point accumulators of force_n3.cuh; the chunk table of force_nl.cuh), synccheck for barrier misuse.
 # The reference's counterpart is its DEBUG build (Makefile:18-20, CUDA_GET_LAST_ERROR gpu_utility.h:102-133).
@@ -9,10 +9,13 @@ OUT=${1:-gpurun_out}
 mkdir -p "$OUT"
 rc=0
 for tool in memcheck racecheck synccheck; do
-  for n3 in 1 0; do
-    echo "== compute-sanitizer --tool $tool, COMD_NL_N3=$n3" | tee -a "$OUT/r2_sanitizer_$tool.txt"
-    COMD_NL_N3=$n3 timeout 1200 compute-sanitizer --tool $tool --error-exitcode 9 --print-limit 20 \
-      python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | grep -v "^$" | tail -25 | tee -a "$OUT/r2_sanitizer_$tool.txt"
+  # link-cell kernels (TMA-staged tiles), once-per-pair list kernels (shared-memory accumulators), full-list kernels (chunk table);
+  # 5 force calls + 12 time steps of EAM Cu_u6 6^3 each, the last ones replayed from the CUDA graph
+  for path in "0 " "1 nl_n3=1,graph_step=1" "1 nl_n3=0"; do
+    set -- $path
+    echo "== compute-sanitizer --tool $tool, COMD_NL=$1 COMD_OPTS=${2:-}" | tee -a "$OUT/r2_sanitizer_$tool.txt"
+    COMD_NL=$1 COMD_OPTS=${2:-} timeout 1200 compute-sanitizer --tool $tool --error-exitcode 9 --print-limit 20 \
+      python tools/prof_force.py funcfl 6 5 12 2>&1 | grep -v "^$" | tail -12 | tee -a "$OUT/r2_sanitizer_$tool.txt"
     [ ${PIPESTATUS[0]} -ne 0 ] && rc=1
   done
 done
