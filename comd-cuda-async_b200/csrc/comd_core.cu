@@ -491,6 +491,7 @@ extern "C" int comd_dev_create(ComdDev** out, int deviceId, const ComdGeometry* 
       d->optOverlapMode = 1;
       CUDA_TRY(cudaEventCreateWithFlags(&d->evFlag, cudaEventDisableTiming));
       d->optNlSpeculate = 1;
+      d->optTileHits = 1;
       d->optGraph = -1;
       d->xs = d->stream; d->optOverlap = 1; d->phStep = -1;
       d->e2eSpecArmed = 0;             // opt-in (option e2e_speculate): it only pays when the caller hands back bit-identical buffers
@@ -1075,6 +1076,7 @@ extern "C" int comd_dev_set_option(ComdDev* d, const char* key, long value)
       d->optNlBlock[0] = bx; d->optNlBlock[1] = by; d->optNlBlock[2] = bz;
       if (comdNlN3(d)) d->nlValid = 0;              // in-block pairs are stored once: the list is tied to the block shape
       return COMD_OK; }
+   if (!strcmp(key, "tile_hits")) { d->optTileHits = value != 0; return COMD_OK; }
    if (!strcmp(key, "tile_tx")) { if (value < 1 || value > 16) { comdSetError("tile_tx: 1..16"); return COMD_E_ARG; } d->optTileTx = (int)value; return COMD_OK; }
    comdSetError("comd_dev_set_option: unknown key '%s'", key);
    return COMD_E_ARG;

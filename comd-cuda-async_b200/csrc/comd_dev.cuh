@@ -196,6 +196,7 @@ struct ComdDev
    // tuning knobs (comd_dev_set_option)
    int optForceVariant;         // 0 = thread-per-atom stencil loop (v1), 1 = tiled TMA/filter/process engine
    int optTileTx;               // target cells per tile along x
+   int optTileHits;             // link-cell EAM: pass 1 writes the step's hit list, the list kernel does the pair forces (default 1)
    int posDirty;                // positions moved since the FP32 shadow was written
    int tileSmemSet[4];
    int hAtomCnt[12], hFpCnt[12], fpCntValid;   // host copies of the last message sizes (send 6 | recv 6); F' cache validity per axis
@@ -296,7 +297,7 @@ static inline int gridFor(long n, int block, int maxBlocks = 148 * 16)
 }
 
 // once-per-pair list kernels for this potential?  LJ pair terms are cheaper than the scatter, so "auto" keeps its full list
-static inline bool comdNlN3(const ComdDev* d) { return d->optNlN3 < 0 ? d->potKind == 2 : d->optNlN3 != 0; }
+static inline bool comdNlN3(const ComdDev* d) { return d->useNL && (d->optNlN3 < 0 ? d->potKind == 2 : d->optNlN3 != 0); }
 
 // implemented across the translation units
 int comdForceLJ(ComdDev* d);
@@ -305,6 +306,7 @@ int comdForceEAM(ComdDev* d);
 int comdFprimeHalo(ComdDev* d);
 int comdHaloRunLayout(ComdDev* d, cudaStream_t s);      // force_eam.cu: run starts/offsets/sizes of the six one-plane halo messages
 int comdNeighborBuildIfNeeded(ComdDev* d);
+int comdNeighborAllocate(ComdDev* d);
 int comdCheckErrors(ComdDev* d, const char* where);
 int comdExchangeAtomsPhase(ComdDev* d, int axis);       // comm.cu: moves send buffers to recv buffers (self or NCCL)
 int comdExchangeFprimePhase(ComdDev* d, int axis);

@@ -232,7 +232,7 @@ int comdFprimeHalo(ComdDev* d)
       rc = comdExchangeFprimePhase(d, ax);
       if (rc != COMD_OK) return rc;
       k_fp_unpack<<<grid, 256, 0, s>>>(g, ax, d->runOff, runStride, d->dfEmbed, d->fpRecv[0], d->fpRecv[1],
-                                       d->cnt + C_FPGOT0 + 2 * ax, d->cnt + C_FPGOT0 + 2 * ax + 1, d->cnt, d->useNL ? d->A.rq : nullptr); LAUNCH_CHECK(d);
+                                       d->cnt + C_FPGOT0 + 2 * ax, d->cnt + C_FPGOT0 + 2 * ax + 1, d->cnt, (d->useNL || (d->optForceVariant == 1 && d->optTileHits)) ? d->A.rq : nullptr); LAUNCH_CHECK(d);
    }
    return COMD_OK;
 }
@@ -285,6 +285,21 @@ int comdForceEAM(ComdDev* d)
       return d->wantEnergy ? launchForceNLSplit<PK_EAMFE>(d, Q, d->evFp) : launchForceNLSplit<PK_EAMF>(d, Q, d->evFp);
    }
    d->eValid = 1;
+   if (d->optForceVariant == 1 && d->optTileHits)
+   {  // Link-cell path, hits written once: the tiled engine runs the 27-cell stencil for the density pass alone (TMA-staged rows,
+      // FP32 filter, compaction, exact FP64 test) and writes every pair it found inside the cutoff to a per-step hit list; after the
+      // F' halo the list kernel evaluates all pair forces from those hits instead of a second sweep over the 513 stencil candidates
+      // per atom (round 1 ran the tiled engine twice: C3 2.29 -> see profiles/r2_experiments.md).  Same arithmetic as the list path
+      // (eam.c:311-345 and :390-409 regrouped as PK_RHO / PK_EAMF), the cells are still re-binned every step.
+      int rc = comdNeighborAllocate(d);
+      if (rc != COMD_OK) return rc;
+      d->eValid = d->wantEnergy;
+      rc = launchForceTile<PK_RHOL>(d, Q, nullptr);
+      if (rc != COMD_OK) return rc;
+      rc = comdFprimeHalo(d);
+      if (rc != COMD_OK) return rc;
+      return d->wantEnergy ? launchForceNL<PK_EAMFE>(d, Q) : launchForceNL<PK_EAMF>(d, Q);
+   }
    if (d->optForceVariant == 1)
    {
       int rc = launchForceTile<PK_EAM1>(d, Q, nullptr);

@@ -43,6 +43,7 @@ struct TileHdr
    int cs[9][FT_TXMAX + 3];           // shared index of every cell start of the row
    int iBeg, iEnd;                    // global range of the tile's own atoms
    int total;
+   int rowDelta[9];                   // global index - shared index of the atoms of each row (PK_RHOL: hits leave as global indices)
 };
 static_assert(sizeof(TileHdr) <= FT_HDR, "TileHdr");
 
@@ -50,6 +51,8 @@ static_assert(sizeof(TileHdr) <= FT_HDR, "TileHdr");
 #define PK_LJ   0
 #define PK_EAM1 1
 #define PK_EAM3 3
+#define PK_RHOL 8                     // link-cell EAM pass 1 that also writes the step's hit list: rhobar + F, F' here, every pair
+                                      // force in the list kernel k_force_nl<PK_EAMF|PK_EAMFE> that walks those hits (force_eam.cu)
 
 struct PairParams
 {
@@ -183,6 +186,15 @@ __device__ __forceinline__ void pairEval(const PairParams& P, real_t dx, real_t 
       acc[3] += R(0.5) * phi;
       acc[4] += rho;
    }
+   else if (KIND == PK_RHOL)
+   {  // eam.c:331-343, the density alone (value part of interpolate(), eam.c:557-579)
+      const real_t r = r2 * rsqrt(r2);
+      real_t t;
+      const real_t* __restrict__ v = P.tRho.v + tableIndex(P.tRho, r, t);
+      real_t rho;
+      interpValue(__ldg(v - 1), __ldg(v), __ldg(v + 1), t, rho);
+      acc[0] += rho;
+   }
    else
    {  // eam.c:390-409
       const real_t rinv = rsqrt(r2);
@@ -205,7 +217,11 @@ __device__ __forceinline__ void pairEval(const PairParams& P, real_t dx, real_t 
    }
 }
 
-template <int KIND> struct PairTraits { static constexpr int NACC = KIND == PK_LJ ? 4 : (KIND == PK_EAM1 ? 5 : 3); };
+template <int KIND> struct PairTraits { static constexpr int NACC = KIND == PK_LJ ? 4 : (KIND == PK_EAM1 ? 5 : (KIND == PK_RHOL ? 1 : 3)); };
+
+// hit list of PK_RHOL: the full-list row format of neighbor.cu (chunks of 32 entries, entry 8u+l stored at 4l+u)
+struct TileHits { int* list; int* count; int* countHit; int stride; };
+__device__ __forceinline__ int tileSlot(int pos) { return (pos & ~31) | ((pos & 7) << 2) | ((pos >> 3) & 3); }
 
 // elements of a per-atom array in 16 bytes: TMA bulk copies start and end on such boundaries
 #define FT_AL ((int)(16 / sizeof(real_t)))
@@ -227,7 +243,7 @@ template <int KIND>
 __device__ __forceinline__ void processQueues(const PairParams& P, unsigned short* myQ, unsigned short* myD, int& qn,
                                               int gl, int si, real_t xi, real_t yi, real_t zi, real_t dfi,
                                               const real_t* sx, const real_t* sy, const real_t* sz, const real_t* sdf,
-                                              real_t* acc)
+                                              real_t* acc, const TileHdr& H, int* hitRow, int hitStride, int& nHit)
 {
    const unsigned full = 0xffffffffu;
    int incl = qn;
@@ -241,6 +257,7 @@ __device__ __forceinline__ void processQueues(const PairParams& P, unsigned shor
    for (int rd = 0; rd < rounds; ++rd)
    {
       const int k = rd * FT_G + gl;
+      bool hit = false; int jHit = 0;
       if (k < total)
       {
          const int j = myD[k];
@@ -248,6 +265,22 @@ __device__ __forceinline__ void processQueues(const PairParams& P, unsigned shor
          const real_t r2 = dx * dx + dy * dy + dz * dz;
          const bool in = (KIND == PK_EAM3) ? (r2 < P.rc2) : (r2 <= P.rc2);     // eam.c:317 vs :397
          if (in && j != si) pairEval<KIND>(P, dx, dy, dz, r2, dfi, KIND == PK_EAM3 ? sdf[j] : R(0.0), acc);
+         hit = in && j != si;
+         jHit = j;
+      }
+      if (KIND == PK_RHOL)
+      {  // the pair leaves as an entry of atom i's row: position among the 8 lanes of the atom by ballot, the neighbour as a
+         // global index (the staged rows are straight copies: one offset per stencil row)
+         const unsigned m = (__ballot_sync(full, hit) >> ((threadIdx.x & 31) / FT_G * FT_G)) & ((1u << FT_G) - 1u);
+         if (hit)
+         {
+            int r = 0;
+            #pragma unroll
+            for (int q = 1; q < 9; ++q) r += jHit >= H.rowS[q];
+            const int pos = nHit + __popc(m & ((1u << gl) - 1u));
+            if (pos < hitStride) hitRow[tileSlot(pos)] = jHit + H.rowDelta[r];
+         }
+         nHit += __popc(m);
       }
    }
    __syncwarp();
@@ -261,7 +294,7 @@ k_force_tile(DevGeom g, TileCfg cfg, PairParams P,
              const float4* __restrict__ rf, const int* __restrict__ cell, const int* __restrict__ cellStart,
              const real_t* __restrict__ dfIn,
              real_t* __restrict__ fx, real_t* __restrict__ fy, real_t* __restrict__ fz, real_t* __restrict__ e,
-             real_t* __restrict__ rhobar, real_t* __restrict__ dfOut, int* __restrict__ cnt)
+             real_t* __restrict__ rhobar, real_t* __restrict__ dfOut, int* __restrict__ cnt, TileHits hits, real4* __restrict__ rqOut)
 {
    extern __shared__ __align__(128) unsigned char smem[];
    constexpr int NACC = PairTraits<KIND>::NACC;
@@ -301,7 +334,7 @@ k_force_tile(DevGeom g, TileCfg cfg, PairParams P,
       for (int o = 1; o < 16; o <<= 1) { const int u = __shfl_up_sync(full, incl, o); if (lane >= o) incl += u; }
       const int excl = incl - cntR;
       const int total = __shfl_sync(full, incl, 8);
-      if (lane < 9) { H.rowGA[lane] = ga; H.rowS[lane] = excl; }
+      if (lane < 9) { H.rowGA[lane] = ga; H.rowS[lane] = excl; H.rowDelta[lane] = ga - excl; }
       if (lane == 0) { H.total = total; H.iBeg = H.cs[4][1]; H.iEnd = H.cs[4][Tx + 1]; }
       if (total <= sMax)
       {
@@ -358,7 +391,8 @@ k_force_tile(DevGeom g, TileCfg cfg, PairParams P,
          if (KIND == PK_EAM3) dfi = sdf[si];
       }
       real_t acc[5] = { R(0.0), R(0.0), R(0.0), R(0.0), R(0.0) };
-      int qn = 0;
+      int qn = 0, nHit = 0;
+      int* hitRow = KIND == PK_RHOL ? hits.list + (long)(act ? iBeg + il : iBeg) * hits.stride : nullptr;
       #pragma unroll 1
       for (int r = 0; r < 9; ++r)
       {
@@ -369,7 +403,7 @@ k_force_tile(DevGeom g, TileCfg cfg, PairParams P,
          for (int base = 0; base < maxlen; base += FT_G * FT_CH)
          {
             if (__any_sync(full, qn > FT_QCAP - FT_CH))
-               processQueues<KIND>(P, myQ, myD, qn, gl, si, xi, yi, zi, dfi, sx, sy, sz, sdf, acc);
+               processQueues<KIND>(P, myQ, myD, qn, gl, si, xi, yi, zi, dfi, sx, sy, sz, sdf, acc, H, hitRow, hits.stride, nHit);
             const int left = (maxlen - base + FT_G - 1) / FT_G;
             const int itEnd = left < FT_CH ? left : FT_CH;
             int k = jb + base + gl;
@@ -385,7 +419,7 @@ k_force_tile(DevGeom g, TileCfg cfg, PairParams P,
             }
          }
       }
-      processQueues<KIND>(P, myQ, myD, qn, gl, si, xi, yi, zi, dfi, sx, sy, sz, sdf, acc);
+      processQueues<KIND>(P, myQ, myD, qn, gl, si, xi, yi, zi, dfi, sx, sy, sz, sdf, acc, H, hitRow, hits.stride, nHit);
       #pragma unroll
       for (int a = 0; a < NACC; ++a)
       {
@@ -408,6 +442,18 @@ k_force_tile(DevGeom g, TileCfg cfg, PairParams P,
             e[i] = acc[3] + fe;
             rhobar[i] = acc[4];
             dfOut[i] = dfe;
+         }
+         else if (KIND == PK_RHOL)
+         {
+            real_t fe, dfe;
+            tableLookupFull(P.tF, acc[0], fe, dfe);            // eam.c:352-371 (pass 2 fused)
+            e[i] = fe;                                         // U_i = F(rhobar_i); the pair energies join in k_force_nl<PK_EAMFE>
+            rhobar[i] = acc[0];
+            dfOut[i] = dfe;
+            rqOut[i].w = dfe;                                  // the copy the list kernel gathers
+            hits.count[i] = nHit <= hits.stride ? nHit : 0;
+            hits.countHit[i] = nHit <= hits.stride ? nHit : 0;
+            if (nHit > hits.stride) atomicOr(&cnt[C_ERR], ERRB_NLFULL);
          }
          else
          {
@@ -453,7 +499,8 @@ static int launchForceTile(ComdDev* d, PairParams P, const real_t* dfIn)
    const double rc = sqrt(P.rc2);
    const double rcf = rc + 4.0 * sqrt(3.0) * ext * ldexp(1.0, -24);       // FP32 rounding of both shadow positions, doubled
    cfg.rcf2 = nextafterf((float)(rcf * rcf * (1.0 + 1e-6)), INFINITY);
-   const int slot = KIND == PK_EAM3 ? 2 : KIND;
+   const int slot = KIND == PK_EAM3 ? 2 : (KIND == PK_RHOL ? 3 : KIND);
+   TileHits hits = { d->nlList, d->nlCount, d->nlCountHit, d->nlStride };
    if ((size_t)d->tileSmemSet[slot] < bytes)
    {
       CUDA_TRY(cudaFuncSetAttribute(k_force_tile<KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
@@ -461,7 +508,7 @@ static int launchForceTile(ComdDev* d, PairParams P, const real_t* dfIn)
    }
    const int grid = cfg.tilesX * g.n[1] * g.n[2];
    k_force_tile<KIND><<<grid, FT_THREADS, bytes, d->stream>>>(g, cfg, P, d->A.r[0], d->A.r[1], d->A.r[2], d->A.rf, d->A.cell,
-      d->cellStart, dfIn, d->f[0], d->f[1], d->f[2], d->e, d->rhobar, d->dfEmbed, d->cnt);
+      d->cellStart, dfIn, d->f[0], d->f[1], d->f[2], d->e, d->rhobar, d->dfEmbed, d->cnt, hits, d->A.rq);
    LAUNCH_CHECK(d);
    return COMD_OK;
 }

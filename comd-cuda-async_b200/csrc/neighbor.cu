@@ -275,6 +275,8 @@ static int nlAllocate(ComdDev* d)
    return COMD_OK;
 }
 
+int comdNeighborAllocate(ComdDev* d) { return nlAllocate(d); }      // the hit list of the link-cell EAM path lives in the same rows
+
 int comdNeighborBuildIfNeeded(ComdDev* d)
 {
    if (!d->useNL || d->nlValid) return COMD_OK;

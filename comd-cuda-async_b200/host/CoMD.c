@@ -110,8 +110,8 @@ SimFlat* initSimulation(Command cmd)
    if (printRank())
    {  /* the reference's method names select two very different kernels here: say which, and what it costs */
       if (useNL) printf("Force path: neighbour list (-m %s): once-per-pair list kernels, the fast path of this build\n", cmd.method);
-      else printf("Force path: link cells (-m %s): 27-cell stencil over TMA-staged tiles, re-binned every step; expect ~2.5-3x the step time of "
-                  "-m thread_atom_nl (measured on B200: C3 2.49 vs 0.91 ms/step, C5 41 vs 15 ms/step)\n", cmd.method);
+      else printf("Force path: link cells (-m %s): 27-cell stencil over TMA-staged tiles, re-binned every step; expect ~2.3x the step time of "
+                  "-m thread_atom_nl (measured on B200, EAM: C3 1.77 vs 0.78 ms/step, C5 30 vs 12 ms/step)\n", cmd.method);
    }
    if ((cmd.ljInterpolation || cmd.spline || cmd.usePairlist) && printRank())
       printf("Note: -I / -P / -L select experimental kernels of the reference that this build does not carry; ignored.\n");

@@ -155,6 +155,8 @@ int  comd_comm_barrier(ComdDev* dev);                               /* barrierPa
 /* ---- tuning knobs (no reference counterpart; defaults are the measured-best settings):
  *   "force_variant"      link-cell path: 1 = tiled TMA-staged filter/process kernels (default), 0 = thread-per-atom
  *                        stencil loop (the shape of LJ_Force_thread_atom, gpu_lj_thread_atom.h:31-143)
+ *   "tile_hits"          link-cell EAM path: 1 (default) the tiled density pass writes the step's hit list and the list kernel
+ *                        evaluates the pair forces from it; 0: the tiled engine sweeps the stencil twice (round 1)
  *   "tile_tx"            link-cell path: target cells per force tile along x (1..16)
  *   "energy_every_step"  list path: per-atom EAM pair energies at every step of comd_dev_timestep (default 0)
  *   "nl_n3"              list path: 1 = pairs inside a work block are stored and evaluated once, for both
