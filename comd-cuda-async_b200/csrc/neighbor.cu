@@ -415,3 +415,13 @@ extern "C" unsigned long long comd_hilbert_key(unsigned x, unsigned y, unsigned 
 {
    return bits >= 1 && bits <= 20 ? nlHilbertKey(x, y, z, bits) : 0ull;
 }
+
+// the order table the list kernels would walk for (cells, block shape, set, mode): needs no device (CPU tests)
+extern "C" int comd_block_order_table(const int cells[3], int bx, int by, int bz, int phase, int mode, int capacity, int* out)
+{
+   if (!cells || !out || bx < 1 || by < 1 || bz < 1 || phase < 0 || phase > 2 || mode < 0 || mode > 2) return COMD_E_ARG;
+   const std::vector<int> ids = nlBlockOrderTable(cells, bx, by, bz, phase, mode);
+   if ((int)ids.size() > capacity) return COMD_E_CAPACITY;
+   for (size_t k = 0; k < ids.size(); ++k) out[k] = ids[k];
+   return (int)ids.size();
+}

@@ -122,6 +122,39 @@ static inline unsigned long long nlHilbertKey(unsigned x, unsigned y, unsigned z
    return key;
 }
 
+// The order table of one set as a host vector: mode 0 the set in its own order, 1 largest block first, 2 Hilbert curve.
+// Pure host arithmetic (comd_block_order_table exposes it to the CPU tests: every set must list each of its blocks once).
+static inline std::vector<int> nlBlockOrderTable(const int cellsN[3], int bx, int by, int bz, int phase, int mode)
+{
+   NlBlocks T = {};
+   T.bx = bx; T.by = by; T.bz = bz;
+   T.nbx = (cellsN[0] + bx - 1) / bx; T.nby = (cellsN[1] + by - 1) / by; T.nbz = (cellsN[2] + bz - 1) / bz;
+   T.phase = phase;
+   const int all = T.nbx * T.nby * T.nbz, interior = nlInteriorCount(T);
+   const int n = phase == NLB_ALL ? all : (phase == NLB_INTERIOR ? interior : all - interior);
+   std::vector<int> ids(n > 0 ? n : 0);
+   if (n <= 0) return ids;
+   int bits = 1;
+   while ((1 << bits) < std::max(T.nbx, std::max(T.nby, T.nbz))) ++bits;
+   std::vector<std::pair<unsigned long long, int>> keyed(n);
+   for (int q = 0; q < n; ++q)
+   {
+      int ix, iy, iz;
+      nlBlockCoordOfSet(T, q, ix, iy, iz);
+      unsigned long long key = (unsigned long long)q;          // the set in its own order
+      if (mode == 2) key = nlHilbertKey((unsigned)ix, (unsigned)iy, (unsigned)iz, bits);
+      else if (mode == 1)
+      {  // cells of the block, descending; index order among equals
+         const int cx = std::min(bx, cellsN[0] - ix * bx), cy = std::min(by, cellsN[1] - iy * by), cz = std::min(bz, cellsN[2] - iz * bz);
+         key = ((unsigned long long)(bx * by * bz - cx * cy * cz) << 32) | (unsigned)q;
+      }
+      keyed[q] = { key, ix + T.nbx * (iy + T.nby * iz) };
+   }
+   std::sort(keyed.begin(), keyed.end());
+   for (int q = 0; q < n; ++q) ids[q] = keyed[q].second;
+   return ids;
+}
+
 // order table of one phase set (device memory, cached in the handle until the block shape or the grid changes)
 static int nlBlockOrder(ComdDev* d, NlBlocks& B, int phase, cudaStream_t s)
 {
@@ -133,7 +166,8 @@ static int nlBlockOrder(ComdDev* d, NlBlocks& B, int phase, cudaStream_t s)
    const bool split = phase != NLB_ALL && nlInteriorCount(B) > 0;        // the interior / boundary sets are not index ranges
    if (!d->optNlHilbert && !lpt && !split) return COMD_OK;
    // one cached table per set, valid while the block shape, the grid and the kind of order stay the same
-   const int sig[7] = { B.bx, B.by, B.bz, B.nbx, B.nby, B.nbz, d->optNlHilbert ? 2 : (lpt ? 1 : 0) };
+   const int mode = d->optNlHilbert ? 2 : (lpt ? 1 : 0);
+   const int sig[7] = { B.bx, B.by, B.bz, B.nbx, B.nby, B.nbz, mode };
    bool same = true;
    for (int k = 0; k < 7; ++k) same = same && d->nlOrderSig[phase][k] == sig[k];
    if (!same)
@@ -143,31 +177,10 @@ static int nlBlockOrder(ComdDev* d, NlBlocks& B, int phase, cudaStream_t s)
    }
    if (!d->nlOrder[phase])
    {
-      NlBlocks T = B; T.order = nullptr; T.phase = phase;
-      const int all = B.nbx * B.nby * B.nbz, interior = nlInteriorCount(B);
-      const int n = phase == NLB_ALL ? all : (phase == NLB_INTERIOR ? interior : all - interior);
-      if (n <= 0) return COMD_OK;
-      int bits = 1;
-      while ((1 << bits) < std::max(B.nbx, std::max(B.nby, B.nbz))) ++bits;
-      std::vector<std::pair<unsigned long long, int>> keyed(n);
-      for (int q = 0; q < n; ++q)
-      {
-         int ix, iy, iz;
-         nlBlockCoordOfSet(T, q, ix, iy, iz);
-         unsigned long long key = (unsigned long long)q;          // the set in its own order
-         if (d->optNlHilbert) key = nlHilbertKey((unsigned)ix, (unsigned)iy, (unsigned)iz, bits);
-         else if (lpt)
-         {  // cells of the block, descending; index order among equals
-            const int cx = std::min(B.bx, d->g.n[0] - ix * B.bx), cy = std::min(B.by, d->g.n[1] - iy * B.by), cz = std::min(B.bz, d->g.n[2] - iz * B.bz);
-            key = ((unsigned long long)(B.bx * B.by * B.bz - cx * cy * cz) << 32) | (unsigned)q;
-         }
-         keyed[q] = { key, ix + B.nbx * (iy + B.nby * iz) };
-      }
-      std::sort(keyed.begin(), keyed.end());
-      std::vector<int> ids(n);
-      for (int q = 0; q < n; ++q) ids[q] = keyed[q].second;
-      CUDA_TRY(cudaMalloc(&d->nlOrder[phase], n * sizeof(int)));
-      CUDA_TRY(cudaMemcpyAsync(d->nlOrder[phase], ids.data(), n * sizeof(int), cudaMemcpyHostToDevice, s));
+      const std::vector<int> ids = nlBlockOrderTable(d->g.n, B.bx, B.by, B.bz, phase, mode);
+      if (ids.empty()) return COMD_OK;
+      CUDA_TRY(cudaMalloc(&d->nlOrder[phase], ids.size() * sizeof(int)));
+      CUDA_TRY(cudaMemcpyAsync(d->nlOrder[phase], ids.data(), ids.size() * sizeof(int), cudaMemcpyHostToDevice, s));
       CUDA_TRY(cudaStreamSynchronize(s));            // ids goes out of scope; once per shape
    }
    B.order = d->nlOrder[phase];

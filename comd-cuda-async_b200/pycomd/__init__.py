@@ -52,7 +52,7 @@ ABI_SYMBOLS = [
     "comd_comm_allreduce_sum", "comd_comm_allreduce_sum_int", "comd_comm_barrier", "comd_dev_sync",
     "comd_dev_kernel_stats", "comd_dev_step_host", "comd_dev_fp64_peak", "comd_dev_timer_start", "comd_dev_timer_stop",
     "comd_dev_set_option", "comd_host_alloc", "comd_host_free", "comd_dev_step_host_stats", "comd_dev_neighbor_counters", "comd_dev_halo_bytes", "comd_precision",
-    "comd_hilbert_key", "comd_dev_fp32_peak", "comd_dev_step_stats",
+    "comd_hilbert_key", "comd_dev_fp32_peak", "comd_dev_step_stats", "comd_block_order_table",
 ]
 
 _libs = {}

@@ -207,6 +207,10 @@ int  comd_dev_fp64_peak(ComdDev* dev, double* tflops);
 int  comd_dev_fp32_peak(ComdDev* dev, double* tflops);    /* FFMA twin: the roofline denominator of the -DCOMD_SINGLE build */
 /* position of work block (x, y, z) on the 3-D Hilbert curve of order `bits` (the key option "nl_hilbert" sorts by; needs no device) */
 unsigned long long comd_hilbert_key(unsigned x, unsigned y, unsigned z, int bits);
+/* the order in which the list kernels walk the work blocks (bx*by*bz link cells each) of a domain of cells[3] link cells: set 0 all
+ * blocks, 1 interior (no ghost neighbour), 2 boundary shell; mode 0 the set's own order, 1 largest block first, 2 Hilbert curve.
+ * Writes linear block ids (x fastest) to out, returns their number or a negative COMD_E_*; needs no device */
+int  comd_block_order_table(const int cells[3], int bx, int by, int bz, int set, int mode, int capacity, int* out);
 /* End-to-end step through HOST buffers (bench.py `e2e`): one full timestep() whose inputs
  * (gid, r, p, f at time t; SoA, any order, all local to this rank) start in host memory and
  * whose results (gid, r, p, f, U at t+dt, in device order, *nOut of them) end there.

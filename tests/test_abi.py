@@ -3,6 +3,8 @@ import ctypes
 import os
 import re
 
+import pytest
+
 import pycomd
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -88,3 +90,35 @@ def test_hilbert_key_walks_the_cube_through_face_neighbours():
         path = [cells[k] for k in range(n ** 3)]
         for a, b in zip(path, path[1:]):
             assert sum(abs(p - q) for p, q in zip(a, b)) == 1, (bits, a, b)
+
+
+@pytest.mark.parametrize("cells,block", [((47, 47, 47), (4, 4, 2)), ((95, 95, 95), (4, 4, 4)), ((13, 9, 6), (4, 4, 4)), ((7, 7, 7), (2, 2, 1)), ((5, 3, 3), (4, 4, 4))])
+def test_work_block_sets_list_every_block_exactly_once(cells, block):
+    """What the list kernels walk (nl_blocks.cuh): in every order (the set's own, largest block first, Hilbert curve) the set of
+    all blocks is a permutation of 0 .. n-1, interior and boundary shell partition it, the interior holds exactly the blocks that
+    touch no face of the domain, and largest-first really is non-increasing in cells per block."""
+    import ctypes as C
+    L = pycomd.lib()
+    nb = [(cells[a] + block[a] - 1) // block[a] for a in range(3)]
+    n = nb[0] * nb[1] * nb[2]
+    arr = (C.c_int * 3)(*cells)
+    def table(which, mode):
+        out = (C.c_int * n)()
+        m = L.comd_block_order_table(arr, block[0], block[1], block[2], which, mode, n, out)
+        assert m >= 0
+        return list(out[:m])
+    def is_interior(b):
+        ix, iy, iz = b % nb[0], (b // nb[0]) % nb[1], b // (nb[0] * nb[1])
+        return all(0 < c < m - 1 for c, m in zip((ix, iy, iz), nb))
+    def size(b):
+        ix, iy, iz = b % nb[0], (b // nb[0]) % nb[1], b // (nb[0] * nb[1])
+        return min(block[0], cells[0] - ix * block[0]) * min(block[1], cells[1] - iy * block[1]) * min(block[2], cells[2] - iz * block[2])
+    for mode in (0, 1, 2):
+        everything, inner, shell = table(0, mode), table(1, mode), table(2, mode)
+        assert sorted(everything) == list(range(n))
+        assert sorted(inner + shell) == list(range(n))
+        assert all(is_interior(b) for b in inner) and not any(is_interior(b) for b in shell)
+        if mode == 1:
+            for t in (everything, inner, shell):
+                assert all(size(a) >= size(b) for a, b in zip(t, t[1:]))
+    assert table(0, 0) == list(range(n))
