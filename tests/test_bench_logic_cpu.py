@@ -70,3 +70,25 @@ def test_reference_arm_process_grids():
     for p in (6, 24, 48, 64):
         g = bench._ref_grid(p)
         assert g[0] * g[1] * g[2] == p
+
+
+def test_reference_arm_prints_one_contract_line(tmp_path):
+    """`bench.py --impl reference` (the arm the driver runs first): ONE JSON line with the contract's keys, the reference's own
+    CPU path (oracle/_ref, -m cpu_nl) as one job of cooperating ranks on this host's cores, zero bytes over PCIe."""
+    import json
+    import subprocess
+    if not os.path.exists(os.path.join(ROOT, "oracle", "_ref", "CoMD-ref")):
+        pytest.skip("oracle/_ref not built (needs /root/reference at build time)")
+    res = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "1", "--steps", "1", "--warmup", "1",
+                          "--workload", "eam_u6_20"], cwd=tmp_path, capture_output=True, text=True, timeout=600)
+    assert res.returncode == 0, res.stderr[-2000:]
+    lines = [ln for ln in res.stdout.splitlines() if ln.startswith("{")]
+    assert len(lines) == 1
+    j = json.loads(lines[0])
+    for key in ("impl", "metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling", "vs_baseline",
+                "dtype", "data", "config", "cpu_baseline", "e2e"):
+        assert key in j, key
+    assert j["impl"] == "reference" and j["unit"] == "atom-steps/s" and j["higher_is_better"] is True and j["value"] > 1e5
+    assert j["cpu_baseline"]["kind"] == "reference" and j["cpu_baseline"]["cores"] >= 1 and "cooperating ranks" in j["cpu_baseline"]["sample"]
+    assert j["e2e"] == {"value": j["value"], "unit": "atom-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    assert "workload" in j["config"] and "model" not in j["config"]
