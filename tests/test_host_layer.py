@@ -170,3 +170,30 @@ def test_driver_refuses_to_run_without_a_gpu_and_keeps_the_option_table(tools, t
     if not gpu_available:
         res = subprocess.run([tools["CoMD-b200"], "-x", "6", "-y", "6", "-z", "6"], cwd=tmp_path, capture_output=True, text=True)
         assert res.returncode != 0 and "no CUDA device" in res.stderr      # fails loudly, no CPU fallback
+
+
+@pytest.mark.parametrize("args", [["-e", "-x", "6", "-y", "6", "-z", "6", "-N", "10", "-n", "5"],
+                                  ["-x", "8", "-y", "6", "-z", "6", "-T", "450", "-r", "0.05", "-D", "2.0", "-l", "3.7"],
+                                  ["-e", "-t", "setfl", "-p", "Cu01.eam.alloy", "-x", "6", "-y", "6", "-z", "6", "-H", "1", "-a", "1"]])
+def test_command_line_block_is_the_references_text(tools, tmp_path, args, gpu_available):
+    """north_star: "the same command-line options and YAML output".  The block both drivers print (and write to their YAML
+    report) right after parsing -- option names, order, units, number formatting (mycommand.c:262-320) -- is compared line by
+    line between CoMD-b200 and the reference executable for the same arguments; only the value of `GPU method` may differ
+    (the reference needs -m cpu_nl to run here).  Works without a device: the block is out before the device is created."""
+    ref = os.path.join(ROOT, "oracle", "_ref", "CoMD-ref")
+    if not os.path.exists(ref):
+        pytest.skip("oracle/_ref/CoMD-ref not built (needs /root/reference at build time)")
+    def block(exe, extra):
+        res = subprocess.run([exe] + args + ["-d", POTS] + extra, cwd=tmp_path, capture_output=True, text=True, timeout=300)
+        out = res.stdout
+        a = out.index("Command Line Parameters:")
+        b = out.index("Space-filling (Hilbert)", a)
+        return out[a:out.index("\n", b)].splitlines()
+    ours = block(tools["CoMD-b200"], [])
+    theirs = block(ref, ["-m", "cpu_nl"])
+    assert len(ours) == len(theirs) > 15
+    for x, y in zip(ours, theirs):
+        if x.strip().startswith("GPU method"):
+            assert x.split(":")[0] == y.split(":")[0]
+            continue
+        assert x == y, (x, y)
