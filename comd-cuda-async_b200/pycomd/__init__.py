@@ -53,6 +53,7 @@ ABI_SYMBOLS = [
     "comd_dev_kernel_stats", "comd_dev_step_host", "comd_dev_fp64_peak", "comd_dev_timer_start", "comd_dev_timer_stop",
     "comd_dev_set_option", "comd_host_alloc", "comd_host_free", "comd_dev_step_host_stats", "comd_dev_neighbor_counters", "comd_dev_halo_bytes", "comd_precision",
     "comd_hilbert_key", "comd_dev_fp32_peak", "comd_dev_step_stats", "comd_block_order_table",
+    "comd_energy_sums_static",
 ]
 
 _libs = {}
@@ -110,6 +111,8 @@ def lib(precision="f64"):
         L.comd_host_alloc.argtypes = [C.POINTER(C.c_void_p), C.c_size_t]
         L.comd_host_free.argtypes = [C.c_void_p]
         L.comd_dev_step_host_stats.argtypes = [C.c_void_p, C.POINTER(C.c_long)]
+        # device pointers travel as integers (tensor.data_ptr()), the stream as a cudaStream_t value
+        L.comd_energy_sums_static.argtypes = [C.c_int, C.c_void_p, C.c_long, C.c_double] + [C.c_void_p] * 5
         _libs[precision] = L
     return _libs[precision]
 

@@ -232,6 +232,32 @@ int  comd_dev_step_host(ComdDev* dev, int nLocal, double dt,
  * (in-place update); a result buffer over the input of ANOTHER quantity switches the early start off. */
 int  comd_dev_step_host_stats(ComdDev* dev, long* nResumed);
 
+/* ---- energy sums without any device allocation.  No counterpart in the reference (its ReduceEnergy,
+ * gpu_reduce.h:32-98, always works on the slabs AllocateGpu made).
+ * Every other entry point needs a ComdDev, and comd_dev_create() builds one out of cudaMalloc calls.  That shuts
+ * out callers that must not, or cannot, allocate on the device: a diagnostics hook invoked inside a running
+ * time-step loop (cudaMalloc and cudaFree wait for the whole GPU and would serialise the halo/compute overlap),
+ * and a host that has already given all of HBM to its own arena or caching allocator, underneath which a
+ * library's cudaMalloc may just fail.  Such a caller owns its per-atom arrays; this call needs nothing else.
+ *   U, px, py, pz : DEVICE pointers, nAtoms entries each -- per-atom potential energy and momentum of the atoms
+ *                   to be summed (pass local atoms only; there is no ghost filter here)
+ *   eOut          : DEVICE pointer to 2 doubles: eOut[0] = sum U, eOut[1] = sum |p|^2 / (2 mass), the two
+ *                   values comd_dev_energy() returns, summed in double in both precision builds
+ *   stream        : a cudaStream_t (NULL = the default stream).  The two kernels are enqueued there and the
+ *                   call returns without waiting; eOut is valid once that stream has reached them.
+ * The block partials between the two reduction levels sit in a fixed 256 KB __device__ array inside the library
+ * (each GPU that loads the library holds it until the process ends), sized for COMD_ENERGY_STATIC_MAX_ATOMS
+ * atoms: a larger nAtoms returns COMD_E_ARG and launches nothing.  The call itself uses no cudaMalloc, cudaFree
+ * or other allocating routine.  All calls of a process on one GPU share that array: back-to-back calls on one
+ * stream are fine, calls that can overlap on the GPU (different streams) race and must be ordered by the caller.
+ * Nothing in the array needs clearing between calls -- each call overwrites every slot it reads.
+ * The FIRST call on each GPU also resolves the array's device address (cudaGetSymbolAddress, which loads the
+ * module there): make that call once during set-up, before any stream capture begins. */
+#define COMD_ENERGY_STATIC_MAX_ATOMS 67108864L      /* 16384 tiles of 4096 atoms */
+int  comd_energy_sums_static(int deviceId, void* stream, long nAtoms, double mass,
+                             const comd_real* U, const comd_real* px, const comd_real* py, const comd_real* pz,
+                             double* eOut);
+
 #ifdef __cplusplus
 }
 #endif
