@@ -363,7 +363,11 @@ int main(int argc, char** argv)
          if (r2 <= rc * rc) ++nNbr;
       }
       double peak = 0.0;
+#ifdef COMD_SINGLE
+      DEV_TRY(comd_dev_fp32_peak(sim->dev, &peak));      /* real_t = float: the FFMA pipe is the one the forces run on */
+#else
       DEV_TRY(comd_dev_fp64_peak(sim->dev, &peak));
+#endif
       setRooflineInfo(cmd.doeam ? 93.0 * nNbr + 42.0 : 27.0 * nNbr + 22.0, peak, getNRanks());
    }
    printPerformanceResults(sim->atoms->nGlobal, sim->printRate);

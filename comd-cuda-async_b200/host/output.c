@@ -13,6 +13,15 @@
 #include <time.h>
 #include <unistd.h>
 
+/* the pipe the roofline lines are quoted against: CoMD.c measures the FFMA peak in the real_t = float build, the DFMA peak otherwise */
+#ifdef COMD_SINGLE
+#define COMD_FP_NAME  "FP32"
+#define COMD_FMA_NAME "FFMA"
+#else
+#define COMD_FP_NAME  "FP64"
+#define COMD_FMA_NAME "DFMA"
+#endif
+
 #ifndef COMD_VARIANT
 #define COMD_VARIANT "CoMD-b200"
 #endif
@@ -131,8 +140,8 @@ void printPerformanceResults(int nGlobalAtoms, int printRate)
    if (perfGlobal.fp64PeakTflops > 0.0)
    {
       const double tf = perfGlobal.atomsPerUSec * 1e6 * perfGlobal.flopPerAtomStep * 1e-12;
-      fprintf(screenOut, " FP64 roofline:                %.3f TFLOP/s algorithmic (%.0f flop/atom-step) of %.2f TFLOP/s measured DFMA peak on %d GPU%s = %.4f\n\n",
-              tf, perfGlobal.flopPerAtomStep, perfGlobal.fp64PeakTflops * perfGlobal.nRanks, perfGlobal.nRanks, perfGlobal.nRanks > 1 ? "s" : "",
+      fprintf(screenOut, " %s roofline:                %.3f TFLOP/s algorithmic (%.0f flop/atom-step) of %.2f TFLOP/s measured %s peak on %d GPU%s = %.4f\n\n",
+              COMD_FP_NAME, tf, perfGlobal.flopPerAtomStep, perfGlobal.fp64PeakTflops * perfGlobal.nRanks, COMD_FMA_NAME, perfGlobal.nRanks, perfGlobal.nRanks > 1 ? "s" : "",
               tf / (perfGlobal.fp64PeakTflops * perfGlobal.nRanks));
    }
 }
@@ -176,7 +185,7 @@ void printPerformanceResultsYaml(FILE* file)
    if (perfGlobal.fp64PeakTflops > 0.0)
    {
       const double tf = perfGlobal.atomsPerUSec * 1e6 * perfGlobal.flopPerAtomStep * 1e-12;
-      fprintf(file, "  RooflineFP64:\n    AlgorithmicFlopPerAtomStep: %.0f\n    AchievedTFlops: %.4f\n    MeasuredPeakTFlopsPerGpu: %.3f\n    Gpus: %d\n    Fraction: %.4f\n",
+      fprintf(file, "  Roofline" COMD_FP_NAME ":\n    AlgorithmicFlopPerAtomStep: %.0f\n    AchievedTFlops: %.4f\n    MeasuredPeakTFlopsPerGpu: %.3f\n    Gpus: %d\n    Fraction: %.4f\n",
               perfGlobal.flopPerAtomStep, tf, perfGlobal.fp64PeakTflops, perfGlobal.nRanks, tf / (perfGlobal.fp64PeakTflops * perfGlobal.nRanks));
    }
    fprintf(file, "\n");
