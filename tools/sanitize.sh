@@ -5,6 +5,14 @@
 # The reference's counterpart is its DEBUG build (Makefile:18-20, CUDA_GET_LAST_ERROR gpu_utility.h:102-133).
 # usage (on a GPU box): bash tools/sanitize.sh [out_dir]      -> <out_dir>/r2_sanitizer_{memcheck,racecheck,synccheck}.txt
 set -u
+# The shared B200 pool does not allow compute-sanitizer (profiles/r2_sanitizer_note.txt: runs under it have left GPUs needing
+# a reset).  This script therefore refuses to start unless the caller states that the GPU is their own.
+if [ "${COMD_SANITIZE_OFF_POOL:-0}" != "1" ]; then
+  echo "tools/sanitize.sh: not run. compute-sanitizer is closed on the GPU pool (profiles/r2_sanitizer_note.txt)." >&2
+  echo "On a GPU you own, set COMD_SANITIZE_OFF_POOL=1.  On the pool the stand-ins are the bit-identity tests across" >&2
+  echo "scheduling choices (tests/test_gpu_parity.py) and the ERRB_* guards of the force kernels." >&2
+  exit 3
+fi
 OUT=${1:-gpurun_out}
 mkdir -p "$OUT"
 rc=0
