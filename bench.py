@@ -235,17 +235,25 @@ def cpu_reference_rate(pot, procs=None):
                 pass
         shutil.rmtree(scratch, ignore_errors=True)
         if mpi or copies:
-            src = mpi if mpi else copies
+            # the baseline is the FASTER of the two ways of filling the cores (the copies carry no halo traffic and have come out
+            # ~8 % ahead in every recorded run): a speed-up quoted against this line is then against the best CPU figure measured
+            best_of = {"mpi_job": max(mpi.values(), key=lambda r: r["value"])["value"] if mpi else 0.0,
+                       "independent_copies": max(copies.values(), key=lambda r: r["value"])["value"] if copies else 0.0}
+            out["value_is"] = max(best_of, key=best_of.get)
+            src = mpi if out["value_is"] == "mpi_job" else copies
             best = max(src, key=lambda k: src[k]["value"])
             out["value"] = src[best]["value"]; out["build"] = best; out["per_core"] = out["value"] / procs
             out["sample_wall_s"] = src[best]["wall_s"]
-            if mpi:
-                out["sample"] = ("ONE job of %d cooperating ranks (%dx%dx%d, fork + shm MPI shim, -DDO_MPI): %s, %d^3 unit cells per rank "
-                                 "(%d atoms in all) x %d steps, -m cpu_nl" % (procs, grid[0], grid[1], grid[2], name, n, 4 * n ** 3 * procs, steps))
-                out["grid"] = "%dx%dx%d" % grid
+            mpi_text = ("ONE job of %d cooperating ranks (%dx%dx%d, fork + shm MPI shim, -DDO_MPI): %s, %d^3 unit cells per rank "
+                        "(%d atoms in all) x %d steps, -m cpu_nl" % (procs, grid[0], grid[1], grid[2], name, n, 4 * n ** 3 * procs, steps))
+            copies_text = "%d concurrent single-rank copies of: %s %dx%dx%d unit cells (%d atoms) x %d steps, -m cpu_nl" % (
+                procs, name, n, n, n, 4 * n ** 3, steps)
+            if out["value_is"] == "mpi_job":
+                out["sample"] = mpi_text + ("; also timed, slower: " + copies_text if copies else "")
             else:
-                out["sample"] = "%d concurrent single-rank copies of: %s %dx%dx%d unit cells (%d atoms) x %d steps, -m cpu_nl" % (
-                    procs, name, n, n, n, 4 * n ** 3, steps)
+                out["sample"] = copies_text + ("; also timed, slower: " + mpi_text if mpi else "")
+            if mpi:
+                out["grid"] = "%dx%dx%d" % grid
             out["mpi_job"] = {k: v["value"] for k, v in mpi.items()} or None
             out["independent_copies"] = {k: v["value"] for k, v in copies.items()} or None
             out["wall_s"] = round(time.time() - t0, 2)

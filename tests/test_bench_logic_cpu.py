@@ -89,6 +89,10 @@ def test_reference_arm_prints_one_contract_line(tmp_path):
                 "dtype", "data", "config", "cpu_baseline", "e2e"):
         assert key in j, key
     assert j["impl"] == "reference" and j["unit"] == "atom-steps/s" and j["higher_is_better"] is True and j["value"] > 1e5
-    assert j["cpu_baseline"]["kind"] == "reference" and j["cpu_baseline"]["cores"] >= 1 and "cooperating ranks" in j["cpu_baseline"]["sample"]
+    cb = j["cpu_baseline"]
+    assert cb["kind"] == "reference" and cb["cores"] >= 1 and "cooperating ranks" in cb["sample"] and "single-rank copies" in cb["sample"]
+    # the line's value is the FASTER of the two ways of filling the cores, and says which one it is
+    every = list((cb["mpi_job"] or {}).values()) + list((cb["independent_copies"] or {}).values())
+    assert cb["value_is"] in ("mpi_job", "independent_copies") and cb["value"] == max(every) == max(cb[cb["value_is"]].values())
     assert j["e2e"] == {"value": j["value"], "unit": "atom-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
     assert "workload" in j["config"] and "model" not in j["config"]
