@@ -448,6 +448,7 @@ extern "C" int comd_dev_create(ComdDev** out, int deviceId, const ComdGeometry* 
       comdSetError("comd_dev_create: no CUDA device (this library has no CPU fallback)");
       return COMD_E_CUDA;
    }
+   if (deviceId < 0 || deviceId >= COMD_MAX_DEVICES) { comdSetError("comd_dev_create: device id %d outside 0..%d", deviceId, COMD_MAX_DEVICES - 1); return COMD_E_ARG; }
    CUDA_TRY(cudaSetDevice(deviceId));
    ComdDev* d = new ComdDev();
    memset(d, 0, sizeof(ComdDev));
@@ -755,8 +756,10 @@ int comdCheckErrors(ComdDev* d, const char* where)
    if (e & ERRB_CAPACITY) { comdSetError("%s: atom or message capacity exceeded (capacity %ld atoms)", where, d->cap); return COMD_E_CAPACITY; }
    if (e & ERRB_ESCAPE) { comdSetError("%s: an atom moved more than one link cell beyond the local domain in one step", where); return COMD_E_STATE; }
    if (e & ERRB_FPMISMATCH) { comdSetError("%s: F' halo message does not match the ghost population", where); return COMD_E_MISMATCH; }
-   if (e & ERRB_TILE) { comdSetError("%s: a force tile exceeds its shared-memory staging capacity (density far above the lattice average)", where); return COMD_E_CAPACITY; }
-   if (e & ERRB_FIXED) { comdSetError("%s: a pair contribution left the fixed-point range of the in-block accumulators (atoms closer than ~1.5 A?)", where); return COMD_E_STATE; }
+   // the once-per-pair list kernels (force_n3.cuh) are the only list kernels with these two limits: say how to go on without them
+   const char* n3Hint = comdNlN3(d) ? "; forces of this evaluation are invalid -- set option \"nl_n3\" to 0 (full-list kernels, no such limit) and upload the atoms again" : "";
+   if (e & ERRB_TILE) { comdSetError("%s: a force tile / work block exceeds its shared-memory capacity (local density more than 1.3x the average)%s", where, n3Hint); return COMD_E_CAPACITY; }
+   if (e & ERRB_FIXED) { comdSetError("%s: a pair contribution (> 32 eV/A: atoms closer than ~1.5 A?) or a per-atom sum (> 256 eV/A) left the fixed-point range of the in-block accumulators%s", where, n3Hint); return COMD_E_STATE; }
    if (e & ERRB_NLFULL) { comdSetError("%s: neighbour-list row overflow", where); return COMD_E_CAPACITY; }
    comdSetError("%s: device error bits 0x%x", where, e);
    return COMD_E_STATE;

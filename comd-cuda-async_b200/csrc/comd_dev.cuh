@@ -14,6 +14,10 @@
 #include <stdint.h>
 #include "../../include/comd_b200.h"
 
+// Function attributes (dynamic shared-memory limit, carve-out) are per device; the launchers cache what they have set in
+// static tables indexed by ComdDev::device.  comd_dev_create refuses ids beyond the table.
+#define COMD_MAX_DEVICES 64
+
 // ---- precision (mytype.h:8-20; the reference's Makefile:73-77 switches -DCOMD_DOUBLE / -DCOMD_SINGLE) --------------
 // real_t is the type of every per-atom quantity, table and message on the device and across the C ABI (comd_real).
 // R(x) writes a literal of that type: in the double build it is the literal itself, so the FP64 code is unchanged.

@@ -754,3 +754,110 @@ def test_c4_c5_full_size_properties(workload):
     assert abs(sum(e1) - sum(e0)) <= (5e-5 if pot_kind == "lj" else 5e-6) * abs(sum(e0))   # the reference's own LJ run drifts 1.1e-5 (cut-and-shifted pair force), its EAM runs 4e-6
     assert dev.neighbor_counters()["builds"] >= 1
     dev.close()
+
+
+def _expect_error_then_recover(kind, gid, r, p, orc, n, code, words, nl_block=0):
+    """The once-per-pair list kernels (option nl_n3 1) must REPORT a configuration outside their limits at the next call
+    that returns data -- never hand back forces from a wrapped or skipped accumulator -- and the report names the way on:
+    nl_n3 0 and a fresh upload.  Following it gives the oracle's forces and energies for the very same atoms
+    (ljForce.c:146-265 / eam.c:266-419 compute any configuration; so does this library, through its full-list kernels)."""
+    dev, _ = device_for(orc, (n, n, n), nl_skin=0.1)
+    try:
+        dev.set_option("nl_n3", 1)
+        dev.set_option("nl_block", nl_block)
+        dev.upload(gid, r, p)
+        dev.compute_force()
+        with pytest.raises(pycomd.ComdError) as err:
+            dev.download()
+        assert err.value.code == code, str(err.value)
+        for w in words + ("nl_n3",):
+            assert w in str(err.value), str(err.value)
+        dev.set_option("nl_n3", 0)
+        dev.upload(gid, r, p)                                  # clears the sticky error bits, re-bins, rebuilds the list in full form
+        dev.compute_force()
+        d = by_gid(dev.download())
+    finally:
+        dev.close()
+    orc.set_atoms(gid, r, p)
+    o = by_gid(orc.atoms())
+    assert np.array_equal(d["gid"], o["gid"])
+    assert rel_err(d["f"], o["f"]) <= FORCE_TOL
+    assert rel_err(d["U"], o["U"] * u_scale(kind)) <= FORCE_TOL
+    return d
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("kind", ["lj", "funcfl"])
+def test_once_per_pair_kernels_report_a_pair_beyond_their_fixed_point_range(kind):
+    """Two atoms 1.2 A apart: their pair force is far beyond the +-32 eV/A one addend of the shared-memory fixed-point
+    accumulators can hold (force_n3.cuh).  ERRB_FIXED -> COMD_E_STATE, not a silently wrapped sum."""
+    n = 8
+    orc = oracle_sim(KINDS[kind], n, delta=0.0, temperature=300.0)
+    a = by_gid(orc.atoms())
+    lat = orc.potential()["lat"]
+    r = a["r"].copy()
+    centre = np.argmin(np.sum((r - 0.5 * n * lat) ** 2, axis=1))
+    other = np.argsort(np.sum((r - r[centre]) ** 2, axis=1))[1]         # a nearest neighbour: pulled in to 1.2 A along x
+    r[other] = r[centre] + np.array([1.2, 0.0, 0.0])
+    d = _expect_error_then_recover(kind, a["gid"], r, a["p"], orc, n, -4, ("fixed-point",))
+    assert np.max(np.abs(d["f"])) > 32.0                                 # the configuration really is outside the range
+
+
+@pytest.mark.gpu
+def test_once_per_pair_kernels_report_a_work_block_denser_than_their_accumulators():
+    """A crystal squeezed to 1.45x its density over the first 4 link cells along x (and thinned out over the rest): the work
+    block there holds more atoms than the launch sized its shared-memory accumulators for (1.3x the mean + 48).
+    ERRB_TILE -> COMD_E_CAPACITY, not forces with that block left out."""
+    kind, n, squeeze = "funcfl", 12, 1.45
+    orc = oracle_sim(KINDS[kind], n, delta=0.0, temperature=300.0)
+    a = by_gid(orc.atoms())
+    pot = orc.potential()
+    L = n * pot["lat"]
+    cells = int(L / (1.1 * pot["cutoff"]))                               # link cells per axis on cutoff + skin
+    edge = 4.2 * (L / cells)                                             # the squeezed slab covers the first block (4 cells) and a bit
+    x0 = edge * squeeze                                                  # original extent that is mapped onto [0, edge)
+    assert x0 < 0.95 * L
+    r = a["r"].copy()
+    x = r[:, 0]
+    r[:, 0] = np.where(x < x0, x / squeeze, edge + (x - x0) * (L - edge) / (L - x0))
+    assert r[:, 0].min() >= 0.0 and r[:, 0].max() < L
+    # (a domain this small would get one-cell work blocks, whose fixed slack of 48 slots hides any squeeze: ask for the
+    # 4x4x4-cell blocks a production-size domain runs with)
+    _expect_error_then_recover(kind, a["gid"], r, a["p"], orc, n, -3, ("work block",), nl_block=40404)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("pot_kind,n3", [("lj", 1), ("funcfl", 1), ("funcfl", 0)])
+def test_second_gpu_of_one_process_gets_its_own_kernel_attributes(pot_kind, n3):
+    """One process, two handles on two GPUs (the ABI takes a device id; CoMD.c:105-117 maps one rank to one GPU, a host
+    that drives several GPUs from one process is equally legal).  The dynamic shared-memory limit and carve-out of the list
+    kernels are per-device function attributes: the handle on GPU 1 must get them too, or its launches fail once the
+    accumulators exceed 48 KB.  Forces and energies on GPU 1 equal GPU 0's bit for bit.  Needs two GPUs; skipped on one."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs in one process")
+    kind = KINDS[pot_kind]
+    got = []
+    for device_id in (0, 1):
+        orc = oracle_sim(kind, 12, delta=0.05, temperature=600.0)
+        a = orc.atoms()
+        pot = orc.potential()
+        skin = 0.1 * pot["cutoff"]
+        geom = pycomd.make_geometry([12 * pot["lat"]] * 3, pot["cutoff"] + skin)
+        dev = pycomd.Device(geom, 4 * 12 ** 3 * 3 + 16384, device_id=device_id)
+        dev.set_mass(pot["mass"])
+        if kind == po.POT_LJ:
+            dev.set_lj(2.315, LJ_EPS, pot["cutoff"])
+        else:
+            dev.set_eam(pot["cutoff"], orc.table(0), orc.table(1), orc.table(2))
+        dev.set_neighbor_list(True, skin)
+        dev.set_option("nl_n3", n3)
+        dev.set_option("nl_block", 40404)                      # 4x4x4 cells: the largest accumulator block (> 48 KB for LJ)
+        dev.upload(a["gid"], a["r"], a["p"])
+        dev.compute_force()
+        dev.timestep(3, 1.0)
+        got.append((by_gid(dev.download()), dev.energy()))
+        dev.close()
+    (d0, e0), (d1, e1) = got
+    assert np.array_equal(d0["f"], d1["f"]) and np.array_equal(d0["r"], d1["r"]) and np.array_equal(d0["U"], d1["U"])
+    assert e0 == e1
