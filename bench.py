@@ -798,6 +798,15 @@ def main():
     }
     if not args.no_cpu_baseline:
         out["cpu_baseline"] = cpu_reference_rate(pot)
+    # LAST key of the line on purpose: the driver's records keep only the tail of stdout, and at N > 1 that tail is the only place
+    # the C4 LJ weak-scaling number (north_star's second scaling metric, BASELINE.json configs[3]) can survive in
+    w = secondary.get("lj_weak_C4")
+    out["scaling_summary"] = {
+        "n_gpus": world,
+        "eam_strong_C5": {"value": value, "ms_per_step": 1e3 * t_max / args.steps, "scaling": scaling} if args.workload == "eam_strong" else None,
+        "lj_weak_C4": ({"value": w["value"], "ms_per_step": w["ms_per_step"], "force_ms_per_step": w["force_ms_per_step"], "atoms": w["atoms"],
+                        "atoms_per_gpu": w["atoms_per_gpu"], "steps": w["steps"], "scaling": "weak", "unit": "atom-steps/s"} if w else None),
+        "note": "weak efficiency at N = lj_weak_C4.value(N) / (N * lj_weak_C4.value(1)); strong = eam_strong_C5.value(N) / (N * value(1))"}
     print(json.dumps(out))
     return 0 if (parity is None or parity["pass"]) else 1
 

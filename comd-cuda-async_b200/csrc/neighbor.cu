@@ -8,7 +8,9 @@
 //   neighborListUpdateRequired{Cpu,Gpu}                   neighborList.c:212-247, gpu_kernels.cu:1461-1480
 //   redistributeAtomsGpuNL (rebuild-or-refresh decision)  timestep.c:278-354
 //   unloadAtomsBuffer, in-place ghost update              haloExchange.c:1673-1683
-// The list is FULL (every local atom lists all its neighbours, like the reference's GPU lists),
+// The list is FULL (every local atom lists all its neighbours, like the reference's GPU lists) for the full-list kernels
+// (option nl_n3 0, LJ's default); for the once-per-pair kernels (nl_n3 1, EAM's default) a pair whose two atoms lie in the same
+// work block is stored on the lower row only and tagged (force_n3.cuh), every other pair on both rows.  Either way the rows are
 // row-major with a fixed stride, entries are indices into the sorted atom arrays (ghosts
 // included) in ascending order, i.e. cell-major / gid-minor: summation order stays canonical.
 #include "comd_dev.cuh"

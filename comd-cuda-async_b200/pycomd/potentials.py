@@ -21,8 +21,7 @@ LJ_CU = dict(sigma=2.315, epsilon=0.167, mass=63.55 * AMU_TO_INTERNAL_MASS, lat=
 
 def pot_dir():
     root = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-    for d in (os.environ.get("COMD_POT_DIR", ""), os.path.join(root, "pots"), os.path.join(root, "oracle", "_ref", "pots"),
-              "/root/reference/pots"):
+    for d in (os.environ.get("COMD_POT_DIR", ""), os.path.join(root, "pots"), "/root/reference/pots"):
         if d and os.path.exists(os.path.join(d, "Cu_u6.eam")):
             return d
     raise FileNotFoundError("EAM tables (Cu_u6.eam, Cu01.eam.alloy) not found; set COMD_POT_DIR or run build()")

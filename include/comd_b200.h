@@ -225,10 +225,10 @@ int  comd_dev_step_host(ComdDev* dev, int nLocal, double dt,
 /* A caller that hands the atoms of one comd_dev_step_host call to the next (same gids, same order, no
  * position further than skin/2 from the neighbour list's snapshot) is served without re-sorting and
  * without rebuilding the list; anything else takes the full upload path.  *nResumed counts the former.
- * On one rank, with pinned buffers and no other call on the handle in between, such a call does not wait
- * for its upload either: the step starts from the atoms the device handed out last time, the uploaded inputs
- * are compared with them bit for bit, and only if they differ is the step redone from the upload (after
- * which the handle stops speculating).  A result buffer may be the input buffer of the same quantity
+ * Every call waits for its upload before the step starts.  Only with option "e2e_speculate" 1 (off by default), on one
+ * rank, with pinned buffers and no other call on the handle in between, does such a call start early: from the atoms the
+ * device handed out last time, while the uploaded inputs are compared with them bit for bit; if they differ the step is
+ * redone from the upload and the handle stops speculating.  A result buffer may be the input buffer of the same quantity
  * (in-place update); a result buffer over the input of ANOTHER quantity switches the early start off. */
 int  comd_dev_step_host_stats(ComdDev* dev, long* nResumed);
 

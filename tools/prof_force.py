@@ -15,10 +15,12 @@ potential = P.load(pot)
 lat = potential["lat"]
 NL = int(os.environ.get("COMD_NL", "0"))
 skin = 0.1 * potential["cutoff"] if NL else 0.0
-geom = pycomd.make_geometry([n * lat] * 3, potential["cutoff"] + skin)
+PREC = os.environ.get("COMD_PREC", "f64")            # f32: the -DCOMD_SINGLE build (libcomd_b200_f32.so)
+T = pycomd.REAL[PREC]
+geom = pycomd.make_geometry([T(n) * T(lat)] * 3, T(T(potential["cutoff"]) + T(skin)), precision=PREC)
 gid, r = P.fcc_block([n] * 3, lat, [0.0] * 3, [n * lat] * 3)
 p = P.maxwell_momenta(len(gid), potential["mass"], 600.0, seed=7)
-dev = pycomd.Device(geom, int(len(gid) * 1.6) + 65536)
+dev = pycomd.Device(geom, int(len(gid) * 1.6) + 65536, precision=PREC)
 dev.set_mass(potential["mass"])
 if pot == "lj":
     dev.set_lj(potential["sigma"], potential["epsilon"], potential["cutoff"])
