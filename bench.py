@@ -58,6 +58,7 @@ NCU_DRAM = json.load(open(os.path.join(ROOT, "profiles", "ncu_dram_per_atom.json
 
 FORCE_TOL = 1e-12       # north_star: step-0 per-atom forces and energies, FP64, max-norm relative
 ENERGY100_TOL = 1e-6    # north_star: total energy at step 100
+DRIFT_TOL = (1e-11, 1e-12, 1e-11)   # drift case of the parity leg: total energy (relative), positions (A), forces (max-norm relative) after 60 steps
 
 
 def measured_peaks():
@@ -558,7 +559,9 @@ def parity_leg(R):
     rec["drift"] = {"steps": steps_d, "atoms_that_changed_rank": int(np.sum(sd["owner"] != own0)), "list_builds": nc["builds"], "ghost_refreshes": nc["refreshes"],
                     "energy_rel_err": abs(ed - eo2) / abs(eo2), "max_position_err_A": pos_err, "force_rel_err": f_err,
                     "owner_mismatches": int(np.sum(sd["owner"] != owner_of(sd["r"], gext, R.grid))), "atoms": int(len(sd["gid"]))}
-    ok &= rec["drift"]["energy_rel_err"] <= 1e-9 and pos_err <= 1e-8 and f_err <= 1e-6 and rec["drift"]["owner_mismatches"] == 0
+    # 60 steps of a drifting crystal against the oracle: measured 1.0e-13 / 2.8e-14 A / 1.4e-13 at N = 1, 2 and 8 (profiles/r2_v3_*, r3_*)
+    rec["drift"]["tolerances"] = {"energy_rel_err": DRIFT_TOL[0], "max_position_err_A": DRIFT_TOL[1], "force_rel_err": DRIFT_TOL[2]}
+    ok &= rec["drift"]["energy_rel_err"] <= DRIFT_TOL[0] and pos_err <= DRIFT_TOL[1] and f_err <= DRIFT_TOL[2] and rec["drift"]["owner_mismatches"] == 0
     ok &= len(sd["gid"]) == len(og["gid"]) and (R.world == 1 or rec["drift"]["atoms_that_changed_rank"] > 0)
     same_bits = lambda q: bool(all(np.array_equal(sd[k], q[k]) for k in ("gid", "r", "p", "f", "owner")))
     rec["sync_free_step_bit_identical_to_synchronised"] = same_bits(runs[1][0]) and runs[1][3] == nc
@@ -800,7 +803,7 @@ def main():
         out["cpu_baseline"] = cpu_reference_rate(pot)
     # LAST key of the line on purpose: the driver's records keep only the tail of stdout, and at N > 1 that tail is the only place
     # the C4 LJ weak-scaling number (north_star's second scaling metric, BASELINE.json configs[3]) can survive in
-    w = secondary.get("lj_weak_C4")
+    w = (secondary or {}).get("lj_weak_C4")           # --no-secondary leaves `secondary` None
     out["scaling_summary"] = {
         "n_gpus": world,
         "eam_strong_C5": {"value": value, "ms_per_step": 1e3 * t_max / args.steps, "scaling": scaling} if args.workload == "eam_strong" else None,
